@@ -1,0 +1,331 @@
+// quant.cu -- activation quantiser (standalone and fused into the RMSNorm epilogue), the
+// reference's weight quantisers, the unpacked-byte matmul of the KernelProvider seam, and the
+// one-time BitNet32-F16 plane split done at upload.
+#include "common.cuh"
+
+namespace b200 {
+
+// ---------------------------------------------------------------------------------------
+// block-wide reductions (blockDim.x multiple of 32, <= 1024)
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ float block_max(float v, float* sh) {
+    v = warp_max(v);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    if (lane == 0) sh[warp] = v;
+    __syncthreads();
+    float r = lane < nw ? sh[lane] : 0.f;
+    r = warp_max(r);
+    __syncthreads();
+    return r;
+}
+
+__device__ __forceinline__ double block_sum_f64(double v, double* sh) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    if (lane == 0) sh[warp] = v;
+    __syncthreads();
+    double r = lane < nw ? sh[lane] : 0.0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) r += __shfl_xor_sync(0xffffffffu, r, o);
+    __syncthreads();
+    return r;
+}
+
+// q = clamp(round_half_away(v * inv), -127, 127) as i8; NaN -> 0 (Rust `as i8`)
+__device__ __forceinline__ int quant1(float v, float inv) {
+    float r = roundf(v * inv);
+    if (r != r) return 0;
+    r = fminf(fmaxf(r, -127.f), 127.f);
+    return (int)r;
+}
+
+// ---------------------------------------------------------------------------------------
+// per-token absmax int8: quantize_symmetric_i8(row, 8), cpu/quantize.rs:32-49
+// one CTA per token row; optional fused RMSNorm (cpu/layer_norm.rs:118-137) in front
+// ---------------------------------------------------------------------------------------
+template <bool NORM>
+__global__ void __launch_bounds__(256) actquant_kernel(const float* __restrict__ x,
+                                                       const float* __restrict__ gamma, float eps,
+                                                       int K, int8_t* __restrict__ q,
+                                                       float* __restrict__ scale,
+                                                       float* __restrict__ normed) {
+    __shared__ float shf[32];
+    __shared__ double shd[32];
+    const int row = blockIdx.x, tid = threadIdx.x;
+    const float* xr = x + (size_t)row * K;
+    const bool vec = (K % 4 == 0) && ((reinterpret_cast<uintptr_t>(xr) & 15) == 0);
+
+    float inv_rms = 1.f;
+    if (NORM) {
+        double ss = 0.0;
+        for (int k = tid; k < K; k += blockDim.x) {
+            const double v = (double)xr[k];
+            ss += v * v;
+        }
+        ss = block_sum_f64(ss, shd);
+        const float ms = (float)(ss / (double)K);
+        inv_rms = 1.0f / sqrtf(ms + eps);
+    }
+    auto value = [&](int k) -> float {
+        float v = xr[k];
+        if (NORM) v = v * inv_rms * gamma[k];
+        return v;
+    };
+
+    float amax = 0.f;
+    for (int k = tid; k < K; k += blockDim.x) amax = fmaxf(amax, fabsf(value(k)));
+    amax = block_max(amax, shf);
+
+    const float sc = amax == 0.f ? 0.f : amax / 127.f;
+    const float inv = amax == 0.f ? 0.f : 1.0f / sc;
+    if (tid == 0) scale[row] = sc;
+
+    int8_t* qr = q + (size_t)row * K;
+    float* nr = normed ? normed + (size_t)row * K : nullptr;
+    if (vec && ((reinterpret_cast<uintptr_t>(qr) & 3) == 0)) {
+        for (int k4 = tid; k4 < K / 4; k4 += blockDim.x) {
+            const int k = k4 * 4;
+            const float v0 = value(k), v1 = value(k + 1), v2 = value(k + 2), v3 = value(k + 3);
+            int b0 = 0, b1 = 0, b2 = 0, b3 = 0;
+            if (amax != 0.f) {
+                b0 = quant1(v0, inv); b1 = quant1(v1, inv); b2 = quant1(v2, inv); b3 = quant1(v3, inv);
+            }
+            const uint32_t packed = (uint32_t)(uint8_t)b0 | ((uint32_t)(uint8_t)b1 << 8) |
+                                    ((uint32_t)(uint8_t)b2 << 16) | ((uint32_t)(uint8_t)b3 << 24);
+            *reinterpret_cast<uint32_t*>(qr + k) = packed;
+            if (nr) { nr[k] = v0; nr[k + 1] = v1; nr[k + 2] = v2; nr[k + 3] = v3; }
+        }
+    } else {
+        for (int k = tid; k < K; k += blockDim.x) {
+            const float v = value(k);
+            qr[k] = (int8_t)(amax == 0.f ? 0 : quant1(v, inv));
+            if (nr) nr[k] = v;
+        }
+    }
+}
+
+int launch_actquant(const bitnet_b200_ctx* ctx, const float* x, const float* gamma, float eps,
+                    int M, int K, int8_t* q, float* scale, float* normed, bool norm) {
+    if (M <= 0 || K <= 0) return fail("actquant: M and K must be > 0");
+    if (norm)
+        actquant_kernel<true><<<M, 256, 0, ctx->stream>>>(x, gamma, eps, K, q, scale, normed);
+    else
+        actquant_kernel<false><<<M, 256, 0, ctx->stream>>>(x, nullptr, 0.f, K, q, scale, normed);
+    B200_LAUNCH_CHECK("actquant_kernel");
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------
+// KernelProvider::quantize -- weight quantisers, cpu/fallback.rs:102-290
+// one warp per block of BLOCK elements; ORs 2-bit codes into `out` (caller zeroes)
+// ---------------------------------------------------------------------------------------
+__global__ void quantize_weights_kernel(const float* __restrict__ in, int len, uint8_t* out,
+                                        int out_len, float* __restrict__ scales, int block,
+                                        int qtype) {
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    const int nblocks = (len + block - 1) / block;
+    if (warp >= nblocks) return;
+    const int start = warp * block, end = min(start + block, len);
+    float mx = 0.f;
+    for (int i = start + lane; i < end; i += 32) mx = fmaxf(mx, fabsf(in[i]));
+    mx = warp_max(mx);
+    const float sc = mx > 1e-8f ? mx / 1.5f : 1.0f;
+    if (lane == 0) scales[warp] = sc;
+    // each lane owns whole output bytes (4 consecutive elements) so the OR needs no atomics
+    for (int b = start / 4 + lane; b * 4 < end; b += 32) {
+        uint32_t byte = 0;
+        for (int j = 0; j < 4; ++j) {
+            const int i = b * 4 + j;
+            if (i < start || i >= end) continue;
+            const float nv = in[i] / sc;
+            uint32_t code;
+            if (qtype == 0) {
+                code = nv > 0.5f ? 1u : (nv < -0.5f ? 3u : 0u);
+            } else {
+                const float l0 = qtype == 1 ? -1.0f : -1.2f, l1 = qtype == 1 ? -0.33f : -0.4f;
+                const float l2 = qtype == 1 ? 0.33f : 0.4f, l3 = qtype == 1 ? 1.0f : 1.2f;
+                float bd = fabsf(nv - l0);
+                code = 0;
+                float d = fabsf(nv - l1);
+                if (d < bd) { bd = d; code = 1; }
+                d = fabsf(nv - l2);
+                if (d < bd) { bd = d; code = 2; }
+                d = fabsf(nv - l3);
+                if (d < bd) { bd = d; code = 3; }
+            }
+            byte |= code << (2 * j);
+        }
+        if (b < out_len) out[b] |= (uint8_t)byte;
+    }
+}
+
+int launch_quantize_weights(cudaStream_t st, const float* in, int len, uint8_t* out, int out_len,
+                            float* scales, int qtype) {
+    const int block = qtype == 0 ? 32 : (qtype == 1 ? 64 : 128);
+    const int nblocks = (len + block - 1) / block;
+    const int threads = 256, wpb = threads / 32;
+    quantize_weights_kernel<<<(nblocks + wpb - 1) / wpb, threads, 0, st>>>(in, len, out, out_len,
+                                                                           scales, block, qtype);
+    B200_LAUNCH_CHECK("quantize_weights_kernel");
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------
+// KernelProvider::matmul_i2s on UNPACKED bytes: C[m,n] = sum_l a[m,l] * b[l,n]
+// (cpu/fallback.rs:39-83). b is [k, n] row-major, one byte per weight, any value 0..255.
+// Each thread owns 4 adjacent columns; a 4x4 byte block of b is transposed with PRMT so
+// that dp4a (signed a x unsigned b) consumes it. Up to 8 rows of a per pass, staged in smem.
+// ---------------------------------------------------------------------------------------
+constexpr int MM_ROWS = 8;
+__global__ void __launch_bounds__(128) matmul_u8_kernel(const int8_t* __restrict__ a,
+                                                        const uint8_t* __restrict__ b,
+                                                        float* __restrict__ c, int m, int n,
+                                                        int k) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint32_t* as = reinterpret_cast<uint32_t*>(smem_raw);  // [MM_ROWS][k4] words, zero padded
+    const int k4 = (k + 3) / 4;
+    const int m0 = blockIdx.y * MM_ROWS;
+    const int mr = min(MM_ROWS, m - m0);
+    for (int i = threadIdx.x; i < MM_ROWS * k4; i += blockDim.x) {
+        const int r = i / k4, kw = i % k4;
+        uint32_t wv = 0;
+        if (r < mr)
+            for (int j = 0; j < 4; ++j) {
+                const int kk = kw * 4 + j;
+                if (kk < k) wv |= (uint32_t)(uint8_t)a[(size_t)(m0 + r) * k + kk] << (8 * j);
+            }
+        as[i] = wv;
+    }
+    __syncthreads();
+    const int col0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (col0 >= n) return;
+    const bool full = (col0 + 4 <= n) && (n % 4 == 0);
+    int acc[MM_ROWS][4];
+#pragma unroll
+    for (int r = 0; r < MM_ROWS; ++r)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[r][j] = 0;
+    for (int kw = 0; kw < k4; ++kw) {
+        uint32_t rowsw[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int kk = kw * 4 + j;
+            uint32_t v = 0;
+            if (kk < k) {
+                const uint8_t* src = b + (size_t)kk * n + col0;
+                if (full) {
+                    v = *reinterpret_cast<const uint32_t*>(src);
+                } else {
+                    for (int t = 0; t < 4; ++t)
+                        if (col0 + t < n) v |= (uint32_t)src[t] << (8 * t);
+                }
+            }
+            rowsw[j] = v;
+        }
+        // transpose the 4x4 byte block: colw[t] = bytes t of rows 0..3
+        const uint32_t t01l = prmt(rowsw[0], rowsw[1], 0x5140u);  // r0b0 r1b0 r0b1 r1b1
+        const uint32_t t01h = prmt(rowsw[0], rowsw[1], 0x7362u);  // r0b2 r1b2 r0b3 r1b3
+        const uint32_t t23l = prmt(rowsw[2], rowsw[3], 0x5140u);
+        const uint32_t t23h = prmt(rowsw[2], rowsw[3], 0x7362u);
+        uint32_t colw[4];
+        colw[0] = prmt(t01l, t23l, 0x5410u);
+        colw[1] = prmt(t01l, t23l, 0x7632u);
+        colw[2] = prmt(t01h, t23h, 0x5410u);
+        colw[3] = prmt(t01h, t23h, 0x7632u);
+#pragma unroll
+        for (int r = 0; r < MM_ROWS; ++r) {
+            const uint32_t av = as[r * k4 + kw];
+#pragma unroll
+            for (int t = 0; t < 4; ++t) acc[r][t] = dp4a_su(av, colw[t], acc[r][t]);
+        }
+    }
+    for (int r = 0; r < mr; ++r)
+        for (int t = 0; t < 4; ++t)
+            if (col0 + t < n) c[(size_t)(m0 + r) * n + col0 + t] = (float)acc[r][t];
+}
+
+int launch_matmul_u8(cudaStream_t st, const int8_t* a, const uint8_t* b, float* c, int m, int n,
+                     int k) {
+    const size_t smem = (size_t)MM_ROWS * ((k + 3) / 4) * 4;
+    if (smem > 200 * 1024) return fail("matmul_i2s: k too large for the staging buffer");
+    if (smem > 48 * 1024)
+        B200_CUDA(cudaFuncSetAttribute(matmul_u8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)smem));
+    dim3 grid((unsigned)div_ceil((size_t)n, 4 * 128), (unsigned)div_ceil((size_t)m, MM_ROWS));
+    matmul_u8_kernel<<<grid, 128, smem, st>>>(a, b, c, m, n, k);
+    B200_LAUNCH_CHECK("matmul_u8_kernel");
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------
+// launch_i2s_matmul fill (cuda/quantized_matmul.rs:282-303; numerics of
+// cpu/quantized_matmul.rs:57-96): f32 activations, map C packed [n, ceil(k/4)], f32 scales
+// per (col, k-block). One CTA per output column, all m rows.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) i2s_matmul_f32_kernel(const float* __restrict__ act,
+                                                             const uint8_t* __restrict__ packed,
+                                                             const float* __restrict__ scales,
+                                                             float* __restrict__ out, int m, int n,
+                                                             int k, int bs) {
+    __shared__ float sh[4];
+    const int col = blockIdx.x, packed_k = (k + 3) / 4, nbk = (k + bs - 1) / bs;
+    for (int row = 0; row < m; ++row) {
+        float acc = 0.f;
+        for (int idx = threadIdx.x; idx < k; idx += blockDim.x) {
+            const uint32_t bits = (packed[(size_t)col * packed_k + idx / 4] >> ((idx % 4) * 2)) & 3u;
+            const float wv = bits == 1u ? 1.f : (bits == 3u ? -1.f : 0.f);
+            acc = fmaf(act[(size_t)row * k + idx], wv * scales[(size_t)col * nbk + idx / bs], acc);
+        }
+        acc = warp_sum(acc);
+        if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
+        __syncthreads();
+        if (threadIdx.x == 0) out[(size_t)row * n + col] = sh[0] + sh[1] + sh[2] + sh[3];
+        __syncthreads();
+    }
+}
+
+int launch_i2s_matmul_f32(cudaStream_t st, const float* act, const uint8_t* packed,
+                          const float* scales, float* out, int m, int n, int k, int bs) {
+    i2s_matmul_f32_kernel<<<n, 128, 0, st>>>(act, packed, scales, out, m, n, k, bs);
+    B200_LAUNCH_CHECK("i2s_matmul_f32_kernel");
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------
+// BitNet32-F16 upload: split [rows, cols/32, 10 B] into a code plane [rows, cols/4] and an
+// f16 scale plane [rows, cols/32] (lossless; 10-byte blocks cannot be loaded 16 B aligned)
+// ---------------------------------------------------------------------------------------
+__global__ void split_bitnet32_kernel(const uint8_t* __restrict__ src, size_t nblocks,
+                                      uint8_t* __restrict__ codes, __half* __restrict__ scales,
+                                      float* __restrict__ scales_f32, int clamp) {
+    const size_t b = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= nblocks) return;
+    const uint8_t* s = src + b * 10;
+    uint32_t lo = 0, hi = 0;
+    for (int j = 0; j < 4; ++j) {
+        lo |= (uint32_t)s[j] << (8 * j);
+        hi |= (uint32_t)s[4 + j] << (8 * j);
+    }
+    reinterpret_cast<uint2*>(codes)[b] = make_uint2(lo, hi);
+    const uint16_t hb = (uint16_t)(s[8] | (s[9] << 8));
+    scales[b] = __ushort_as_half(hb);
+    float sv = __half2float(__ushort_as_half(hb));
+    if (clamp) {
+        sv = fabsf(sv);
+        sv = sv < 1e-3f ? 1e-3f : sv;
+        sv = sv > 1e3f ? 1e3f : sv;
+    }
+    scales_f32[b] = sv;
+}
+
+int launch_split_bitnet32(cudaStream_t st, const uint8_t* src, size_t nblocks, uint8_t* codes,
+                          __half* scales, float* scales_f32, int clamp) {
+    const int threads = 256;
+    split_bitnet32_kernel<<<(unsigned)div_ceil(nblocks, threads), threads, 0, st>>>(
+        src, nblocks, codes, scales, scales_f32, clamp);
+    B200_LAUNCH_CHECK("split_bitnet32_kernel");
+    return 0;
+}
+
+}  // namespace b200

@@ -1,0 +1,145 @@
+"""Device-resident fast path (Part 3 of include/bitnet_b200.h) on torch CUDA tensors.
+
+torch is plumbing only: it owns device memory and the stream; every kernel that runs is
+from libbitnet_b200.so. Nothing here falls back to torch ops.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import ffi
+
+LAYOUT_QK256 = 0
+LAYOUT_BITNET32_F16 = 1
+SCALE_ABS_CLAMP = 0
+SCALE_RAW = 1
+MAP_A = (-2, -1, 1, 2)   # i2s_qk256.rs:139-146 -- production map of both layouts
+MAP_B = (-2, -1, 0, 1)   # quantization/src/utils.rs:76-91
+MAP_C = (0, 1, 0, -1)    # kernels/src/cpu/quantized_matmul.rs:19-27
+
+
+def _torch():
+    import torch
+    return torch
+
+
+def _dev_ptr(t, dtype, what):
+    torch = _torch()
+    if not (isinstance(t, torch.Tensor) and t.is_cuda and t.dtype == dtype and t.is_contiguous()):
+        raise TypeError("%s must be a contiguous CUDA tensor of %s" % (what, dtype))
+    return t.data_ptr()
+
+
+class Context:
+    """bitnet_b200_ctx: a device ordinal and the stream kernels are launched on.
+
+    By default it launches on torch's current stream of that device, so torch-side
+    allocation, events and CUDA-graph capture see the kernels."""
+
+    def __init__(self, device=0, stream="torch"):
+        torch = _torch()
+        self._lib = ffi.lib()
+        self.device = int(device)
+        if stream == "torch":
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+        h = C.c_void_p()
+        ffi.check(self._lib.bitnet_b200_ctx_create(self.device, C.c_void_p(stream or None), C.byref(h)))
+        self._h = h
+
+    def set_stream(self, cuda_stream):
+        ffi.check(self._lib.bitnet_b200_ctx_set_stream(self._h, C.c_void_p(cuda_stream or None)))
+
+    def synchronize(self):
+        ffi.check(self._lib.bitnet_b200_ctx_synchronize(self._h))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.bitnet_b200_ctx_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- weights ---------------------------------------------------------------------
+    def weight(self, host_bytes, layout, rows, cols, lut=None, scale_policy=SCALE_ABS_CLAMP):
+        return Weight(self, host_bytes, layout, rows, cols, lut, scale_policy)
+
+    # ---- activation quantisers -------------------------------------------------------
+    def actquant_i8(self, x, q=None, scale=None):
+        """quantize_symmetric_i8 per token row (cpu/quantize.rs:32-49) on device."""
+        torch = _torch()
+        M, K = x.shape
+        q = torch.empty((M, K), dtype=torch.int8, device=x.device) if q is None else q
+        scale = torch.empty((M,), dtype=torch.float32, device=x.device) if scale is None else scale
+        ffi.check(self._lib.bitnet_b200_actquant_i8(
+            self._h, _dev_ptr(x, torch.float32, "x"), M, K, _dev_ptr(q, torch.int8, "q"),
+            _dev_ptr(scale, torch.float32, "scale")))
+        return q, scale
+
+    def rmsnorm_actquant(self, x, gamma, eps=1e-5, q=None, scale=None, normed=None, want_normed=False):
+        """cpu::rms_norm (cpu/layer_norm.rs:118-137) with the act-quant fused in its epilogue."""
+        torch = _torch()
+        M, K = x.shape
+        q = torch.empty((M, K), dtype=torch.int8, device=x.device) if q is None else q
+        scale = torch.empty((M,), dtype=torch.float32, device=x.device) if scale is None else scale
+        if normed is None and want_normed:
+            normed = torch.empty((M, K), dtype=torch.float32, device=x.device)
+        ffi.check(self._lib.bitnet_b200_rmsnorm_actquant(
+            self._h, _dev_ptr(x, torch.float32, "x"), _dev_ptr(gamma, torch.float32, "gamma"),
+            C.c_float(eps), M, K, _dev_ptr(q, torch.int8, "q"), _dev_ptr(scale, torch.float32, "scale"),
+            None if normed is None else _dev_ptr(normed, torch.float32, "normed")))
+        return (q, scale, normed) if (want_normed or normed is not None) else (q, scale)
+
+    # ---- the ternary linear ------------------------------------------------------------
+    def linear_i8(self, w, q, act_scale, y=None, want_acc=False):
+        torch = _torch()
+        M = q.shape[0]
+        if q.shape[1] != w.cols:
+            raise ValueError("q has %d columns, weight has %d" % (q.shape[1], w.cols))
+        y = torch.empty((M, w.rows), dtype=torch.float32, device=q.device) if y is None else y
+        acc = None
+        if want_acc:
+            shape = (M, w.rows) if w.layout == LAYOUT_QK256 else (M, w.rows, w.cols // 32)
+            acc = torch.zeros(shape, dtype=torch.int32, device=q.device)
+        ffi.check(self._lib.bitnet_b200_linear_i8(
+            self._h, w._h, _dev_ptr(q, torch.int8, "q"), _dev_ptr(act_scale, torch.float32, "act_scale"),
+            M, _dev_ptr(y, torch.float32, "y"), None if acc is None else acc.data_ptr()))
+        return (y, acc) if want_acc else y
+
+    def linear_f32(self, w, x, y=None):
+        torch = _torch()
+        M = x.shape[0]
+        y = torch.empty((M, w.rows), dtype=torch.float32, device=x.device) if y is None else y
+        ffi.check(self._lib.bitnet_b200_linear_f32(
+            self._h, w._h, _dev_ptr(x, torch.float32, "x"), M, _dev_ptr(y, torch.float32, "y")))
+        return y
+
+
+class Weight:
+    """bitnet_b200_weight: one packed tensor uploaded once, in the reference's byte layout."""
+
+    def __init__(self, ctx, host_bytes, layout, rows, cols, lut=None, scale_policy=SCALE_ABS_CLAMP):
+        self._lib = ffi.lib()
+        host = np.ascontiguousarray(host_bytes, dtype=np.uint8).ravel()
+        lut_arr = None if lut is None else np.asarray(lut, dtype=np.int8)
+        h = C.c_void_p()
+        ffi.check(self._lib.bitnet_b200_weight_create(
+            ctx._h, host.ctypes.data, host.size, int(layout), int(rows), int(cols),
+            None if lut_arr is None else lut_arr.ctypes.data, int(scale_policy), C.byref(h)))
+        self._h = h
+        self.layout, self.rows, self.cols = int(layout), int(rows), int(cols)
+        self.nbytes = int(self._lib.bitnet_b200_weight_nbytes(h))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.bitnet_b200_weight_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -1,0 +1,149 @@
+/*
+ * bitnet_b200.h -- C ABI of libbitnet_b200.so: the B200 (sm_100a) implementation of
+ * BitNet-rs's I2_S ternary linear layer (QK256 and BitNet32-F16 layouts) and of the
+ * per-token absmax int8 activation quantiser that feeds it.
+ *
+ * Part 1 is a drop-in for the C bridge the reference already binds
+ *   (crates/bitnet-kernels/src/ffi/bridge.rs:17-39, ffi/cpp_bridge.cpp:34-297):
+ *   same six symbols, same argument meaning, same 0 / -1 + thread-local error string.
+ * Part 2 is the C twin of the free function the live transformer calls
+ *   (crates/bitnet-quantization/src/i2s_qk256.rs:346-372).
+ * Part 3 is additive: device-resident weights and activations, no per-call copies.
+ *
+ * Conventions (all parts): plain pointers and sizes, no C++/torch types; the caller owns
+ * every buffer for the duration of the call; every entry point is re-entrant and may be
+ * called concurrently from arbitrary host threads; int return 0 = ok, -1 = error, message
+ * via bitnet_cpp_get_last_error() (thread-local). There is NO CPU fallback: without a
+ * CUDA device every compute entry point fails with "no CUDA device".
+ *
+ * Paths cited below are relative to the BitNet-rs tree.
+ */
+#ifndef BITNET_B200_H
+#define BITNET_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------------------------ *
+ * Part 1 -- the reference's kernel bridge (KernelProvider seam)                          *
+ * ------------------------------------------------------------------------------------ */
+
+/* replaces ffi/cpp_bridge.cpp:34-53 (bound at ffi/bridge.rs:18). Reference-counted:
+ * several FfiKernel instances may coexist (bridge.rs:165-174,257-263). 0 = ok. */
+int bitnet_cpp_init(void);
+/* replaces ffi/cpp_bridge.cpp:287-297 (bridge.rs:19) */
+void bitnet_cpp_cleanup(void);
+/* replaces ffi/cpp_bridge.cpp:59-65 (bridge.rs:20): non-zero iff an sm_100 device is usable */
+int bitnet_cpp_is_available(void);
+/* replaces ffi/cpp_bridge.cpp:73-120 (bridge.rs:21-28); semantics of
+ * KernelProvider::matmul_i2s (crates/bitnet-kernels/src/lib.rs:42-50, cpu/fallback.rs:39-83):
+ *   a: m*k int8 row-major; b: k*n uint8 row-major, ONE BYTE PER WEIGHT (any value 0..255);
+ *   c: m*n f32 row-major, fully overwritten with sum_l a[i,l]*b[l,j].
+ * Host pointers; synchronous (results in c on return). Accumulates in int32 and converts
+ * once, which equals the reference's f32 accumulation whenever that is exact (|sum| < 2^24). */
+int bitnet_cpp_matmul_i2s(const int8_t* a, const uint8_t* b, float* c, int m, int n, int k);
+/* replaces ffi/cpp_bridge.cpp:127-278 (bridge.rs:29-37); semantics of
+ * KernelProvider::quantize (lib.rs:51-57, cpu/fallback.rs:85-290): the WEIGHT quantisers.
+ * qtype 0 = I2_S (32-blocks), 1 = TL1 (64), 2 = TL2 (128); scale = absmax/1.5 (1.0 if
+ * absmax <= 1e-8); 2-bit codes are OR-ed into `out` LSB-first (caller zeroes it).
+ * Needs out_len >= in_len/4 and scales_len >= ceil(in_len/block). Host pointers. */
+int bitnet_cpp_quantize(const float* in, int in_len, uint8_t* out, int out_len, float* scales,
+                        int scales_len, int qtype);
+/* replaces ffi/cpp_bridge.cpp:280-282 (bridge.rs:38): NULL when no error is pending */
+const char* bitnet_cpp_get_last_error(void);
+
+/* ------------------------------------------------------------------------------------ *
+ * Part 2 -- gemv_qk256 (the symbol the live decode/prefill loop calls)                   *
+ * ------------------------------------------------------------------------------------ */
+
+/* replaces bitnet_quantization::i2s_qk256::gemv_qk256 (i2s_qk256.rs:346-372; called from
+ * crates/bitnet-transformer/src/lib.rs:683-700 and :923-940). Host slices:
+ *   qs: rows*row_stride_bytes packed 2-bit codes, row_stride_bytes = ceil(cols/256)*64;
+ *   x: >= cols f32; y: exactly rows f32. y[r] = sum_c LUT_A[code(r,c)] * x[c], no scale,
+ *   LUT_A = {-2,-1,+1,+2}. Errors carry the reference's substrings "y_out length",
+ *   "x length", "too short" (i2s_qk256.rs:301-312). */
+int bitnet_b200_gemv_qk256(const uint8_t* qs, size_t qs_len, const float* x, size_t x_len,
+                           float* y, size_t y_len, size_t rows, size_t cols,
+                           size_t row_stride_bytes);
+
+/* ------------------------------------------------------------------------------------ *
+ * Part 3 -- additive device-resident API (the fast path)                                 *
+ * ------------------------------------------------------------------------------------ */
+
+typedef struct bitnet_b200_ctx bitnet_b200_ctx;       /* device ordinal + stream */
+typedef struct bitnet_b200_weight bitnet_b200_weight; /* one packed weight tensor in HBM */
+
+enum { BITNET_B200_LAYOUT_QK256 = 0,        /* I2SFlavor::GgmlQk256NoScale  (types.rs:797-806) */
+       BITNET_B200_LAYOUT_BITNET32_F16 = 1  /* I2SFlavor::BitNet32F16, 10 B per 32 weights      */ };
+enum { BITNET_B200_SCALE_ABS_CLAMP = 0,     /* s = clamp(|f16|, 1e-3, 1e3)  (quant/i2s.rs:76-94) */
+       BITNET_B200_SCALE_RAW = 1            /* s = f16 as stored                                 */ };
+
+/* device selection: counterpart of CudaKernel::new_with_device (gpu/cuda.rs:62).
+ * `stream` is a cudaStream_t (as void*) the context launches on, or NULL for its own. */
+int bitnet_b200_ctx_create(int device, void* stream, bitnet_b200_ctx** out);
+int bitnet_b200_ctx_set_stream(bitnet_b200_ctx* ctx, void* stream);
+int bitnet_b200_ctx_synchronize(bitnet_b200_ctx* ctx);
+void bitnet_b200_ctx_destroy(bitnet_b200_ctx* ctx);
+
+/* Upload one weight tensor, once, from host bytes in the reference's on-disk layout:
+ *   QK256: rows * ceil(cols/256)*64 bytes (I2SQk256NoScale, i2s_qk256.rs:65-107; +-128 B
+ *          trailing padding tolerated as there);
+ *   BITNET32_F16: rows * (cols/32) * 10 bytes, blocks along cols (quant/i2s.rs:621-692);
+ *          cols % 32 == 0 required.
+ * `lut` = code -> value map, 4 int8 (NULL = map A {-2,-1,1,2}). BitNet32-F16 is split
+ * on the device, losslessly, into a 16-byte-aligned code plane + f16 scale plane. */
+int bitnet_b200_weight_create(bitnet_b200_ctx* ctx, const void* host_bytes, size_t nbytes,
+                              int layout, size_t rows, size_t cols, const int8_t* lut,
+                              int scale_policy, bitnet_b200_weight** out);
+void bitnet_b200_weight_destroy(bitnet_b200_weight* w);
+size_t bitnet_b200_weight_rows(const bitnet_b200_weight* w);
+size_t bitnet_b200_weight_cols(const bitnet_b200_weight* w);
+/* packed bytes in the reference layout (the algorithmic weight bytes of one linear call) */
+size_t bitnet_b200_weight_nbytes(const bitnet_b200_weight* w);
+
+/* per-token absmax int8 activation quantiser, quantize_symmetric_i8(.., 8) per row
+ * (crates/bitnet-kernels/src/cpu/quantize.rs:32-49), bit-exact: scale = absmax/127,
+ * q = clamp(round_half_away(v * (1/scale)), -127, 127); all-zero row -> scale 0.
+ * x: [M,K] f32, q: [M,K] int8, scale: [M] f32 -- all DEVICE pointers. */
+int bitnet_b200_actquant_i8(bitnet_b200_ctx* ctx, const float* x, int M, int K, int8_t* q,
+                            float* scale);
+/* RMSNorm (cpu::rms_norm, crates/bitnet-kernels/src/cpu/layer_norm.rs:118-137: f64 mean of
+ * squares, x * (1/sqrt(ms+eps)) * gamma) with the act-quant fused into its epilogue.
+ * `normed` (DEVICE, [M,K] f32) may be NULL. */
+int bitnet_b200_rmsnorm_actquant(bitnet_b200_ctx* ctx, const float* x, const float* gamma,
+                                 float eps, int M, int K, int8_t* q, float* scale, float* normed);
+
+/* The ternary linear: y[m,n] = act_scale[m] * sum_blk s[n,blk] * acc_i32[m,n,blk], with
+ * acc = integer dot of LUT codes and int8 activations (QK256: one block, s = 1).
+ * q: [M,K] int8, act_scale: [M] f32, y: [M,N] f32 -- DEVICE pointers. M <= 16 runs the
+ * bandwidth-bound GEMV, M >= 64 the tcgen05 kind::i8 GEMM; between, whichever is faster.
+ * acc_out (DEVICE, may be NULL): QK256 -> [M,N] int32; BitNet32-F16 -> [M,N,K/32] int32.
+ * It exists so the bit-exact check can read the accumulators directly. */
+int bitnet_b200_linear_i8(bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, const int8_t* q,
+                          const float* act_scale, int M, float* y, int32_t* acc_out);
+/* f32-activation GEMV on a device-resident QK256 weight (device twin of Part 2):
+ * x: [M,K] f32, y: [M,N] f32, DEVICE pointers. */
+int bitnet_b200_linear_f32(bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, const float* x,
+                           int M, float* y);
+
+/* Host-slice fills of the reference's stubbed CUDA launchers:
+ *   launch_qk256_gemv (crates/bitnet-kernels/src/cuda/qk256_gemv.rs:119-137)
+ *   launch_i2s_matmul (crates/bitnet-kernels/src/cuda/quantized_matmul.rs:282-303):
+ * out[m,n] = sum_blk scales[n*nblk+blk] * sum_{k in blk} act[m,k] * LUT_C[code(n,k)],
+ * weights packed [n, ceil(k/4)] (map C {0,+1,0,-1}), f32 activations, block_size 32 or 256. */
+int bitnet_b200_i2s_matmul_f32(const float* act, const uint8_t* packed, const float* scales,
+                               float* out, int m, int n, int k, int block_size);
+
+/* library / build identification */
+const char* bitnet_b200_version(void);
+/* number of kernels this library has launched on the calling process (bench bookkeeping) */
+uint64_t bitnet_b200_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BITNET_B200_H */

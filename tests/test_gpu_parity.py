@@ -1,0 +1,409 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle. Needs a B200.
+
+Bar (BASELINE.json north_star): int32 accumulators bit-exact against the reference CPU
+kernel on identical packed weights and quantised activations; scaled fp32 outputs within
+1e-3 relative; int8 activation quantiser bit-exact."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+
+
+@pytest.fixture(scope="module")
+def ctx(b200):
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    c = b200.Context(0)
+    yield c
+    c.close()
+
+
+@pytest.fixture(scope="module")
+def kernel(b200):
+    k = b200.B200Kernel()
+    assert k.is_available() and k.name() == "b200"
+    yield k
+    k.close()
+
+
+def dev(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def _f(fn, n):
+    return np.array([fn(i) for i in range(n)])
+
+
+# =========================================================================================
+# KernelProvider::matmul_i2s (unpacked bytes) -- reference tests of cpu/fallback.rs, x86.rs
+# =========================================================================================
+def test_provider_matmul_identity(kernel):
+    # fallback.rs:305-318
+    c = np.zeros(4, np.float32)
+    kernel.matmul_i2s(np.array([1, 2, 3, 4], np.int8), np.array([1, 0, 0, 1], np.uint8), c, 2, 2, 2)
+    assert c.tolist() == [1.0, 2.0, 3.0, 4.0]
+
+
+def test_provider_matmul_dimension_validation(kernel, b200):
+    # fallback.rs:320-331
+    with pytest.raises(b200.KernelError, match="Matrix A dimension mismatch"):
+        kernel.matmul_i2s(np.array([1, 2], np.int8), np.array([1, 0], np.uint8), np.zeros(4, np.float32), 2, 2, 2)
+
+
+@pytest.mark.parametrize("m,n,k", [(3, 5, 7), (9, 13, 15), (17, 19, 33), (31, 27, 65), (2, 2, 2), (8, 8, 8),
+                                   (16, 16, 16), (7, 9, 11), (32, 32, 32), (33, 33, 33), (64, 64, 64)])
+def test_provider_matmul_reference_shapes(kernel, oracle, m, n, k):
+    # x86.rs:860-895 inputs (a=(idx%11)-5, b=(idx*3+7)%251): arbitrary byte values, not just codes
+    a = _f(lambda i: (i % 11) - 5, m * k).astype(np.int8)
+    b = _f(lambda i: (i * 3 + 7) % 251, k * n).astype(np.uint8)
+    c = np.full(m * n, np.nan, np.float32)
+    kernel.matmul_i2s(a, b, c, m, n, k)
+    assert np.array_equal(c.reshape(m, n), oracle.matmul_i2s(a, b, m, n, k, "fallback"))
+
+
+def test_provider_matmul_config1_shape(kernel, oracle):
+    # BASELINE.json configs[0]: 2560 -> 6912, batch 1, codes as the caller's `+2` bytes
+    m, k, n = 1, 2560, 6912
+    a = (oracle.fill_normal(m * k, 42) * 40).round().clip(-127, 127).astype(np.int8)
+    b = (oracle.fill_bytes(k * n, 0xB2000000) & 3).astype(np.uint8)
+    c = np.zeros(m * n, np.float32)
+    kernel.matmul_i2s(a, b, c, m, n, k)
+    ref = oracle.matmul_i2s(a, b, m, n, k, "avx2" if oracle.lib().oracle_has_avx2() else "fallback")
+    assert np.array_equal(c.reshape(m, n), ref)
+
+
+# =========================================================================================
+# KernelProvider::quantize -- weight quantisers
+# =========================================================================================
+def _lcg_input(size, seed):
+    # tests/gpu_quantization_parity.rs:19-52 style: LCG + diverse ranges
+    st = seed
+    out = np.zeros(size, np.float32)
+    for i in range(size):
+        st = (st * 1103515245 + 12345) % (1 << 64)
+        nrm = np.float32(st) / np.float32(2 ** 64)
+        out[i] = [2 * nrm - 1, 0.5 * (2 * nrm - 1), 1.5 if nrm > 0.5 else -1.5, 0.6 if nrm > 0.5 else -0.6,
+                  0.4 if nrm > 0.5 else -0.4, 0.0, 1e-6 * (2 * nrm - 1), 3 * (2 * nrm - 1)][i % 8]
+    return out
+
+
+@pytest.mark.parametrize("qtype", [0, 1, 2])
+@pytest.mark.parametrize("size", [32, 128, 1000, 4096, 65536])
+def test_provider_quantize_matches_cpu(kernel, oracle, b200, qtype, size):
+    x = _lcg_input(size, 12345 + size)
+    out = np.zeros((size + 3) // 4, np.uint8)
+    block = [32, 64, 128][qtype]
+    scales = np.zeros(-(-size // block), np.float32)
+    kernel.quantize(x, out, scales, b200.QuantizationType(qtype))
+    ro, rs = oracle.quantize(x, qtype)
+    assert np.array_equal(scales, rs)
+    assert np.array_equal(out, ro)
+
+
+def test_provider_quantize_edge_list_and_or_semantics(kernel, oracle, b200):
+    edge = np.array([0.0, 0.5, -0.5, 0.499, -0.499, 0.501, -0.501, 1.0, -1.0, 1.5, -1.5, 2.0, -2.0,
+                     1e-8, -1e-8, 1e8, -1e8, np.inf, -np.inf, 0.1, -0.1, 0.75, -0.75, 1e-30] + [0.0] * 8,
+                    np.float32)
+    out = np.zeros(edge.size // 4, np.uint8)
+    scales = np.zeros(1, np.float32)
+    kernel.quantize(edge, out, scales, b200.QuantizationType.I2S)
+    ro, rs = oracle.quantize(edge, 0)
+    assert np.array_equal(out, ro) and np.array_equal(scales, rs)
+    pre = np.full(edge.size // 4, 0xFF, np.uint8)
+    kernel.quantize(edge, pre, scales, b200.QuantizationType.I2S)
+    assert np.all(pre == 0xFF)      # ORs into the caller's bytes (fallback.rs:153)
+    with pytest.raises(b200.KernelError, match="Output buffer too small"):
+        kernel.quantize(np.ones(32, np.float32), np.zeros(1, np.uint8), np.zeros(1, np.float32), 0)
+
+
+# =========================================================================================
+# gemv_qk256 on host slices -- the live transformer's call
+# =========================================================================================
+def test_gemv_qk256_reference_known_answers(b200):
+    # i2s_qk256.rs:440-465, :633-683; qk256_integration.rs:117-148; qk256_dispatch.rs:106-119
+    x = np.arange(256, dtype=np.float32)
+    y = np.zeros(3, np.float32)
+    b200.gemv_qk256(np.full(3 * 64, 0x55, np.uint8), x, y, 3, 256, 64)
+    assert np.all(np.abs(y + x.sum()) < 1e-3)
+    for code in range(4):
+        byte = code | (code << 2) | (code << 4) | (code << 6)
+        y = np.zeros(4, np.float32)
+        b200.gemv_qk256(np.full(4 * 64, byte, np.uint8), np.ones(256, np.float32), y, 4, 256, 64)
+        assert np.all(y == [-2.0, -1.0, 1.0, 2.0][code] * 256)
+    y = np.zeros(256, np.float32)
+    b200.gemv_qk256(np.full(256 * 64, 0x55, np.uint8), np.full(256, 0.5, np.float32), y, 256, 256, 64)
+    assert np.all(y == -128.0)
+    # tail: cols = 300 (i2s_qk256.rs:419-437)
+    x = (np.arange(300) % 7).astype(np.float32)
+    y = np.zeros(1, np.float32)
+    b200.gemv_qk256(np.full(128, 0xAA, np.uint8), x, y, 1, 300, 128)
+    assert abs(y[0] - x.sum()) < 1e-3
+
+
+@pytest.mark.parametrize("rows,cols", [(1, 256), (16, 512), (33, 300), (7, 777), (640, 2560), (2560, 6912)])
+def test_gemv_qk256_vs_oracle(b200, oracle, rows, cols):
+    stride = -(-cols // 256) * 64
+    qs = oracle.fill_bytes(rows * stride, 0xB2000000 + rows)
+    x = oracle.fill_normal(cols, 42)
+    y = np.zeros(rows, np.float32)
+    b200.gemv_qk256(qs, x, y, rows, cols, stride)
+    ref = oracle.gemv_qk256(qs, x, rows, cols, stride, "scalar")
+    # the reference's own AVX2-vs-scalar bound (qk256_avx2_correctness.rs:53): 1e-4 abs-or-rel
+    d = np.abs(y - ref)
+    assert np.all((d <= 1e-4 * np.sqrt(cols / 256)) | (d <= 1e-4 * np.abs(ref)))
+    xi = (x * 40).round().clip(-127, 127).astype(np.float32)
+    b200.gemv_qk256(qs, xi, y, rows, cols, stride)
+    assert np.array_equal(y, oracle.gemv_qk256(qs, xi, rows, cols, stride))   # exact
+
+
+# =========================================================================================
+# per-token absmax int8 activation quantiser -- bit exact
+# =========================================================================================
+@pytest.mark.parametrize("M,K", [(1, 2560), (3, 6912), (16, 4096), (2, 14336), (5, 300), (4, 7), (64, 2560)])
+def test_actquant_bit_exact(ctx, oracle, M, K):
+    x = oracle.fill_normal(M * K, 42 + K).reshape(M, K)
+    x[0, : min(K, 8)] = [0.5, -0.5, 1.5, -1.5, 2.5, -2.5, 0.49999997, 126.5][: min(K, 8)]
+    q, s = ctx.actquant_i8(dev(x))
+    rq, rs = oracle.quantize_rows_i8(x)
+    assert np.array_equal(s.cpu().numpy(), rs)
+    assert np.array_equal(q.cpu().numpy(), rq)
+
+
+def test_actquant_edge_rows(ctx, oracle):
+    K = 2560
+    x = np.zeros((6, K), np.float32)
+    x[1, 17] = 3.0                                  # single spike -> 127
+    x[2] = oracle.fill_normal(K, 1)
+    x[2, 5] = x[2, 9] = -np.abs(x[2]).max()         # +-absmax ties
+    x[3] = (np.arange(K) % 255 - 127) * 0.5         # .5 rounding boundaries: absmax 63.5 -> inv 2
+    x[4] = 1e-30 * oracle.fill_normal(K, 2)         # tiny
+    x[5] = 1e30 * oracle.fill_normal(K, 3)          # huge
+    q, s = ctx.actquant_i8(dev(x))
+    rq, rs = oracle.quantize_rows_i8(x)
+    assert np.array_equal(s.cpu().numpy(), rs) and np.array_equal(q.cpu().numpy(), rq)
+    assert s[0].item() == 0.0 and not q[0].any().item()     # all-zero row -> scale 0 (quantize.rs:38-40)
+    assert q[1, 17].item() == 127
+
+
+@pytest.mark.parametrize("M,K", [(1, 2560), (4, 4096), (3, 6912), (2, 300)])
+def test_rmsnorm_actquant(ctx, oracle, M, K):
+    x = oracle.fill_normal(M * K, 7, 2.0).reshape(M, K)     # pre-norm hidden ~ N(0, 4)
+    g = oracle.fill_uniform(K, 8, 0.5, 1.5)
+    q, s, normed = ctx.rmsnorm_actquant(dev(x), dev(g), 1e-5, want_normed=True)
+    normed = normed.cpu().numpy()
+    ref = oracle.rms_norm(x, g, 1e-5)
+    assert np.max(np.abs(normed - ref) / (np.abs(ref) + 1e-6)) < 1e-6     # f64 mean, order differs
+    # the fused epilogue is exactly quantize_symmetric_i8 of the normalised row it produced
+    rq, rs = oracle.quantize_rows_i8(normed)
+    assert np.array_equal(s.cpu().numpy(), rs) and np.array_equal(q.cpu().numpy(), rq)
+    q2, s2 = ctx.rmsnorm_actquant(dev(x), dev(g), 1e-5)
+    assert torch.equal(q2, q) and torch.equal(s2, s)
+
+
+def test_rmsnorm_actquant_rejects_bad_eps(ctx, b200):
+    x = torch.zeros(1, 32, device="cuda")
+    with pytest.raises(b200.B200Error, match="eps"):
+        ctx.rmsnorm_actquant(x, torch.ones(32, device="cuda"), 0.0)
+
+
+# =========================================================================================
+# the ternary linear, QK256 -- int32 accumulators bit-exact
+# =========================================================================================
+SHAPES_2B = [(2560, 2560), (640, 2560), (3840, 2560), (6912, 2560), (13824, 2560), (2560, 6912)]
+
+
+def _qk256_case(oracle, rows, cols, M, seed):
+    stride = -(-cols // 256) * 64
+    qs = oracle.fill_bytes(rows * stride, 0xB2000000 + seed)
+    x = oracle.fill_normal(M * cols, 42 + seed).reshape(M, cols)
+    q, s = oracle.quantize_rows_i8(x)
+    return qs, q, s
+
+
+@pytest.mark.parametrize("rows,cols", [(8, 256), (9, 512), (33, 300), (7, 777), (100, 1024), (17, 4096)])
+@pytest.mark.parametrize("M", [1, 2, 3, 4, 5, 8, 9, 16, 17])
+def test_linear_qk256_small(ctx, b200, oracle, rows, cols, M):
+    qs, q, s = _qk256_case(oracle, rows, cols, M, rows + M)
+    w = ctx.weight(qs, b200.LAYOUT_QK256, rows, cols)
+    y, acc = ctx.linear_i8(w, dev(q), dev(s), want_acc=True)
+    racc, ry = oracle.linear_qk256_i8(qs, rows, cols, q, s)
+    assert np.array_equal(acc.cpu().numpy(), racc)
+    assert np.array_equal(y.cpu().numpy(), ry)          # one exact int->f32 and one multiply
+
+
+@pytest.mark.parametrize("rows,cols", SHAPES_2B + [(4096, 4096), (1024, 14336)])
+@pytest.mark.parametrize("M", [1, 16])
+def test_linear_qk256_model_shapes(ctx, b200, oracle, rows, cols, M):
+    qs, q, s = _qk256_case(oracle, rows, cols, M, rows ^ cols)
+    w = ctx.weight(qs, b200.LAYOUT_QK256, rows, cols)
+    assert w.nbytes == rows * cols // 4
+    y, acc = ctx.linear_i8(w, dev(q), dev(s), want_acc=True)
+    racc, ry = oracle.linear_qk256_i8(qs, rows, cols, q, s)   # the reference kernel itself (AVX2 gemv_qk256)
+    assert np.array_equal(acc.cpu().numpy(), racc)
+    assert np.array_equal(y.cpu().numpy(), ry)
+    y2 = ctx.linear_i8(w, dev(q), dev(s))                      # the no-accumulator path
+    assert torch.equal(y2, y)
+
+
+@pytest.mark.parametrize("lut_name", ["MAP_B", "MAP_C"])
+def test_linear_qk256_other_code_maps(ctx, b200, oracle, lut_name):
+    rows, cols, M = 64, 1024, 3
+    qs, q, s = _qk256_case(oracle, rows, cols, M, 5)
+    lut = getattr(oracle, lut_name)
+    w = ctx.weight(qs, b200.LAYOUT_QK256, rows, cols, lut=lut)
+    _, acc = ctx.linear_i8(w, dev(q), dev(s), want_acc=True)
+    racc, _ = oracle.linear_qk256_i8(qs, rows, cols, q, s, lut)
+    assert np.array_equal(acc.cpu().numpy(), racc)
+
+
+def test_linear_qk256_extreme_activations(ctx, b200, oracle):
+    # every activation +-127 and every code +-2: |acc| = 127*2*K, the F5 bound
+    rows, cols = 16, 14336
+    stride = cols // 4
+    qs = np.zeros((rows, stride), np.uint8)
+    qs[0::2] = 0xFF
+    qs[1::2] = 0x00
+    q = np.full((2, cols), 127, np.int8)
+    q[1] = -127
+    s = np.array([1.0, 0.5], np.float32)
+    w = ctx.weight(qs, b200.LAYOUT_QK256, rows, cols)
+    _, acc = ctx.linear_i8(w, dev(q), dev(s), want_acc=True)
+    racc, _ = oracle.linear_qk256_i8(qs.ravel(), rows, cols, q, s)
+    assert np.array_equal(acc.cpu().numpy(), racc)
+    assert abs(int(racc[0, 0])) == 127 * 2 * cols
+
+
+def test_linear_qk256_zero_row_and_padding(ctx, b200, oracle):
+    rows, cols = 12, 512
+    qs, q, s = _qk256_case(oracle, rows, cols, 3, 9)
+    q[1] = 0
+    s[1] = 0.0                                            # all-zero token: scale 0 -> outputs 0
+    padded = np.concatenate([qs, np.zeros(96, np.uint8)])  # +-128 B alignment padding tolerated
+    w = ctx.weight(padded, b200.LAYOUT_QK256, rows, cols)
+    y, acc = ctx.linear_i8(w, dev(q), dev(s), want_acc=True)
+    racc, ry = oracle.linear_qk256_i8(qs, rows, cols, q, s)
+    assert np.array_equal(acc.cpu().numpy(), racc) and np.array_equal(y.cpu().numpy(), ry)
+    assert not y[1].any().item()
+    with pytest.raises(b200.B200Error, match="data size mismatch"):
+        ctx.weight(np.zeros(rows * 128 + 129, np.uint8), b200.LAYOUT_QK256, rows, cols)
+
+
+def test_linear_f32_device(ctx, b200, oracle):
+    rows, cols, M = 640, 2560, 3
+    qs = oracle.fill_bytes(rows * cols // 4, 3)
+    x = oracle.fill_normal(M * cols, 4).reshape(M, cols)
+    w = ctx.weight(qs, b200.LAYOUT_QK256, rows, cols)
+    y = ctx.linear_f32(w, dev(x)).cpu().numpy()
+    for i in range(M):
+        ref = oracle.gemv_qk256(qs, x[i], rows, cols, cols // 4, "scalar")
+        d = np.abs(y[i] - ref)
+        assert np.all((d <= 1e-4 * np.sqrt(cols / 256)) | (d <= 1e-4 * np.abs(ref)))
+
+
+# =========================================================================================
+# the ternary linear, BitNet32-F16 -- per-block int32 bit-exact, scaled output within 1e-3
+# =========================================================================================
+def _rel(y, ref):
+    return np.max(np.abs(y - ref)) / (np.max(np.abs(ref)) + 1e-30)
+
+
+@pytest.mark.parametrize("rows,cols", [(4, 32), (9, 64), (33, 320), (17, 4096)] + SHAPES_2B)
+@pytest.mark.parametrize("M", [1, 3, 16])
+def test_linear_bitnet32(ctx, b200, oracle, rows, cols, M):
+    if rows * cols > 4_000_000 and M == 3:
+        pytest.skip("covered by M=1 and M=16")
+    data = oracle.make_bitnet32(rows, cols, 0xB2000000 + rows)
+    x = oracle.fill_normal(M * cols, 43 + rows).reshape(M, cols)
+    q, s = oracle.quantize_rows_i8(x)
+    w = ctx.weight(data, b200.LAYOUT_BITNET32_F16, rows, cols)
+    assert w.nbytes == rows * cols // 32 * 10
+    y, acc = ctx.linear_i8(w, dev(q), dev(s), want_acc=True)
+    racc, ry = oracle.linear_bitnet32_i8(data, rows, cols, q, s, want_blocks=True)
+    assert np.array_equal(acc.cpu().numpy(), racc)                 # per-32-block int32, bit exact
+    y = y.cpu().numpy()
+    assert _rel(y, ry) < 1e-5                                      # same math, different fp32 sum order
+    assert _rel(y, oracle.linear_bitnet32_dequant(data, rows, cols, q, s)) < 1e-3   # the north_star bar
+    assert torch.equal(ctx.linear_i8(w, dev(q), dev(s)).cpu(), torch.from_numpy(y)) or \
+        _rel(ctx.linear_i8(w, dev(q), dev(s)).cpu().numpy(), y) < 1e-6
+
+
+@pytest.mark.parametrize("policy", ["SCALE_ABS_CLAMP", "SCALE_RAW"])
+def test_linear_bitnet32_scale_edge_cases(ctx, b200, oracle, policy):
+    # quant/i2s.rs:1007-1057: zero / negative / inf / tiny / max f16 scales
+    rows, cols, M = 8, 64, 2
+    data = oracle.make_bitnet32(rows, cols, 11).reshape(-1, 10)
+    specials = [0x0000, 0xB800, 0x7C00, 0x0001, 0x7BFF, 0x8000, 0x3C00, 0x1400]   # 0,-0.5,inf,denorm,65504,-0,1,~1e-3
+    for i, bits in enumerate(specials):
+        data[i, 8] = bits & 0xFF
+        data[i, 9] = bits >> 8
+    if policy == "SCALE_RAW":
+        data[2, 8:10] = [0x00, 0x3C]        # raw policy: keep inf out of the sum
+    x = oracle.fill_normal(M * cols, 5).reshape(M, cols)
+    q, s = oracle.quantize_rows_i8(x)
+    pol = getattr(b200, policy)
+    w = ctx.weight(data.ravel(), b200.LAYOUT_BITNET32_F16, rows, cols, scale_policy=pol)
+    y = ctx.linear_i8(w, dev(q), dev(s)).cpu().numpy()
+    ry = oracle.linear_bitnet32_i8(data.ravel(), rows, cols, q, s, scale_policy=pol)
+    assert np.all(np.isfinite(y))
+    assert _rel(y, ry) < 1e-5
+
+
+def test_linear_bitnet32_rejects_bad_sizes(ctx, b200):
+    with pytest.raises(b200.B200Error, match="size mismatch"):
+        ctx.weight(np.zeros(79, np.uint8), b200.LAYOUT_BITNET32_F16, 4, 64)
+    with pytest.raises(b200.B200Error, match="cols % 32"):
+        ctx.weight(np.zeros(80, np.uint8), b200.LAYOUT_BITNET32_F16, 4, 40)
+
+
+# =========================================================================================
+# launch_i2s_matmul fill (map C, f32 activations, per-block f32 scales)
+# =========================================================================================
+def test_i2s_matmul_f32_reference_vectors(b200, oracle):
+    def run(act, packed, scales, m, n, k, bs):
+        out = np.full(m * n, np.nan, np.float32)
+        b200.i2s_matmul_f32(np.asarray(act, np.float32), np.asarray(packed, np.uint8),
+                            np.asarray(scales, np.float32), out, m, n, k, bs)
+        return out.tolist()
+    p = oracle.pack_i2s([1, 1, 1, 1])
+    assert run([1, 2, 3, 4], [p, p], [1, 1], 1, 2, 4, 4) == [10.0, 10.0]            # snapshot [10,10]
+    assert run([1, 2, 3, 4], [oracle.pack_i2s([1, -1, 0, 1])], [2.0], 1, 1, 4, 4) == [6.0]   # snapshot [6]
+    assert run(np.ones(64), np.full(16, 0b01010101), [1.0, 3.0], 1, 1, 64, 32) == [128.0]   # :589-613
+    m, n, k = 5, 37, 512
+    packed = oracle.fill_bytes(n * k // 4, 21)
+    act = oracle.fill_normal(m * k, 22)
+    scales = oracle.fill_uniform(n * (k // 32), 23, 0.5, 1.5)
+    out = np.zeros(m * n, np.float32)
+    b200.i2s_matmul_f32(act, packed, scales, out, m, n, k, 32)
+    ref = oracle.i2s_matmul(act, packed, scales, m, n, k, 32, "f32")
+    assert _rel(out.reshape(m, n), ref) < 1e-5
+    with pytest.raises(b200.KernelError, match="scales too small"):
+        b200.i2s_matmul_f32(np.ones(64, np.float32), np.zeros(16, np.uint8), np.ones(1, np.float32),
+                            np.zeros(1, np.float32), 1, 1, 64, 32)
+
+
+# =========================================================================================
+# threading: every export is re-entrant
+# =========================================================================================
+def test_concurrent_host_threads(b200, oracle):
+    import threading
+    rows, cols = 64, 512
+    qs = oracle.fill_bytes(rows * cols // 4, 31)
+    errs = []
+
+    def work(i):
+        try:
+            k = b200.B200Kernel()
+            x = (oracle.fill_normal(cols, 100 + i) * 20).round().astype(np.float32)
+            y = np.zeros(rows, np.float32)
+            for _ in range(3):
+                b200.gemv_qk256(qs, x, y, rows, cols, cols // 4)
+                assert np.array_equal(y, oracle.gemv_qk256(qs, x, rows, cols, cols // 4, "scalar"))
+            k.close()
+        except Exception as e:  # noqa: BLE001
+            errs.append(e)
+
+    ts = [threading.Thread(target=work, args=(i,)) for i in range(4)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    assert not errs, errs
