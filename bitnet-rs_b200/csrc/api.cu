@@ -232,20 +232,11 @@ int bitnet_b200_ctx_create(int device, void* stream, bitnet_b200_ctx** out) {
         auto* c = new bitnet_b200_ctx();
         c->device = device;
         c->num_sms = prop.multiProcessorCount;
-        if (stream) {
-            c->stream = reinterpret_cast<cudaStream_t>(stream);
-        } else {
-            cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
-            if (e != cudaSuccess) {
-                delete c;
-                return fail_cuda("cudaStreamCreateWithFlags", e);
-            }
-            c->owns_stream = true;
-        }
+        // NULL is a real stream: the legacy default stream (what torch uses by default)
+        c->stream = reinterpret_cast<cudaStream_t>(stream);
         cudaError_t e = cudaMalloc(&c->workspace, 4096);
         if (e == cudaSuccess) e = cudaMemsetAsync(c->workspace, 0, 4096, c->stream);
         if (e != cudaSuccess) {
-            if (c->owns_stream) cudaStreamDestroy(c->stream);
             delete c;
             return fail_cuda("cudaMalloc(workspace)", e);
         }
@@ -258,10 +249,6 @@ int bitnet_b200_ctx_create(int device, void* stream, bitnet_b200_ctx** out) {
 
 int bitnet_b200_ctx_set_stream(bitnet_b200_ctx* ctx, void* stream) {
     if (!ctx) return fail("ctx is NULL");
-    if (ctx->owns_stream) {
-        cudaStreamDestroy(ctx->stream);
-        ctx->owns_stream = false;
-    }
     ctx->stream = reinterpret_cast<cudaStream_t>(stream);
     return 0;
 }
@@ -276,7 +263,6 @@ void bitnet_b200_ctx_destroy(bitnet_b200_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     if (ctx->workspace) cudaFree(ctx->workspace);
-    if (ctx->owns_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
 
@@ -440,8 +426,10 @@ int bitnet_b200_gemv_qk256(const uint8_t* qs, size_t qs_len, const float* x, siz
         }
         int dev;
         if (need_device(&dev)) return -1;
+        StreamGuard sg;  // own non-blocking stream: concurrent host threads do not serialise
+        if (sg.create()) return -1;
         bitnet_b200_ctx* ctx = nullptr;
-        if (bitnet_b200_ctx_create(dev, nullptr, &ctx)) return -1;
+        if (bitnet_b200_ctx_create(dev, sg.s, &ctx)) return -1;
         std::unique_ptr<bitnet_b200_ctx, void (*)(bitnet_b200_ctx*)> cg(ctx, bitnet_b200_ctx_destroy);
         bitnet_b200_weight* w = nullptr;
         if (bitnet_b200_weight_create(ctx, qs, rows * row_stride_bytes, BITNET_B200_LAYOUT_QK256, rows,

@@ -45,7 +45,6 @@ inline size_t div_ceil(size_t a, size_t b) { return (a + b - 1) / b; }
 struct bitnet_b200_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
-    bool owns_stream = false;
     int num_sms = 148;
     int* workspace = nullptr;  // small device scratch (tile counters etc.)
 };

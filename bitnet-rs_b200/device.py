@@ -47,7 +47,12 @@ class Context:
         self._h = h
 
     def set_stream(self, cuda_stream):
+        """Launch on this cudaStream_t from now on (0 / None = the legacy default stream)."""
         ffi.check(self._lib.bitnet_b200_ctx_set_stream(self._h, C.c_void_p(cuda_stream or None)))
+
+    def use_torch_stream(self):
+        """Re-bind to torch's current stream (call inside `torch.cuda.graph(...)` / `stream(...)`)."""
+        self.set_stream(_torch().cuda.current_stream(self.device).cuda_stream)
 
     def synchronize(self):
         ffi.check(self._lib.bitnet_b200_ctx_synchronize(self._h))

@@ -83,7 +83,8 @@ enum { BITNET_B200_SCALE_ABS_CLAMP = 0,     /* s = clamp(|f16|, 1e-3, 1e3)  (qua
        BITNET_B200_SCALE_RAW = 1            /* s = f16 as stored                                 */ };
 
 /* device selection: counterpart of CudaKernel::new_with_device (gpu/cuda.rs:62).
- * `stream` is a cudaStream_t (as void*) the context launches on, or NULL for its own. */
+ * `stream` is the cudaStream_t (as void*) the context launches on; NULL is the legacy
+ * default stream. The context never owns the stream. */
 int bitnet_b200_ctx_create(int device, void* stream, bitnet_b200_ctx** out);
 int bitnet_b200_ctx_set_stream(bitnet_b200_ctx* ctx, void* stream);
 int bitnet_b200_ctx_synchronize(bitnet_b200_ctx* ctx);

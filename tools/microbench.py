@@ -27,6 +27,30 @@ def rand_weight(ctx, layout, rows, cols, seed):
     return ctx.weight(data, layout, rows, cols)
 
 
+def graph_time(ctx, fn, iters, reps=5):
+    """Capture `iters` back-to-back launches in one CUDA graph; time replays with events."""
+    for i in range(3):
+        fn(i)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        ctx.use_torch_stream()
+        for i in range(iters):
+            fn(i)
+    ctx.use_torch_stream()
+    g.replay()
+    torch.cuda.synchronize()
+    best = 1e30
+    for _ in range(reps):
+        e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+        e0.record()
+        g.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1) * 1e3 / iters)
+    return best
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--ms", default="1,2,4,8,16")
@@ -52,16 +76,7 @@ def main():
                 q = torch.randint(-127, 128, (M, cols), dtype=torch.int8, device="cuda")
                 s = torch.rand(M, device="cuda") + 0.5
                 y = torch.empty(M, rows, device="cuda")
-                for i in range(10):
-                    ctx.linear_i8(ws[i % len(ws)], q, s, y=y)
-                torch.cuda.synchronize()
-                e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
-                e0.record()
-                for i in range(args.iters):
-                    ctx.linear_i8(ws[i % len(ws)], q, s, y=y)
-                e1.record()
-                torch.cuda.synchronize()
-                us = e0.elapsed_time(e1) * 1e3 / args.iters
+                us = graph_time(ctx, lambda i: ctx.linear_i8(ws[i % len(ws)], q, s, y=y), args.iters)
                 alg = wbytes + M * cols + 4 * M + 4 * M * rows
                 print(json.dumps({"kernel": "linear_i8", "layout": lname, "shape": sname, "N": rows, "K": cols,
                                   "M": M, "us": round(us, 3), "alg_bytes": alg,
@@ -75,17 +90,11 @@ def main():
             x = torch.randn(M, K, device="cuda")
             g = torch.rand(K, device="cuda") + 0.5
             for fused in (False, True):
-                fn = (lambda: ctx.rmsnorm_actquant(x, g, 1e-5)) if fused else (lambda: ctx.actquant_i8(x))
-                for _ in range(5):
-                    fn()
-                torch.cuda.synchronize()
-                e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
-                e0.record()
-                for _ in range(100):
-                    fn()
-                e1.record()
-                torch.cuda.synchronize()
-                us = e0.elapsed_time(e1) * 10
+                qb = torch.empty(M, K, dtype=torch.int8, device="cuda")
+                sb = torch.empty(M, device="cuda")
+                fn = (lambda i: ctx.rmsnorm_actquant(x, g, 1e-5, q=qb, scale=sb)) if fused else \
+                    (lambda i: ctx.actquant_i8(x, q=qb, scale=sb))
+                us = graph_time(ctx, fn, 50)
                 alg = M * K * 5 + 4 * M
                 print(json.dumps({"kernel": "rmsnorm_actquant" if fused else "actquant_i8", "M": M, "K": K,
                                   "us": round(us, 3), "GBs": round(alg / us / 1e3, 1)}), flush=True)
