@@ -1,0 +1,304 @@
+#!/usr/bin/env python
+"""bench.py -- BitNet b1.58-2B-4T-shape batch-1 decode on B200 (BASELINE.json configs[1]).
+
+  python bench.py --gpus N --steps K --warmup W          (N > 1: launched by torchrun)
+  python bench.py --impl reference ...                   (the reference's CPU path, host cores)
+
+A "step" is one decode step: one token per sequence through all 30 layers (RMSNorm+act-quant,
+ternary q/k/v/o/gate/up/down linears, RoPE, KV append, GQA attention, SwiGLU glue), the final
+norm, the tied-embedding logits and the greedy argmax. Prints ONE JSON line (rank 0).
+
+  value     tok/s with the token fed back on device (inputs resident in HBM), CUDA events
+  e2e       tok/s through the C-ABI decode call with HOST buffers: token ids H2D and the
+            greedy token D2H every step, inside the timed region
+  roofline  the ternary GEMVs of one step (4 fused launches per layer, 521 MB of packed
+            weights > L2) replayed back to back: algorithmic bytes / measured time vs the
+            measured HBM copy peak
+  cpu_baseline  the CPU oracle (C++ restatement of the reference's AVX2 kernels) on a bounded
+            sample, on this box's host cores
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+PROMPT = 32  # default; --prompt overrides
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=64)
+    ap.add_argument("--warmup", type=int, default=8)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--layout", default="qk256", choices=["qk256", "bitnet32"])
+    ap.add_argument("--prompt", type=int, default=32, help="synthetic prompt tokens decoded before timing")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-budget-s", type=float, default=20.0)
+    return ap.parse_args()
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks and throttle reasons DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                 "-lms", "50"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.12)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+                for n, v in zip(names, r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def linear_alg_bytes(shape, M):
+    """W + M*K + 4*M + 4*M*N per linear call, reference-layout weight bytes."""
+    qd, kd = shape.n_heads * shape.head_dim, shape.n_kv_heads * shape.head_dim
+    fused = [(qd + 2 * kd, shape.hidden), (shape.hidden, qd), (2 * shape.ffn, shape.hidden),
+             (shape.hidden, shape.ffn)]
+    return shape.n_layers * sum(n * shape.row_bytes(k) + M * k + 4 * M + 4 * M * n for n, k in fused)
+
+
+# ------------------------------------------------------------------------------------------
+# CPU arm: the oracle model (C++ restatement of the reference's kernels) on host cores
+# ------------------------------------------------------------------------------------------
+def cpu_decode_tok_s(shape_full, steps, warmup, budget_s):
+    """tok/s of the CPU path for the full shape, from 1-layer and 3-layer decoders timed on
+    `steps` full-vocab decode steps each and extrapolated linearly in the layer count."""
+    import bitnet_rs_b200 as b2
+    from oracle import pyoracle as orc
+
+    threads = os.cpu_count() or 1
+    emb, fn = b2.synth_embedding(shape_full)
+    cos_t, sin_t = b2.rope_tables(shape_full)
+    per = {}
+    t_start = time.perf_counter()
+    done_steps = steps
+    for n in (1, 3):
+        sh = b2.ModelShape(**{**shape_full.__dict__, "n_layers": n})
+        m = orc.Model(sh, threads=threads)
+        for l in range(n):
+            m.set_layer(l, b2.synth_layer(shape_full, l))
+        m.set_embedding(emb, fn)
+        m.set_rope(cos_t, sin_t)
+        tok = 42
+        for _ in range(min(warmup, 3)):
+            tok = m.step(tok)
+        times = []
+        for i in range(steps):
+            t0 = time.perf_counter()
+            tok = m.step(tok)
+            times.append(time.perf_counter() - t0)
+            if time.perf_counter() - t_start > budget_s * (0.5 if n == 1 else 1.0) and i >= 2:
+                break
+        done_steps = min(done_steps, len(times))
+        per[n] = float(np.mean(times))
+        m.close()
+    a = max((per[3] - per[1]) / 2.0, 1e-9)          # seconds per layer
+    b = max(per[1] - a, 0.0)                        # embedding + final norm + logits + argmax
+    t_full = a * shape_full.n_layers + b
+    sample = ("%d full-vocab decode steps each of a 1-layer and a 3-layer 2B-4T-shape decoder "
+              "(%.1f ms and %.1f ms per step), extrapolated linearly to %d layers; oracle = C++ "
+              "restatement of gemv_qk256_avx2 + quantize_symmetric_i8 + rms_norm, rows split over %d threads"
+              % (done_steps, per[1] * 1e3, per[3] * 1e3, shape_full.n_layers, threads))
+    return 1.0 / t_full, threads, sample, t_full, done_steps
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import bitnet_rs_b200 as b2
+    layout = b2.LAYOUT_QK256 if args.layout == "qk256" else b2.LAYOUT_BITNET32_F16
+    shape = b2.ModelShape.bitnet_2b4t(max_ctx=PROMPT + 2 * (args.warmup + args.steps) + 8, layout=layout)
+    steps = min(args.steps, 100)
+    v, cores, sample, t_full, done = cpu_decode_tok_s(shape, steps, args.warmup, 150.0)
+    if done < args.steps:
+        sample += "; %d of the requested %d steps were timed (bounded sample)" % (done, args.steps)
+    line = {
+        "impl": "reference", "metric": "2B-4T decode tok/s", "value": v, "unit": "tok/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": t_full * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8", "data": "synthetic",
+        "config": workload_config(shape, args),
+        "cpu_baseline": {"value": v, "unit": "tok/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(shape, args):
+    return {
+        "workload": "BitNet b1.58-2B-4T-shape full decode (30 layers, hidden 2560, FFN 6912, GQA 20/5, "
+                    "vocab 128256), random-init I2_S weights, batch 1 per GPU (BASELINE.json configs[1])",
+        "layout": "QK256" if shape.layout == 0 else "BitNet32-F16",
+        "batch_per_gpu": shape.batch, "prompt_tokens": PROMPT,
+        "parallelism": "1 GPU" if args.gpus == 1 else "%d independent replicas (one request stream per GPU)" % args.gpus,
+        "l2": "inputs larger than L2: %.0f MB of packed ternary weights + 657 MB f16 LM head per step vs 126 MB L2"
+              % (shape.ternary_bytes() / 1e6),
+    }
+
+
+def main():
+    global PROMPT
+    args = parse()
+    PROMPT = args.prompt
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import bitnet_rs_b200 as b2
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU arm")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    K, W = args.steps, max(args.warmup, 3)
+    layout = b2.LAYOUT_QK256 if args.layout == "qk256" else b2.LAYOUT_BITNET32_F16
+    shape = b2.ModelShape.bitnet_2b4t(max_ctx=PROMPT + 2 * (W + K) + 8, layout=layout)
+    ctx = b2.Context(local)
+    model = b2.Model(ctx, shape)
+    model.load_synthetic()
+    B = shape.batch
+
+    # prompt: 32 synthetic token ids (i * 7919 mod vocab), one decode step each
+    tok = None
+    for i in range(PROMPT):
+        tok = model.decode(np.array([(i * 7919 + rank) % shape.vocab] * B, np.int32))
+
+    sampler = ClockSampler(local)
+    launches0 = b2.launch_count()
+
+    # ---- value: device-resident greedy loop, CUDA events --------------------------------
+    model.decode_device(W)
+    barrier()
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    model.decode_device(K)
+    e1.record()
+    barrier()
+    ms_dev = e0.elapsed_time(e1)
+    launches_timed = b2.launch_count() - launches0 - W * model.launches_per_step
+
+    # ---- e2e: the C-ABI decode call with host buffers, copies inside the timed region ----
+    tok = model.get_tokens()
+    for _ in range(W):
+        tok = model.decode(tok)
+    barrier()
+    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e2.record()
+    for _ in range(K):
+        tok = model.decode(tok)
+    e3.record()
+    barrier()
+    ms_e2e = e2.elapsed_time(e3)
+    clocks = sampler.stop()
+
+    # ---- roofline: only the ternary GEMVs of a step, back to back ------------------------
+    ms_lin, n_lin = model.time_linears(20)
+    alg = linear_alg_bytes(shape, B)
+    peak, peak_src = measured_peak()
+    achieved = alg / (ms_lin * 1e-3) / 1e9
+
+    if dist is not None:
+        t = torch.tensor([ms_dev, ms_e2e], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_dev, ms_e2e = float(t[0]), float(t[1])
+
+    if rank == 0:
+        line = {
+            "metric": "2B-4T decode tok/s", "value": world * B * K / (ms_dev * 1e-3), "unit": "tok/s",
+            "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms_dev / K,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8",
+            "data": "synthetic", "config": workload_config(shape, args), "clocks": clocks,
+            "e2e": {"value": world * B * K / (ms_e2e * 1e-3), "unit": "tok/s", "h2d_bytes_per_step": 4 * B,
+                    "d2h_bytes_per_step": 4 * B, "ms_per_step": ms_e2e / K},
+            "gpu_launches": int(launches_timed),
+            "launches_per_step": model.launches_per_step,
+            "roofline": {"bound": "hbm", "kernel": "gemv_i8_kernel (ternary GEMV, M=%d)" % B,
+                         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": alg / n_lin, "launches_per_pass": n_lin,
+                         "us_per_launch": ms_lin * 1e3 / n_lin,
+                         "pct_of_8TBs_nominal": 100.0 * achieved / 8000.0,
+                         "whole_step_weight_GBs": (shape.ternary_bytes() + 2 * shape.vocab * shape.hidden)
+                         / (ms_dev / K * 1e-3) / 1e9},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            try:
+                v, cores, sample, _, _ = cpu_decode_tok_s(shape, 6, 1, args.cpu_budget_s)
+                line["cpu_baseline"] = {"value": v, "unit": "tok/s", "cores": cores, "kind": "port", "sample": sample}
+            except Exception as ex:  # the baseline is reported, never required for the GPU number
+                line["cpu_baseline"] = {"value": None, "unit": "tok/s", "cores": 0, "kind": "port",
+                                        "sample": "failed: %r" % (ex,)}
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

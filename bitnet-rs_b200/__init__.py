@@ -31,7 +31,19 @@ from .device import (  # noqa: F401
     Weight,
 )
 
+from .model import (  # noqa: F401
+    Model,
+    ModelShape,
+    rope_tables,
+    synth_bytes,
+    synth_embedding,
+    synth_layer,
+    synth_uniform,
+    synth_weight,
+)
+
 __all__ = [
+    "Model", "ModelShape",
     "B200Error", "B200Kernel", "Context", "I2SQk256NoScale", "KernelError", "KernelManager",
     "KernelProvider", "QuantizationType", "Weight", "build", "gemv_qk256", "i2s_matmul_f32",
     "lib", "LAYOUT_QK256", "LAYOUT_BITNET32_F16", "MAP_A", "MAP_B", "MAP_C",

@@ -26,13 +26,13 @@ int fail_cuda(const char* what, cudaError_t e) {
 
 // kernels (gemv.cu, quant.cu, gemm_tcgen05.cu)
 int launch_gemv_i8(const bitnet_b200_ctx*, const bitnet_b200_weight*, const int8_t*, const float*,
-                   int, float*, int32_t*);
+                   int, float*, int32_t*, const float* residual);
 int launch_gemv_f32(const bitnet_b200_ctx*, const bitnet_b200_weight*, const float*, int, float*);
 int launch_gemm_i8(const bitnet_b200_ctx*, const bitnet_b200_weight*, const int8_t*, const float*,
                    int, float*, int32_t*);
 bool gemm_i8_supported(const bitnet_b200_weight*, int M);
 int launch_actquant(const bitnet_b200_ctx*, const float*, const float*, float, int, int, int8_t*,
-                    float*, float*, bool);
+                    float*, float*, int mode);
 int launch_quantize_weights(cudaStream_t, const float*, int, uint8_t*, int, float*, int);
 int launch_matmul_u8(cudaStream_t, const int8_t*, const uint8_t*, float*, int, int, int);
 int launch_i2s_matmul_f32(cudaStream_t, const float*, const uint8_t*, const float*, float*, int,
@@ -362,7 +362,7 @@ int bitnet_b200_actquant_i8(bitnet_b200_ctx* ctx, const float* x, int M, int K, 
                             float* scale) {
     if (!ctx || !x || !q || !scale) return fail("actquant_i8: NULL argument");
     B200_CUDA(cudaSetDevice(ctx->device));
-    return launch_actquant(ctx, x, nullptr, 0.f, M, K, q, scale, nullptr, false);
+    return launch_actquant(ctx, x, nullptr, 0.f, M, K, q, scale, nullptr, 0);
 }
 
 int bitnet_b200_rmsnorm_actquant(bitnet_b200_ctx* ctx, const float* x, const float* gamma,
@@ -371,7 +371,7 @@ int bitnet_b200_rmsnorm_actquant(bitnet_b200_ctx* ctx, const float* x, const flo
     if (!(eps > 0.f) || !isfinite(eps))  // validate_rms_norm_args, cpu/layer_norm.rs
         return fail("rmsnorm_actquant: eps must be positive and finite");
     B200_CUDA(cudaSetDevice(ctx->device));
-    return launch_actquant(ctx, x, gamma, eps, M, K, q, scale, normed, true);
+    return launch_actquant(ctx, x, gamma, eps, M, K, q, scale, normed, 1);
 }
 
 int bitnet_b200_linear_i8(bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, const int8_t* q,
@@ -384,7 +384,7 @@ int bitnet_b200_linear_i8(bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, con
     const bool force_gemv = acc_out && w->layout == BITNET_B200_LAYOUT_BITNET32_F16;
     if (!force_gemv && gemm_i8_supported(w, M))
         return launch_gemm_i8(ctx, w, q, act_scale, M, y, acc_out);
-    return launch_gemv_i8(ctx, w, q, act_scale, M, y, acc_out);
+    return launch_gemv_i8(ctx, w, q, act_scale, M, y, acc_out, nullptr);
 }
 
 int bitnet_b200_linear_f32(bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, const float* x,

@@ -149,5 +149,35 @@ __device__ __forceinline__ float warp_max(float v) {
     return v;
 }
 
+// Sum V per-thread values over the 32 lanes of a warp. On return lane l holds in v[0] the
+// total of value index (l >> (5 - log2 V)).
+template <int V, typename T>
+__device__ __forceinline__ void warp_reduce_transpose(T (&v)[V]) {
+    const int lane = threadIdx.x & 31;
+    int off = 16;
+#pragma unroll
+    for (int cnt = V / 2; cnt >= 1; cnt >>= 1) {
+        const bool hi = (lane & off) != 0;
+#pragma unroll
+        for (int i = 0; i < cnt; ++i) {
+            T send = hi ? v[i] : v[i + cnt];
+            T keep = hi ? v[i + cnt] : v[i];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+        }
+        off >>= 1;
+    }
+#pragma unroll
+    for (; off >= 1; off >>= 1) v[0] += __shfl_xor_sync(0xffffffffu, v[0], off);
+}
+
+template <int V>
+struct Log2 {
+    static constexpr int value = 1 + Log2<V / 2>::value;
+};
+template <>
+struct Log2<1> {
+    static constexpr int value = 0;
+};
+
 }  // namespace b200
 #endif

@@ -1,2 +1,610 @@
-// decode.cu -- glue kernels of the 2B-4T-shaped decode step (filled in with the model harness).
+// decode.cu -- a BitNet-b1.58-2B-4T-shaped decoder step on device, as ONE CUDA graph.
+//
+// The ternary linears and the act-quant that feeds them are the hot path (gemv.cu, quant.cu);
+// this file adds the glue the reference runs through candle on the host
+// (crates/bitnet-transformer/src/lib.rs): embedding gather (:1390-1426), split-half RoPE
+// (:134-184), KV-cache append (:1171-1202), GQA decode attention (:374-540), SwiGLU glue
+// (:756-789, fused into the act-quant), tied-embedding logits (:1599-1630) and greedy argmax.
+// Norms are true RMSNorm (cpu::rms_norm), as SURVEY.md §3.1 prescribes for this build.
+//
+// The whole step (about 10 launches per layer) is captured once into a CUDA graph; the
+// position lives in device memory so the same graph replays for every token, and the greedy
+// token is fed back on device so a decode loop needs no host round trip.
+#include <memory>
+#include <vector>
+
 #include "common.cuh"
+
+namespace b200 {
+
+int launch_gemv_i8(const bitnet_b200_ctx*, const bitnet_b200_weight*, const int8_t*, const float*,
+                   int, float*, int32_t*, const float* residual);
+int launch_actquant(const bitnet_b200_ctx*, const float*, const float*, float, int, int, int8_t*,
+                    float*, float*, int mode);
+
+// ---------------------------------------------------------------------------------------
+__global__ void embed_kernel(const __half* __restrict__ emb, const int* __restrict__ tokens,
+                             float* __restrict__ x, int H) {
+    const int b = blockIdx.x;
+    const __half* row = emb + (size_t)tokens[b] * H;
+    for (int i = threadIdx.x; i < H; i += blockDim.x) x[(size_t)b * H + i] = __half2float(row[i]);
+}
+
+// RoPE (split-half pairs (i, i + D/2)) on q in place and on k into the cache; v into the cache.
+// grid (NH + 2*NKV, B), block D/2. qkv row = [q (NH*D) | k (NKV*D) | v (NKV*D)].
+__global__ void rope_kv_kernel(float* __restrict__ qkv, const float* __restrict__ cos_t,
+                               const float* __restrict__ sin_t, float* __restrict__ kc,
+                               float* __restrict__ vc, const int* __restrict__ pos_p, int NH,
+                               int NKV, int D, int max_ctx) {
+    const int head = blockIdx.x, b = blockIdx.y, i = threadIdx.x, half = D / 2;
+    const int pos = *pos_p;
+    float* row = qkv + (size_t)b * (NH + 2 * NKV) * D;
+    if (head < NH + NKV) {
+        float* v = row + (size_t)head * D;
+        const float c = cos_t[(size_t)pos * half + i], s = sin_t[(size_t)pos * half + i];
+        const float a = v[i], bb = v[i + half];
+        const float r0 = a * c - bb * s, r1 = a * s + bb * c;
+        if (head < NH) {
+            v[i] = r0;
+            v[i + half] = r1;
+        } else {
+            float* dst = kc + (((size_t)b * NKV + (head - NH)) * max_ctx + pos) * D;
+            dst[i] = r0;
+            dst[i + half] = r1;
+        }
+    } else {
+        const int g = head - NH - NKV;
+        const float* v = row + (size_t)(NH + NKV + g) * D;
+        float* dst = vc + (((size_t)b * NKV + g) * max_ctx + pos) * D;
+        dst[i] = v[i];
+        dst[i + half] = v[i + half];
+    }
+}
+
+// Decode attention for one (head, sequence): scores over 0..pos, softmax, weighted V sum.
+// grid (NH, B), block D threads (D = 128 -> 4 warps), dynamic smem = max_ctx floats.
+__global__ void attn_decode_kernel(const float* __restrict__ qkv, const float* __restrict__ kc,
+                                   const float* __restrict__ vc, float* __restrict__ att,
+                                   const int* __restrict__ pos_p, int NH, int NKV, int D,
+                                   int max_ctx) {
+    extern __shared__ float sc[];
+    __shared__ float red[32];
+    const int head = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
+    const int lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
+    const int pos = *pos_p, g = head / (NH / NKV);
+    const float* q = qkv + (size_t)b * (NH + 2 * NKV) * D + (size_t)head * D;
+    const float* kb = kc + ((size_t)b * NKV + g) * max_ctx * D;
+    const float* vb = vc + ((size_t)b * NKV + g) * max_ctx * D;
+    const float scale = 1.0f / sqrtf((float)D);
+    // each lane holds D/32 query elements (strided so that K loads coalesce)
+    float qr[8];
+    const int per = D / 32;
+    for (int j = 0; j < per; ++j) qr[j] = q[lane + 32 * j];
+    float mx = -INFINITY;
+    for (int p = warp; p <= pos; p += nwarps) {
+        const float* kp = kb + (size_t)p * D;
+        float d = 0.f;
+        for (int j = 0; j < per; ++j) d = fmaf(qr[j], kp[lane + 32 * j], d);
+        d = warp_sum(d) * scale;
+        if (lane == 0) sc[p] = d;
+        mx = fmaxf(mx, d);
+    }
+    if (lane == 0) red[warp] = mx;
+    __syncthreads();
+    mx = red[0];
+    for (int w = 1; w < nwarps; ++w) mx = fmaxf(mx, red[w]);
+    __syncthreads();
+    float sum = 0.f;
+    for (int p = tid; p <= pos; p += blockDim.x) {
+        const float e = expf(sc[p] - mx);
+        sc[p] = e;
+        sum += e;
+    }
+    sum = warp_sum(sum);
+    if (lane == 0) red[warp] = sum;
+    __syncthreads();
+    sum = 0.f;
+    for (int w = 0; w < nwarps; ++w) sum += red[w];
+    const float inv = 1.0f / sum;
+    for (int d = tid; d < D; d += blockDim.x) {
+        float a = 0.f;
+        for (int p = 0; p <= pos; ++p) a = fmaf(sc[p] * inv, vb[(size_t)p * D + d], a);
+        att[((size_t)b * NH + head) * D + d] = a;
+    }
+}
+
+// Tied-embedding logits: f16 table [V, H] x f32 hidden [B, H] -> f32 [B, V].
+// Thread t owns the 8 consecutive k = 8t..8t+7 of every row (one 16-byte load per row),
+// R rows in flight; same transposing reduction as the ternary GEMV.
+template <int MT, int R>
+__global__ void __launch_bounds__(1024) logits_f16_kernel(const __half* __restrict__ emb,
+                                                          const float* __restrict__ xn,
+                                                          float* __restrict__ logits, int V, int H,
+                                                          int M, int rows_per_cta) {
+    constexpr int NV = R * MT;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float* red = reinterpret_cast<float*>(smem_raw);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
+    const int nvec = H / 8;
+    const bool active = tid < nvec;
+    float xv[MT][8];
+#pragma unroll
+    for (int m = 0; m < MT; ++m)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) xv[m][j] = (active && m < M) ? xn[(size_t)m * H + tid * 8 + j] : 0.f;
+    const int row_begin = blockIdx.x * rows_per_cta;
+    const int row_end = min(V, row_begin + rows_per_cta);
+    int buf = 0;
+    for (int r0 = row_begin; r0 < row_end; r0 += R, buf ^= 1) {
+        uint4 w[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int row = r0 + r;
+            w[r] = (active && row < row_end) ? ldg_nc_u128(emb + (size_t)row * H + (size_t)tid * 8)
+                                             : make_uint4(0, 0, 0, 0);
+        }
+        float v[NV];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const __half2* hp = reinterpret_cast<const __half2*>(&w[r]);
+            float f[8];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float2 t = __half22float2(hp[j]);
+                f[2 * j] = t.x;
+                f[2 * j + 1] = t.y;
+            }
+#pragma unroll
+            for (int m = 0; m < MT; ++m) {
+                float a = 0.f;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) a = fmaf(f[j], xv[m][j], a);
+                v[r * MT + m] = a;
+            }
+        }
+        warp_reduce_transpose<NV, float>(v);
+        constexpr int SHIFT = 5 - Log2<NV>::value;
+        if ((lane & ((1 << SHIFT) - 1)) == 0) red[(buf * nwarps + warp) * NV + (lane >> SHIFT)] = v[0];
+        __syncthreads();
+        if (tid < NV) {
+            float tot = 0.f;
+            for (int wv = 0; wv < nwarps; ++wv) tot += red[(buf * nwarps + wv) * NV + tid];
+            const int r = tid / MT, m = tid % MT, row = r0 + r;
+            if (row < row_end && m < M) logits[(size_t)m * V + row] = tot;
+        }
+    }
+}
+
+// greedy argmax per sequence (lowest index on ties); feeds the token back and advances pos
+__global__ void __launch_bounds__(1024) argmax_kernel(const float* __restrict__ logits, int V,
+                                                      int* __restrict__ next, int* __restrict__ tokens,
+                                                      int* __restrict__ pos_p, int advance) {
+    __shared__ float bv[32];
+    __shared__ int bi[32];
+    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const float* lg = logits + (size_t)b * V;
+    float best = -INFINITY;
+    int idx = 0x7fffffff;
+    for (int i = tid; i < V; i += blockDim.x) {
+        const float v = lg[i];
+        if (v > best || (v == best && i < idx)) {
+            best = v;
+            idx = i;
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+        if (ov > best || (ov == best && oi < idx)) {
+            best = ov;
+            idx = oi;
+        }
+    }
+    if (lane == 0) {
+        bv[warp] = best;
+        bi[warp] = idx;
+    }
+    __syncthreads();
+    if (tid == 0) {
+        for (int w = 1; w < (int)(blockDim.x >> 5); ++w)
+            if (bv[w] > best || (bv[w] == best && bi[w] < idx)) {
+                best = bv[w];
+                idx = bi[w];
+            }
+        if (idx == 0x7fffffff) idx = 0;
+        next[b] = idx;
+        tokens[b] = idx;
+        if (advance && b == 0) *pos_p = *pos_p + 1;
+    }
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+// ---------------------------------------------------------------------------------------
+// the model object
+// ---------------------------------------------------------------------------------------
+struct LayerW {
+    bitnet_b200_weight *wqkv = nullptr, *wo = nullptr, *wgateup = nullptr, *wdown = nullptr;
+    float *attn_norm = nullptr, *ffn_norm = nullptr;
+};
+
+struct bitnet_b200_model {
+    bitnet_b200_ctx* ctx = nullptr;
+    bitnet_b200_model_config cfg{};
+    std::vector<LayerW> layers;
+    __half* emb = nullptr;
+    float *final_norm = nullptr, *rope_cos = nullptr, *rope_sin = nullptr;
+    float *kc = nullptr, *vc = nullptr;  // [L][B][NKV][max_ctx][D]
+    int *pos = nullptr, *tokens = nullptr, *next = nullptr;
+    float *x = nullptr, *qkv = nullptr, *att = nullptr, *gu = nullptr, *xn = nullptr, *logits = nullptr;
+    int8_t* q8 = nullptr;
+    float* s8 = nullptr;
+    int* next_host = nullptr;  // pinned
+    int* tok_host = nullptr;   // pinned
+    cudaGraphExec_t graph = nullptr;
+    uint64_t launches_per_step = 0;
+    bool have_emb = false, have_rope = false;
+    int layers_set = 0;
+};
+
+static int dmalloc(void** p, size_t n) {
+    B200_CUDA(cudaMalloc(p, n ? n : 1));
+    return 0;
+}
+
+template <typename T>
+static int upload(T** dst, const T* src, size_t n, cudaStream_t st) {
+    if (!*dst && dmalloc(reinterpret_cast<void**>(dst), n * sizeof(T))) return -1;
+    B200_CUDA(cudaMemcpyAsync(*dst, src, n * sizeof(T), cudaMemcpyHostToDevice, st));
+    B200_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+static size_t row_bytes(int layout, size_t cols) {
+    return layout == BITNET_B200_LAYOUT_QK256 ? div_ceil(cols, 256) * 64 : cols / 32 * 10;
+}
+
+static int enqueue_step(bitnet_b200_model* m) {
+    const auto& c = m->cfg;
+    bitnet_b200_ctx* ctx = m->ctx;
+    cudaStream_t st = ctx->stream;
+    const int B = c.batch, H = c.hidden, F = c.ffn, D = c.head_dim, NH = c.n_heads, NKV = c.n_kv_heads;
+    const int QD = NH * D;
+    const uint64_t l0 = g_launches.load();
+    embed_kernel<<<B, 256, 0, st>>>(m->emb, m->tokens, m->x, H);
+    B200_LAUNCH_CHECK("embed_kernel");
+    for (int l = 0; l < c.n_layers; ++l) {
+        const LayerW& L = m->layers[(size_t)l];
+        const size_t kvoff = (size_t)l * B * NKV * c.max_ctx * D;
+        if (launch_actquant(ctx, m->x, L.attn_norm, c.rms_eps, B, H, m->q8, m->s8, nullptr, 1)) return -1;
+        if (launch_gemv_i8(ctx, L.wqkv, m->q8, m->s8, B, m->qkv, nullptr, nullptr)) return -1;
+        rope_kv_kernel<<<dim3(NH + 2 * NKV, B), D / 2, 0, st>>>(m->qkv, m->rope_cos, m->rope_sin,
+                                                                m->kc + kvoff, m->vc + kvoff, m->pos,
+                                                                NH, NKV, D, c.max_ctx);
+        B200_LAUNCH_CHECK("rope_kv_kernel");
+        attn_decode_kernel<<<dim3(NH, B), D, (size_t)c.max_ctx * 4, st>>>(
+            m->qkv, m->kc + kvoff, m->vc + kvoff, m->att, m->pos, NH, NKV, D, c.max_ctx);
+        B200_LAUNCH_CHECK("attn_decode_kernel");
+        if (launch_actquant(ctx, m->att, nullptr, 0.f, B, QD, m->q8, m->s8, nullptr, 0)) return -1;
+        if (launch_gemv_i8(ctx, L.wo, m->q8, m->s8, B, m->x, nullptr, m->x)) return -1;
+        if (launch_actquant(ctx, m->x, L.ffn_norm, c.rms_eps, B, H, m->q8, m->s8, nullptr, 1)) return -1;
+        if (launch_gemv_i8(ctx, L.wgateup, m->q8, m->s8, B, m->gu, nullptr, nullptr)) return -1;
+        if (launch_actquant(ctx, m->gu, nullptr, 0.f, B, F, m->q8, m->s8, nullptr, 2)) return -1;
+        if (launch_gemv_i8(ctx, L.wdown, m->q8, m->s8, B, m->x, nullptr, m->x)) return -1;
+    }
+    if (launch_actquant(ctx, m->x, m->final_norm, c.rms_eps, B, H, m->q8, m->s8, m->xn, 1)) return -1;
+    {
+        const int threads = (int)div_ceil((size_t)H / 8, 32) * 32;
+        const int rpc = 64;
+        const int grid = (int)div_ceil((size_t)c.vocab, rpc);
+        for (int m0 = 0; m0 < B; m0 += 4) {
+            const int mc = B - m0 < 4 ? B - m0 : 4;
+            const float* xin = m->xn + (size_t)m0 * H;
+            float* lo = m->logits + (size_t)m0 * c.vocab;
+            if (mc == 1) {
+                logits_f16_kernel<1, 8><<<grid, threads, 2 * (threads / 32) * 8 * 4, st>>>(m->emb, xin, lo, c.vocab, H, mc, rpc);
+            } else if (mc == 2) {
+                logits_f16_kernel<2, 8><<<grid, threads, 2 * (threads / 32) * 16 * 4, st>>>(m->emb, xin, lo, c.vocab, H, mc, rpc);
+            } else {
+                logits_f16_kernel<4, 4><<<grid, threads, 2 * (threads / 32) * 16 * 4, st>>>(m->emb, xin, lo, c.vocab, H, mc, rpc);
+            }
+            B200_LAUNCH_CHECK("logits_f16_kernel");
+        }
+    }
+    argmax_kernel<<<B, 1024, 0, st>>>(m->logits, c.vocab, m->next, m->tokens, m->pos, 1);
+    B200_LAUNCH_CHECK("argmax_kernel");
+    m->launches_per_step = g_launches.load() - l0;
+    return 0;
+}
+
+static int ensure_graph(bitnet_b200_model* m) {
+    if (m->graph) return 0;
+    if (!m->have_emb || !m->have_rope || m->layers_set != m->cfg.n_layers)
+        return fail("model: weights incomplete (set every layer, the embedding and the RoPE tables first)");
+    const int smem = m->cfg.max_ctx * 4;
+    if (smem > 48 * 1024)
+        B200_CUDA(cudaFuncSetAttribute(attn_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    cudaStream_t st = m->ctx->stream;
+    cudaGraph_t g = nullptr;
+    B200_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+    const int rc = enqueue_step(m);
+    cudaError_t e = cudaStreamEndCapture(st, &g);
+    if (rc) {
+        if (g) cudaGraphDestroy(g);
+        return -1;
+    }
+    if (e != cudaSuccess) return fail_cuda("cudaStreamEndCapture", e);
+    e = cudaGraphInstantiate(&m->graph, g, 0);
+    cudaGraphDestroy(g);
+    if (e != cudaSuccess) return fail_cuda("cudaGraphInstantiate", e);
+    return 0;
+}
+
+extern "C" {
+
+int bitnet_b200_model_create(bitnet_b200_ctx* ctx, const bitnet_b200_model_config* cfg,
+                             bitnet_b200_model** out) {
+    try {
+        if (!ctx || !cfg || !out) return fail("model_create: NULL argument");
+        *out = nullptr;
+        const auto& c = *cfg;
+        if (c.hidden <= 0 || c.ffn <= 0 || c.n_layers <= 0 || c.n_heads <= 0 || c.n_kv_heads <= 0 ||
+            c.head_dim <= 0 || c.vocab <= 0 || c.max_ctx <= 0 || c.batch <= 0)
+            return fail("model_create: all dimensions must be > 0");
+        if (c.n_heads % c.n_kv_heads) return fail("model_create: n_heads must be a multiple of n_kv_heads");
+        if (c.head_dim % 64 || c.head_dim > 256) return fail("model_create: head_dim must be 64, 128, 192 or 256");
+        if (c.hidden % 32 || c.ffn % 32 || c.hidden % 8) return fail("model_create: hidden and ffn must be multiples of 32");
+        if ((size_t)c.max_ctx * 4 > 200 * 1024) return fail("model_create: max_ctx too large for the decode attention kernel");
+        B200_CUDA(cudaSetDevice(ctx->device));
+        std::unique_ptr<bitnet_b200_model, void (*)(bitnet_b200_model*)> m(new bitnet_b200_model(),
+                                                                          bitnet_b200_model_destroy);
+        m->ctx = ctx;
+        m->cfg = c;
+        m->layers.resize((size_t)c.n_layers);
+        const size_t B = (size_t)c.batch, H = (size_t)c.hidden, F = (size_t)c.ffn, D = (size_t)c.head_dim;
+        const size_t NH = (size_t)c.n_heads, NKV = (size_t)c.n_kv_heads;
+        const size_t kv = (size_t)c.n_layers * B * NKV * c.max_ctx * D;
+        if (dmalloc((void**)&m->kc, kv * 4) || dmalloc((void**)&m->vc, kv * 4)) return -1;
+        if (dmalloc((void**)&m->pos, 4) || dmalloc((void**)&m->tokens, B * 4) || dmalloc((void**)&m->next, B * 4)) return -1;
+        if (dmalloc((void**)&m->x, B * H * 4) || dmalloc((void**)&m->qkv, B * (NH + 2 * NKV) * D * 4) ||
+            dmalloc((void**)&m->att, B * NH * D * 4) || dmalloc((void**)&m->gu, B * 2 * F * 4) ||
+            dmalloc((void**)&m->xn, B * H * 4) || dmalloc((void**)&m->logits, B * (size_t)c.vocab * 4))
+            return -1;
+        const size_t qmax = std::max(std::max(H, F), NH * D);
+        if (dmalloc((void**)&m->q8, B * qmax) || dmalloc((void**)&m->s8, B * 4)) return -1;
+        B200_CUDA(cudaMallocHost((void**)&m->next_host, B * 4));
+        B200_CUDA(cudaMallocHost((void**)&m->tok_host, B * 4));
+        B200_CUDA(cudaMemsetAsync(m->kc, 0, kv * 4, ctx->stream));
+        B200_CUDA(cudaMemsetAsync(m->vc, 0, kv * 4, ctx->stream));
+        B200_CUDA(cudaMemsetAsync(m->pos, 0, 4, ctx->stream));
+        B200_CUDA(cudaMemsetAsync(m->tokens, 0, B * 4, ctx->stream));
+        B200_CUDA(cudaStreamSynchronize(ctx->stream));
+        *out = m.release();
+        return 0;
+    } catch (const std::exception& e) {
+        return fail(e.what());
+    }
+}
+
+void bitnet_b200_model_destroy(bitnet_b200_model* m) {
+    if (!m) return;
+    if (m->graph) cudaGraphExecDestroy(m->graph);
+    for (auto& L : m->layers) {
+        bitnet_b200_weight_destroy(L.wqkv);
+        bitnet_b200_weight_destroy(L.wo);
+        bitnet_b200_weight_destroy(L.wgateup);
+        bitnet_b200_weight_destroy(L.wdown);
+        cudaFree(L.attn_norm);
+        cudaFree(L.ffn_norm);
+    }
+    void* ptrs[] = {m->emb, m->final_norm, m->rope_cos, m->rope_sin, m->kc, m->vc, m->pos, m->tokens,
+                    m->next, m->x, m->qkv, m->att, m->gu, m->xn, m->logits, m->q8, m->s8};
+    for (void* p : ptrs)
+        if (p) cudaFree(p);
+    if (m->next_host) cudaFreeHost(m->next_host);
+    if (m->tok_host) cudaFreeHost(m->tok_host);
+    delete m;
+}
+
+// One layer's seven projections, host bytes in the reference layout ([out, in] rows):
+// wq [NH*D, H], wk/wv [NKV*D, H], wo [H, NH*D], wgate/wup [F, H], wdown [H, F].
+// q|k|v are concatenated by rows, gate/up interleaved by rows (row 2i = gate i, 2i+1 = up i):
+// both layouts keep a row's bytes contiguous, so fusing is a byte shuffle at upload.
+int bitnet_b200_model_set_layer(bitnet_b200_model* m, int layer, const void* wq, const void* wk,
+                                const void* wv, const void* wo, const void* wgate, const void* wup,
+                                const void* wdown, const float* attn_norm, const float* ffn_norm) {
+    try {
+        if (!m || !wq || !wk || !wv || !wo || !wgate || !wup || !wdown || !attn_norm || !ffn_norm)
+            return fail("model_set_layer: NULL argument");
+        const auto& c = m->cfg;
+        if (layer < 0 || layer >= c.n_layers) return fail("model_set_layer: layer out of range");
+        if (m->graph) return fail("model_set_layer: the step graph is already built");
+        B200_CUDA(cudaSetDevice(m->ctx->device));
+        LayerW& L = m->layers[(size_t)layer];
+        const bool fresh = L.wqkv == nullptr;
+        const size_t H = (size_t)c.hidden, F = (size_t)c.ffn, QD = (size_t)c.n_heads * c.head_dim,
+                     KD = (size_t)c.n_kv_heads * c.head_dim;
+        const size_t rbH = row_bytes(c.layout, H), rbQ = row_bytes(c.layout, QD), rbF = row_bytes(c.layout, F);
+        std::vector<uint8_t> qkv((QD + 2 * KD) * rbH), gu(2 * F * rbH);
+        memcpy(qkv.data(), wq, QD * rbH);
+        memcpy(qkv.data() + QD * rbH, wk, KD * rbH);
+        memcpy(qkv.data() + (QD + KD) * rbH, wv, KD * rbH);
+        for (size_t i = 0; i < F; ++i) {
+            memcpy(gu.data() + (2 * i) * rbH, (const uint8_t*)wgate + i * rbH, rbH);
+            memcpy(gu.data() + (2 * i + 1) * rbH, (const uint8_t*)wup + i * rbH, rbH);
+        }
+        bitnet_b200_weight_destroy(L.wqkv);
+        bitnet_b200_weight_destroy(L.wo);
+        bitnet_b200_weight_destroy(L.wgateup);
+        bitnet_b200_weight_destroy(L.wdown);
+        L.wqkv = L.wo = L.wgateup = L.wdown = nullptr;
+        if (bitnet_b200_weight_create(m->ctx, qkv.data(), qkv.size(), c.layout, QD + 2 * KD, H, nullptr, 0, &L.wqkv)) return -1;
+        if (bitnet_b200_weight_create(m->ctx, wo, H * rbQ, c.layout, H, QD, nullptr, 0, &L.wo)) return -1;
+        if (bitnet_b200_weight_create(m->ctx, gu.data(), gu.size(), c.layout, 2 * F, H, nullptr, 0, &L.wgateup)) return -1;
+        if (bitnet_b200_weight_create(m->ctx, wdown, H * rbF, c.layout, H, F, nullptr, 0, &L.wdown)) return -1;
+        if (upload(&L.attn_norm, attn_norm, H, m->ctx->stream)) return -1;
+        if (upload(&L.ffn_norm, ffn_norm, H, m->ctx->stream)) return -1;
+        if (fresh) m->layers_set++;
+        return 0;
+    } catch (const std::exception& e) {
+        return fail(e.what());
+    }
+}
+
+int bitnet_b200_model_set_embedding(bitnet_b200_model* m, const uint16_t* emb_f16,
+                                    const float* final_norm) {
+    if (!m || !emb_f16 || !final_norm) return fail("model_set_embedding: NULL argument");
+    B200_CUDA(cudaSetDevice(m->ctx->device));
+    if (upload(reinterpret_cast<uint16_t**>(&m->emb), emb_f16, (size_t)m->cfg.vocab * m->cfg.hidden, m->ctx->stream)) return -1;
+    if (upload(&m->final_norm, final_norm, (size_t)m->cfg.hidden, m->ctx->stream)) return -1;
+    m->have_emb = true;
+    return 0;
+}
+
+int bitnet_b200_model_set_rope(bitnet_b200_model* m, const float* cos_t, const float* sin_t) {
+    if (!m || !cos_t || !sin_t) return fail("model_set_rope: NULL argument");
+    B200_CUDA(cudaSetDevice(m->ctx->device));
+    const size_t n = (size_t)m->cfg.max_ctx * (m->cfg.head_dim / 2);
+    if (upload(&m->rope_cos, cos_t, n, m->ctx->stream)) return -1;
+    if (upload(&m->rope_sin, sin_t, n, m->ctx->stream)) return -1;
+    m->have_rope = true;
+    return 0;
+}
+
+int bitnet_b200_model_reset(bitnet_b200_model* m) {
+    if (!m) return fail("model_reset: NULL argument");
+    B200_CUDA(cudaMemsetAsync(m->pos, 0, 4, m->ctx->stream));
+    return 0;
+}
+
+// One decode step through host buffers: H2D of the batch's token ids (pinned staging), the
+// step graph, D2H of the greedy tokens (and optionally the logits); synchronous.
+int bitnet_b200_model_decode(bitnet_b200_model* m, const int32_t* tokens, int32_t* next_tokens,
+                             float* logits_out) {
+    try {
+        if (!m || !tokens || !next_tokens) return fail("model_decode: NULL argument");
+        B200_CUDA(cudaSetDevice(m->ctx->device));
+        if (ensure_graph(m)) return -1;
+        cudaStream_t st = m->ctx->stream;
+        const size_t B = (size_t)m->cfg.batch;
+        for (size_t b = 0; b < B; ++b) {
+            if (tokens[b] < 0 || tokens[b] >= m->cfg.vocab) return fail("model_decode: token id out of range");
+            m->tok_host[b] = tokens[b];
+        }
+        B200_CUDA(cudaMemcpyAsync(m->tokens, m->tok_host, B * 4, cudaMemcpyHostToDevice, st));
+        B200_CUDA(cudaGraphLaunch(m->graph, st));
+        count_launch(m->launches_per_step);
+        B200_CUDA(cudaMemcpyAsync(m->next_host, m->next, B * 4, cudaMemcpyDeviceToHost, st));
+        if (logits_out)
+            B200_CUDA(cudaMemcpyAsync(logits_out, m->logits, B * (size_t)m->cfg.vocab * 4, cudaMemcpyDeviceToHost, st));
+        B200_CUDA(cudaStreamSynchronize(st));
+        for (size_t b = 0; b < B; ++b) next_tokens[b] = m->next_host[b];
+        return 0;
+    } catch (const std::exception& e) {
+        return fail(e.what());
+    }
+}
+
+// n greedy steps entirely on device (token fed back by the argmax kernel); asynchronous.
+// The current device-side tokens are used as the first input (set them with one decode()
+// or model_set_tokens()).
+int bitnet_b200_model_decode_device(bitnet_b200_model* m, int n_steps) {
+    if (!m || n_steps < 0) return fail("model_decode_device: bad argument");
+    B200_CUDA(cudaSetDevice(m->ctx->device));
+    if (ensure_graph(m)) return -1;
+    for (int i = 0; i < n_steps; ++i) {
+        B200_CUDA(cudaGraphLaunch(m->graph, m->ctx->stream));
+        count_launch(m->launches_per_step);
+    }
+    return 0;
+}
+
+int bitnet_b200_model_set_tokens(bitnet_b200_model* m, const int32_t* tokens) {
+    if (!m || !tokens) return fail("model_set_tokens: NULL argument");
+    const size_t B = (size_t)m->cfg.batch;
+    for (size_t b = 0; b < B; ++b) m->tok_host[b] = tokens[b];
+    B200_CUDA(cudaMemcpyAsync(m->tokens, m->tok_host, B * 4, cudaMemcpyHostToDevice, m->ctx->stream));
+    B200_CUDA(cudaStreamSynchronize(m->ctx->stream));
+    return 0;
+}
+
+int bitnet_b200_model_get_tokens(bitnet_b200_model* m, int32_t* next_tokens) {
+    if (!m || !next_tokens) return fail("model_get_tokens: NULL argument");
+    const size_t B = (size_t)m->cfg.batch;
+    B200_CUDA(cudaMemcpyAsync(m->next_host, m->next, B * 4, cudaMemcpyDeviceToHost, m->ctx->stream));
+    B200_CUDA(cudaStreamSynchronize(m->ctx->stream));
+    for (size_t b = 0; b < B; ++b) next_tokens[b] = m->next_host[b];
+    return 0;
+}
+
+// Roofline leg of bench.py: ONLY the ternary linears of one decode step (4 fused GEMVs per
+// layer, this model's real weights -- together larger than L2), captured as one graph and
+// replayed `reps` times between two events on the context's stream. Reports the mean time
+// of one pass and how many GEMV launches a pass holds.
+int bitnet_b200_model_time_linears(bitnet_b200_model* m, int reps, float* ms_per_pass,
+                                   int* launches_per_pass) {
+    try {
+        if (!m || reps <= 0 || !ms_per_pass || !launches_per_pass) return fail("model_time_linears: bad argument");
+        if (m->layers_set != m->cfg.n_layers) return fail("model_time_linears: weights incomplete");
+        B200_CUDA(cudaSetDevice(m->ctx->device));
+        const auto& c = m->cfg;
+        cudaStream_t st = m->ctx->stream;
+        const int B = c.batch;
+        cudaGraph_t g = nullptr;
+        cudaGraphExec_t ge = nullptr;
+        const uint64_t l0 = g_launches.load();
+        B200_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+        int rc = 0;
+        for (int l = 0; l < c.n_layers && !rc; ++l) {
+            const LayerW& L = m->layers[(size_t)l];
+            rc = launch_gemv_i8(m->ctx, L.wqkv, m->q8, m->s8, B, m->qkv, nullptr, nullptr) ||
+                 launch_gemv_i8(m->ctx, L.wo, m->q8, m->s8, B, m->xn, nullptr, nullptr) ||
+                 launch_gemv_i8(m->ctx, L.wgateup, m->q8, m->s8, B, m->gu, nullptr, nullptr) ||
+                 launch_gemv_i8(m->ctx, L.wdown, m->q8, m->s8, B, m->xn, nullptr, nullptr);
+        }
+        cudaError_t e = cudaStreamEndCapture(st, &g);
+        const int per_pass = (int)(g_launches.load() - l0);
+        if (rc) {
+            if (g) cudaGraphDestroy(g);
+            return -1;
+        }
+        if (e != cudaSuccess) return fail_cuda("cudaStreamEndCapture", e);
+        e = cudaGraphInstantiate(&ge, g, 0);
+        cudaGraphDestroy(g);
+        if (e != cudaSuccess) return fail_cuda("cudaGraphInstantiate", e);
+        cudaEvent_t e0, e1;
+        cudaEventCreate(&e0);
+        cudaEventCreate(&e1);
+        cudaGraphLaunch(ge, st);  // warm-up pass
+        cudaEventRecord(e0, st);
+        for (int i = 0; i < reps; ++i) cudaGraphLaunch(ge, st);
+        cudaEventRecord(e1, st);
+        e = cudaStreamSynchronize(st);
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
+        cudaGraphExecDestroy(ge);
+        if (e != cudaSuccess) return fail_cuda("model_time_linears", e);
+        count_launch((uint64_t)per_pass * (uint64_t)reps);
+        *ms_per_pass = ms / (float)reps;
+        *launches_per_pass = per_pass;
+        return 0;
+    } catch (const std::exception& e) {
+        return fail(e.what());
+    }
+}
+
+uint64_t bitnet_b200_model_launches_per_step(const bitnet_b200_model* m) { return m ? m->launches_per_step : 0; }
+uint64_t bitnet_b200_model_weight_bytes(const bitnet_b200_model* m) {
+    if (!m) return 0;
+    uint64_t n = 0;
+    for (const auto& L : m->layers)
+        for (const bitnet_b200_weight* w : {L.wqkv, L.wo, L.wgateup, L.wdown})
+            if (w) n += w->ref_nbytes;
+    return n;
+}
+
+}  // extern "C"

@@ -23,6 +23,7 @@ struct GemvParams {
     const int8_t* q;         // [M, K] int8 activations
     const float* act_scale;  // [M]
     float* y;                // [M, N]
+    const float* residual;   // optional [M, N]: y = residual + act_scale * acc (may alias y)
     int32_t* acc_out;        // optional: QK256 [M,N]; BitNet32 [M,N,nblk32]
     uint32_t lut;            // 4 x int8
     int N, K, M;
@@ -31,36 +32,6 @@ struct GemvParams {
     int nblk32;
     int rows_per_cta;
     int clamp_scale;         // BITNET_B200_SCALE_ABS_CLAMP -> 1
-};
-
-// Sum V per-thread values over the 32 lanes of a warp. On return lane l holds in v[0] the
-// total of value index (l >> (5 - log2 V)).
-template <int V, typename T>
-__device__ __forceinline__ void warp_reduce_transpose(T (&v)[V]) {
-    const int lane = threadIdx.x & 31;
-    int off = 16;
-#pragma unroll
-    for (int cnt = V / 2; cnt >= 1; cnt >>= 1) {
-        const bool hi = (lane & off) != 0;
-#pragma unroll
-        for (int i = 0; i < cnt; ++i) {
-            T send = hi ? v[i] : v[i + cnt];
-            T keep = hi ? v[i + cnt] : v[i];
-            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
-        }
-        off >>= 1;
-    }
-#pragma unroll
-    for (; off >= 1; off >>= 1) v[0] += __shfl_xor_sync(0xffffffffu, v[0], off);
-}
-
-template <int V>
-struct Log2 {
-    static constexpr int value = 1 + Log2<V / 2>::value;
-};
-template <>
-struct Log2<1> {
-    static constexpr int value = 0;
 };
 
 __device__ __forceinline__ uint4 load_act16(const int8_t* q, int K, int m, int p) {
@@ -156,7 +127,9 @@ __global__ void __launch_bounds__(1024) gemv_i8_kernel(const GemvParams p) {
             const int r = tid / MT, m = tid % MT;
             const int row = r0 + r;
             if (row < row_end && m < p.M) {
-                p.y[(size_t)m * p.N + row] = p.act_scale[m] * (float)tot;
+                const float val = p.act_scale[m] * (float)tot;
+                const size_t oi = (size_t)m * p.N + row;
+                p.y[oi] = p.residual ? p.residual[oi] + val : val;
                 if (WACC && !SCALED) p.acc_out[(size_t)m * p.N + row] = (int32_t)tot;
             }
         }
@@ -239,7 +212,7 @@ int gemv_rows_per_cta_override = 0;  // test/bench knob (0 = heuristic)
 
 // y[m, n] for m in [0, M): loops token chunks of at most 8.
 int launch_gemv_i8(const bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, const int8_t* q,
-                   const float* act_scale, int M, float* y, int32_t* acc_out) {
+                   const float* act_scale, int M, float* y, int32_t* acc_out, const float* residual) {
     const int nwords = (int)(w->code_stride / 4);
     if (nwords > 1024)
         return fail("linear_i8 GEMV: cols > 16384 not supported by the decode kernel");
@@ -255,6 +228,7 @@ int launch_gemv_i8(const bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, cons
         p.q = q + (size_t)m0 * w->cols;
         p.act_scale = act_scale + m0;
         p.y = y + (size_t)m0 * w->rows;
+        p.residual = residual ? residual + (size_t)m0 * w->rows : nullptr;
         p.acc_out = acc_out ? acc_out + (size_t)m0 * w->rows * (scaled ? w->nblk32 : 1) : nullptr;
         p.lut = w->lut_word;
         p.N = (int)w->rows;

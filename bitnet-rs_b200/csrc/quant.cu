@@ -41,23 +41,132 @@ __device__ __forceinline__ int quant1(float v, float inv) {
 }
 
 // ---------------------------------------------------------------------------------------
-// per-token absmax int8: quantize_symmetric_i8(row, 8), cpu/quantize.rs:32-49
-// one CTA per token row; optional fused RMSNorm (cpu/layer_norm.rs:118-137) in front
+// per-token absmax int8: quantize_symmetric_i8(row, 8), cpu/quantize.rs:32-49.
+// One CTA per token row. MODE selects what is fused in front of the quantiser:
+//   0  nothing (x is the row)
+//   1  RMSNorm, cpu/layer_norm.rs:118-137: x * (1/sqrt(mean_f64(x^2) + eps)) * gamma
+//   2  SwiGLU glue, transformer lib.rs:756-789: silu(gate) * up with (gate, up) interleaved
+//      in the input row (2K floats)
+// The fast kernel keeps the row in registers (16 values per thread, K <= 16 * blockDim);
+// the generic kernel re-reads it and takes any K.
 // ---------------------------------------------------------------------------------------
-template <bool NORM>
-__global__ void __launch_bounds__(256) actquant_kernel(const float* __restrict__ x,
-                                                       const float* __restrict__ gamma, float eps,
-                                                       int K, int8_t* __restrict__ q,
-                                                       float* __restrict__ scale,
-                                                       float* __restrict__ normed) {
+template <int MODE>
+__device__ __forceinline__ float fused_value(const float* __restrict__ xr,
+                                             const float* __restrict__ gamma, float inv_rms, int k) {
+    if (MODE == 2) {
+        const float g = xr[2 * k], u = xr[2 * k + 1];
+        return (g / (1.0f + expf(-g))) * u;
+    }
+    float v = xr[k];
+    if (MODE == 1) v = v * inv_rms * gamma[k];
+    return v;
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(1024) actquant_fast_kernel(const float* __restrict__ x,
+                                                             const float* __restrict__ gamma,
+                                                             float eps, int K,
+                                                             int8_t* __restrict__ q,
+                                                             float* __restrict__ scale,
+                                                             float* __restrict__ normed) {
+    __shared__ float shf[32];
+    __shared__ double shd[32];
+    const int row = blockIdx.x, tid = threadIdx.x, nt = blockDim.x;
+    const float* xr = x + (size_t)row * (MODE == 2 ? 2 * K : K);
+    float v[16];
+    // thread owns float4 groups g = tid + j*nt (j < 4): elements 4g .. 4g+3
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int k0 = (tid + j * nt) * 4;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) v[j * 4 + e] = 0.f;
+        if (MODE == 2) {
+            if (k0 + 4 <= K) {
+                const float4 a = *reinterpret_cast<const float4*>(xr + 2 * k0);
+                const float4 b = *reinterpret_cast<const float4*>(xr + 2 * k0 + 4);
+                v[j * 4 + 0] = (a.x / (1.0f + expf(-a.x))) * a.y;
+                v[j * 4 + 1] = (a.z / (1.0f + expf(-a.z))) * a.w;
+                v[j * 4 + 2] = (b.x / (1.0f + expf(-b.x))) * b.y;
+                v[j * 4 + 3] = (b.z / (1.0f + expf(-b.z))) * b.w;
+            } else {
+                for (int e = 0; e < 4; ++e)
+                    if (k0 + e < K) v[j * 4 + e] = fused_value<2>(xr, gamma, 1.f, k0 + e);
+            }
+        } else {
+            if (k0 + 4 <= K) {
+                const float4 a = *reinterpret_cast<const float4*>(xr + k0);
+                v[j * 4 + 0] = a.x; v[j * 4 + 1] = a.y; v[j * 4 + 2] = a.z; v[j * 4 + 3] = a.w;
+            } else {
+                for (int e = 0; e < 4; ++e)
+                    if (k0 + e < K) v[j * 4 + e] = xr[k0 + e];
+            }
+        }
+    }
+    if (MODE == 1) {
+        double ss = 0.0;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) ss += (double)v[i] * (double)v[i];
+        ss = block_sum_f64(ss, shd);
+        const float ms = (float)(ss / (double)K);
+        const float inv_rms = 1.0f / sqrtf(ms + eps);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int k0 = (tid + j * nt) * 4;
+            if (k0 + 4 <= K) {
+                const float4 g = *reinterpret_cast<const float4*>(gamma + k0);
+                v[j * 4 + 0] = v[j * 4 + 0] * inv_rms * g.x;
+                v[j * 4 + 1] = v[j * 4 + 1] * inv_rms * g.y;
+                v[j * 4 + 2] = v[j * 4 + 2] * inv_rms * g.z;
+                v[j * 4 + 3] = v[j * 4 + 3] * inv_rms * g.w;
+            } else {
+                for (int e = 0; e < 4; ++e)
+                    if (k0 + e < K) v[j * 4 + e] = v[j * 4 + e] * inv_rms * gamma[k0 + e];
+            }
+        }
+    }
+    float amax = 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) amax = fmaxf(amax, fabsf(v[i]));
+    amax = block_max(amax, shf);
+    const float sc = amax == 0.f ? 0.f : amax / 127.f;
+    const float inv = amax == 0.f ? 0.f : 1.0f / sc;
+    if (tid == 0) scale[row] = sc;
+    int8_t* qr = q + (size_t)row * K;
+    float* nr = normed ? normed + (size_t)row * K : nullptr;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int k0 = (tid + j * nt) * 4;
+        if (k0 >= K) continue;
+        int b[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) b[e] = amax == 0.f ? 0 : quant1(v[j * 4 + e], inv);
+        if (k0 + 4 <= K) {
+            *reinterpret_cast<uint32_t*>(qr + k0) = (uint32_t)(uint8_t)b[0] | ((uint32_t)(uint8_t)b[1] << 8) |
+                                                    ((uint32_t)(uint8_t)b[2] << 16) | ((uint32_t)(uint8_t)b[3] << 24);
+            if (nr) *reinterpret_cast<float4*>(nr + k0) = make_float4(v[j * 4], v[j * 4 + 1], v[j * 4 + 2], v[j * 4 + 3]);
+        } else {
+            for (int e = 0; e < 4; ++e)
+                if (k0 + e < K) {
+                    qr[k0 + e] = (int8_t)b[e];
+                    if (nr) nr[k0 + e] = v[j * 4 + e];
+                }
+        }
+    }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(256) actquant_generic_kernel(const float* __restrict__ x,
+                                                               const float* __restrict__ gamma,
+                                                               float eps, int K,
+                                                               int8_t* __restrict__ q,
+                                                               float* __restrict__ scale,
+                                                               float* __restrict__ normed) {
     __shared__ float shf[32];
     __shared__ double shd[32];
     const int row = blockIdx.x, tid = threadIdx.x;
-    const float* xr = x + (size_t)row * K;
-    const bool vec = (K % 4 == 0) && ((reinterpret_cast<uintptr_t>(xr) & 15) == 0);
-
+    const float* xr = x + (size_t)row * (MODE == 2 ? 2 * K : K);
     float inv_rms = 1.f;
-    if (NORM) {
+    if (MODE == 1) {
         double ss = 0.0;
         for (int k = tid; k < K; k += blockDim.x) {
             const double v = (double)xr[k];
@@ -67,51 +176,45 @@ __global__ void __launch_bounds__(256) actquant_kernel(const float* __restrict__
         const float ms = (float)(ss / (double)K);
         inv_rms = 1.0f / sqrtf(ms + eps);
     }
-    auto value = [&](int k) -> float {
-        float v = xr[k];
-        if (NORM) v = v * inv_rms * gamma[k];
-        return v;
-    };
-
     float amax = 0.f;
-    for (int k = tid; k < K; k += blockDim.x) amax = fmaxf(amax, fabsf(value(k)));
+    for (int k = tid; k < K; k += blockDim.x) amax = fmaxf(amax, fabsf(fused_value<MODE>(xr, gamma, inv_rms, k)));
     amax = block_max(amax, shf);
-
     const float sc = amax == 0.f ? 0.f : amax / 127.f;
     const float inv = amax == 0.f ? 0.f : 1.0f / sc;
     if (tid == 0) scale[row] = sc;
-
     int8_t* qr = q + (size_t)row * K;
     float* nr = normed ? normed + (size_t)row * K : nullptr;
-    if (vec && ((reinterpret_cast<uintptr_t>(qr) & 3) == 0)) {
-        for (int k4 = tid; k4 < K / 4; k4 += blockDim.x) {
-            const int k = k4 * 4;
-            const float v0 = value(k), v1 = value(k + 1), v2 = value(k + 2), v3 = value(k + 3);
-            int b0 = 0, b1 = 0, b2 = 0, b3 = 0;
-            if (amax != 0.f) {
-                b0 = quant1(v0, inv); b1 = quant1(v1, inv); b2 = quant1(v2, inv); b3 = quant1(v3, inv);
-            }
-            const uint32_t packed = (uint32_t)(uint8_t)b0 | ((uint32_t)(uint8_t)b1 << 8) |
-                                    ((uint32_t)(uint8_t)b2 << 16) | ((uint32_t)(uint8_t)b3 << 24);
-            *reinterpret_cast<uint32_t*>(qr + k) = packed;
-            if (nr) { nr[k] = v0; nr[k + 1] = v1; nr[k + 2] = v2; nr[k + 3] = v3; }
-        }
-    } else {
-        for (int k = tid; k < K; k += blockDim.x) {
-            const float v = value(k);
-            qr[k] = (int8_t)(amax == 0.f ? 0 : quant1(v, inv));
-            if (nr) nr[k] = v;
-        }
+    for (int k = tid; k < K; k += blockDim.x) {
+        const float v = fused_value<MODE>(xr, gamma, inv_rms, k);
+        qr[k] = (int8_t)(amax == 0.f ? 0 : quant1(v, inv));
+        if (nr) nr[k] = v;
     }
 }
 
+// mode: 0 plain, 1 rmsnorm, 2 silu(gate)*up on interleaved input
 int launch_actquant(const bitnet_b200_ctx* ctx, const float* x, const float* gamma, float eps,
-                    int M, int K, int8_t* q, float* scale, float* normed, bool norm) {
+                    int M, int K, int8_t* q, float* scale, float* normed, int mode) {
     if (M <= 0 || K <= 0) return fail("actquant: M and K must be > 0");
-    if (norm)
-        actquant_kernel<true><<<M, 256, 0, ctx->stream>>>(x, gamma, eps, K, q, scale, normed);
-    else
-        actquant_kernel<false><<<M, 256, 0, ctx->stream>>>(x, nullptr, 0.f, K, q, scale, normed);
+    const bool aligned = (K % 4 == 0) && ((reinterpret_cast<uintptr_t>(x) & 15) == 0) &&
+                         ((reinterpret_cast<uintptr_t>(q) & 3) == 0) &&
+                         (!normed || (reinterpret_cast<uintptr_t>(normed) & 15) == 0) &&
+                         (!gamma || (reinterpret_cast<uintptr_t>(gamma) & 15) == 0);
+    if (aligned && K <= 16384) {
+        int threads = (int)div_ceil((size_t)K, 16);
+        threads = (int)div_ceil((size_t)threads, 32) * 32;
+        if (threads < 64) threads = 64;
+        switch (mode) {
+            case 0: actquant_fast_kernel<0><<<M, threads, 0, ctx->stream>>>(x, gamma, eps, K, q, scale, normed); break;
+            case 1: actquant_fast_kernel<1><<<M, threads, 0, ctx->stream>>>(x, gamma, eps, K, q, scale, normed); break;
+            default: actquant_fast_kernel<2><<<M, threads, 0, ctx->stream>>>(x, gamma, eps, K, q, scale, normed); break;
+        }
+    } else {
+        switch (mode) {
+            case 0: actquant_generic_kernel<0><<<M, 256, 0, ctx->stream>>>(x, gamma, eps, K, q, scale, normed); break;
+            case 1: actquant_generic_kernel<1><<<M, 256, 0, ctx->stream>>>(x, gamma, eps, K, q, scale, normed); break;
+            default: actquant_generic_kernel<2><<<M, 256, 0, ctx->stream>>>(x, gamma, eps, K, q, scale, normed); break;
+        }
+    }
     B200_LAUNCH_CHECK("actquant_kernel");
     return 0;
 }

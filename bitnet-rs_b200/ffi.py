@@ -17,7 +17,20 @@ SYMBOLS = [
     "bitnet_b200_actquant_i8", "bitnet_b200_rmsnorm_actquant", "bitnet_b200_linear_i8",
     "bitnet_b200_linear_f32", "bitnet_b200_i2s_matmul_f32", "bitnet_b200_version",
     "bitnet_b200_launch_count",
+    "bitnet_b200_model_create", "bitnet_b200_model_destroy", "bitnet_b200_model_set_layer",
+    "bitnet_b200_model_set_embedding", "bitnet_b200_model_set_rope", "bitnet_b200_model_reset",
+    "bitnet_b200_model_decode", "bitnet_b200_model_decode_device", "bitnet_b200_model_set_tokens",
+    "bitnet_b200_model_get_tokens", "bitnet_b200_model_launches_per_step",
+    "bitnet_b200_model_time_linears",
+    "bitnet_b200_model_weight_bytes",
 ]
+
+
+class ModelConfig(C.Structure):
+    """bitnet_b200_model_config"""
+    _fields_ = [(n, C.c_int) for n in ("hidden", "ffn", "n_layers", "n_heads", "n_kv_heads", "head_dim",
+                                        "vocab", "max_ctx", "batch")] + [("rms_eps", C.c_float),
+                                                                         ("layout", C.c_int)]
 
 
 class B200Error(RuntimeError):
@@ -74,6 +87,22 @@ def lib():
         l.bitnet_b200_linear_i8.argtypes = [vp, vp, vp, vp, i32, vp, vp]
         l.bitnet_b200_linear_f32.argtypes = [vp, vp, vp, i32, vp]
         l.bitnet_b200_i2s_matmul_f32.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32]
+        l.bitnet_b200_model_create.argtypes = [vp, C.POINTER(ModelConfig), C.POINTER(vp)]
+        l.bitnet_b200_model_destroy.argtypes = [vp]
+        l.bitnet_b200_model_destroy.restype = None
+        l.bitnet_b200_model_set_layer.argtypes = [vp, i32] + [vp] * 9
+        l.bitnet_b200_model_set_embedding.argtypes = [vp, vp, vp]
+        l.bitnet_b200_model_set_rope.argtypes = [vp, vp, vp]
+        l.bitnet_b200_model_reset.argtypes = [vp]
+        l.bitnet_b200_model_decode.argtypes = [vp, vp, vp, vp]
+        l.bitnet_b200_model_decode_device.argtypes = [vp, i32]
+        l.bitnet_b200_model_set_tokens.argtypes = [vp, vp]
+        l.bitnet_b200_model_get_tokens.argtypes = [vp, vp]
+        l.bitnet_b200_model_time_linears.argtypes = [vp, i32, C.POINTER(C.c_float), C.POINTER(i32)]
+        l.bitnet_b200_model_launches_per_step.argtypes = [vp]
+        l.bitnet_b200_model_launches_per_step.restype = C.c_uint64
+        l.bitnet_b200_model_weight_bytes.argtypes = [vp]
+        l.bitnet_b200_model_weight_bytes.restype = C.c_uint64
         l.bitnet_b200_version.restype = C.c_char_p
         l.bitnet_b200_launch_count.restype = C.c_uint64
         _lib = l

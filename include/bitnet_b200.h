@@ -139,6 +139,46 @@ int bitnet_b200_linear_f32(bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, co
 int bitnet_b200_i2s_matmul_f32(const float* act, const uint8_t* packed, const float* scales,
                                float* out, int m, int n, int k, int block_size);
 
+/* ------------------------------------------------------------------------------------ *
+ * Part 4 -- decode harness ("next" rows of the scope table): a 2B-4T-shaped decoder     *
+ * step on device, the ternary linears above plus the glue the reference runs on the     *
+ * host through candle (crates/bitnet-transformer/src/lib.rs:275-543,751-798,1557-1630). *
+ * ------------------------------------------------------------------------------------ */
+typedef struct bitnet_b200_model bitnet_b200_model;
+typedef struct {
+    int hidden, ffn, n_layers, n_heads, n_kv_heads, head_dim, vocab, max_ctx, batch;
+    float rms_eps;
+    int layout; /* BITNET_B200_LAYOUT_* of every projection */
+} bitnet_b200_model_config; /* cf. BitNetConfig, crates/bitnet-common/src/config.rs:25-46 */
+
+int bitnet_b200_model_create(bitnet_b200_ctx* ctx, const bitnet_b200_model_config* cfg,
+                             bitnet_b200_model** out);
+void bitnet_b200_model_destroy(bitnet_b200_model* m);
+/* host bytes in the reference layout, [out, in] rows: wq [NH*D,H], wk/wv [NKV*D,H],
+ * wo [H,NH*D], wgate/wup [F,H], wdown [H,F]; norms are [H] f32 RMSNorm gains. */
+int bitnet_b200_model_set_layer(bitnet_b200_model* m, int layer, const void* wq, const void* wk,
+                                const void* wv, const void* wo, const void* wgate, const void* wup,
+                                const void* wdown, const float* attn_norm, const float* ffn_norm);
+/* tied embedding / LM head as IEEE f16 bits [vocab, hidden]; final RMSNorm gain [hidden] */
+int bitnet_b200_model_set_embedding(bitnet_b200_model* m, const uint16_t* emb_f16,
+                                    const float* final_norm);
+/* RoPE tables [max_ctx, head_dim/2] (split-half pairing, transformer lib.rs:134-184) */
+int bitnet_b200_model_set_rope(bitnet_b200_model* m, const float* cos_t, const float* sin_t);
+int bitnet_b200_model_reset(bitnet_b200_model* m); /* position <- 0 */
+/* one greedy step through HOST buffers: tokens[batch] in, next_tokens[batch] out (argmax,
+ * lowest index on ties), logits_out [batch, vocab] optional; synchronous */
+int bitnet_b200_model_decode(bitnet_b200_model* m, const int32_t* tokens, int32_t* next_tokens,
+                             float* logits_out);
+/* n greedy steps with the token fed back on device; asynchronous on the context's stream */
+int bitnet_b200_model_decode_device(bitnet_b200_model* m, int n_steps);
+int bitnet_b200_model_set_tokens(bitnet_b200_model* m, const int32_t* tokens);
+int bitnet_b200_model_get_tokens(bitnet_b200_model* m, int32_t* next_tokens);
+/* times only the ternary linears of one step (graph replay between events on the stream) */
+int bitnet_b200_model_time_linears(bitnet_b200_model* m, int reps, float* ms_per_pass,
+                                   int* launches_per_pass);
+uint64_t bitnet_b200_model_launches_per_step(const bitnet_b200_model* m);
+uint64_t bitnet_b200_model_weight_bytes(const bitnet_b200_model* m); /* packed ternary bytes */
+
 /* library / build identification */
 const char* bitnet_b200_version(void);
 /* number of kernels this library has launched on the calling process (bench bookkeeping) */

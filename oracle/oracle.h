@@ -124,6 +124,24 @@ void oracle_fill_bytes(uint8_t* dst, size_t n, uint64_t seed);
 void oracle_fill_normal(float* dst, size_t n, uint64_t seed, float sigma);
 void oracle_fill_uniform(float* dst, size_t n, uint64_t seed, float lo, float hi);
 
+/* ---- 2B-4T-shaped decoder built from the pieces above (model.cpp) ---- */
+typedef struct {
+    int hidden, ffn, n_layers, n_heads, n_kv_heads, head_dim, vocab, max_ctx;
+    float rms_eps;
+    int layout; /* 0 = QK256, 1 = BitNet32-F16 */
+} oracle_model_config;
+void* oracle_model_create(const oracle_model_config* cfg, int n_seqs);
+void oracle_model_destroy(void* m);
+int oracle_model_set_layer(void* m, int layer, const uint8_t* wq, const uint8_t* wk,
+                           const uint8_t* wv, const uint8_t* wo, const uint8_t* wgate,
+                           const uint8_t* wup, const uint8_t* wdown, const float* attn_norm,
+                           const float* ffn_norm);
+int oracle_model_set_embedding(void* m, const uint16_t* emb_f16, const float* final_norm);
+int oracle_model_set_rope(void* m, const float* cos_t, const float* sin_t);
+void oracle_model_reset(void* m);
+int oracle_model_step(void* m, int seq, int token, float* logits_out, float* hidden_out,
+                      int threads);
+
 #ifdef __cplusplus
 }
 #endif

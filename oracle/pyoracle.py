@@ -338,3 +338,64 @@ def ref_lib():
     l.bitnet_dequantize_row_iq2_s.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
     l.bitnet_dequantize_row_iq2_s.restype = None
     return l
+
+
+# ---- 2B-4T-shaped decoder (oracle/model.cpp) ------------------------------------------
+class _ModelConfig(C.Structure):
+    _fields_ = [(n, C.c_int) for n in ("hidden", "ffn", "n_layers", "n_heads", "n_kv_heads", "head_dim",
+                                        "vocab", "max_ctx")] + [("rms_eps", C.c_float), ("layout", C.c_int)]
+
+
+class Model:
+    """CPU oracle model; `shape` is any object with the ModelShape fields."""
+
+    def __init__(self, shape, n_seqs=1, threads=None):
+        self._lib = lib()
+        self._lib.oracle_model_create.restype = C.c_void_p
+        self._lib.oracle_model_create.argtypes = [C.POINTER(_ModelConfig), C.c_int]
+        self._lib.oracle_model_destroy.argtypes = [C.c_void_p]
+        self._lib.oracle_model_set_layer.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 9
+        self._lib.oracle_model_set_embedding.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        self._lib.oracle_model_set_rope.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        self._lib.oracle_model_reset.argtypes = [C.c_void_p]
+        self._lib.oracle_model_step.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
+        self.shape = shape
+        self.threads = threads or os.cpu_count() or 1
+        cfg = _ModelConfig(shape.hidden, shape.ffn, shape.n_layers, shape.n_heads, shape.n_kv_heads,
+                           shape.head_dim, shape.vocab, shape.max_ctx, shape.rms_eps, shape.layout)
+        self._h = self._lib.oracle_model_create(C.byref(cfg), n_seqs)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.oracle_model_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_layer(self, layer, w):
+        arrs = [_c(w[k], np.uint8) for k in ("wq", "wk", "wv", "wo", "wgate", "wup", "wdown")]
+        arrs += [_c(w[k], np.float32) for k in ("attn_norm", "ffn_norm")]
+        _chk(self._lib.oracle_model_set_layer(self._h, layer, *[_p(a) for a in arrs]))
+
+    def set_embedding(self, emb_f16, final_norm):
+        e, f = _c(emb_f16, np.uint16), _c(final_norm, np.float32)
+        _chk(self._lib.oracle_model_set_embedding(self._h, _p(e), _p(f)))
+
+    def set_rope(self, cos_t, sin_t):
+        c, s = _c(cos_t, np.float32), _c(sin_t, np.float32)
+        _chk(self._lib.oracle_model_set_rope(self._h, _p(c), _p(s)))
+
+    def reset(self):
+        self._lib.oracle_model_reset(self._h)
+
+    def step(self, token, seq=0, want_logits=False):
+        logits = np.zeros(self.shape.vocab, np.float32) if want_logits else None
+        t = self._lib.oracle_model_step(self._h, seq, int(token), None if logits is None else _p(logits),
+                                        None, self.threads)
+        if t < 0:
+            raise OracleError("oracle_model_step failed")
+        return (t, logits) if want_logits else t
