@@ -266,6 +266,32 @@ static size_t row_bytes(int layout, size_t cols) {
     return layout == BITNET_B200_LAYOUT_QK256 ? div_ceil(cols, 256) * 64 : cols / 32 * 10;
 }
 
+// Swaps the context onto a private capturable stream for the lifetime of a graph capture.
+struct CaptureStream {
+    bitnet_b200_ctx* ctx;
+    cudaStream_t s = nullptr, saved = nullptr;
+    bool swapped = false;
+    explicit CaptureStream(bitnet_b200_ctx* c) : ctx(c) {
+        if (cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking) != cudaSuccess) {
+            fail("cudaStreamCreateWithFlags failed for graph capture");
+            s = nullptr;
+            return;
+        }
+        saved = ctx->stream;
+        ctx->stream = s;
+        swapped = true;
+    }
+    bool ok() const { return s != nullptr; }
+    void restore() {
+        if (swapped) ctx->stream = saved;
+        swapped = false;
+    }
+    ~CaptureStream() {
+        restore();
+        if (s) cudaStreamDestroy(s);
+    }
+};
+
 static int enqueue_step(bitnet_b200_model* m) {
     const auto& c = m->cfg;
     bitnet_b200_ctx* ctx = m->ctx;
@@ -326,11 +352,15 @@ static int ensure_graph(bitnet_b200_model* m) {
     const int smem = m->cfg.max_ctx * 4;
     if (smem > 48 * 1024)
         B200_CUDA(cudaFuncSetAttribute(attn_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    cudaStream_t st = m->ctx->stream;
+    // capture on a private stream (the legacy default stream cannot be captured), then the
+    // instantiated graph is launched on the context's stream
+    CaptureStream cap(m->ctx);
+    if (!cap.ok()) return -1;
     cudaGraph_t g = nullptr;
-    B200_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+    B200_CUDA(cudaStreamBeginCapture(cap.s, cudaStreamCaptureModeThreadLocal));
     const int rc = enqueue_step(m);
-    cudaError_t e = cudaStreamEndCapture(st, &g);
+    cudaError_t e = cudaStreamEndCapture(cap.s, &g);
+    cap.restore();
     if (rc) {
         if (g) cudaGraphDestroy(g);
         return -1;
@@ -555,7 +585,9 @@ int bitnet_b200_model_time_linears(bitnet_b200_model* m, int reps, float* ms_per
         cudaGraph_t g = nullptr;
         cudaGraphExec_t ge = nullptr;
         const uint64_t l0 = g_launches.load();
-        B200_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+        CaptureStream cap(m->ctx);
+        if (!cap.ok()) return -1;
+        B200_CUDA(cudaStreamBeginCapture(cap.s, cudaStreamCaptureModeThreadLocal));
         int rc = 0;
         for (int l = 0; l < c.n_layers && !rc; ++l) {
             const LayerW& L = m->layers[(size_t)l];
@@ -564,7 +596,8 @@ int bitnet_b200_model_time_linears(bitnet_b200_model* m, int reps, float* ms_per
                  launch_gemv_i8(m->ctx, L.wgateup, m->q8, m->s8, B, m->gu, nullptr, nullptr) ||
                  launch_gemv_i8(m->ctx, L.wdown, m->q8, m->s8, B, m->xn, nullptr, nullptr);
         }
-        cudaError_t e = cudaStreamEndCapture(st, &g);
+        cudaError_t e = cudaStreamEndCapture(cap.s, &g);
+        cap.restore();
         const int per_pass = (int)(g_launches.load() - l0);
         if (rc) {
             if (g) cudaGraphDestroy(g);
