@@ -20,6 +20,9 @@ from .provider import (  # noqa: F401
     i2s_matmul_f32,
 )
 from .device import (  # noqa: F401
+    EPI_RESIDUAL,
+    EPI_STORE,
+    EPI_SWIGLU,
     LAYOUT_BITNET32_F16,
     LAYOUT_QK256,
     MAP_A,

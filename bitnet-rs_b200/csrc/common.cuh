@@ -110,28 +110,80 @@ __device__ __forceinline__ uint16_t ldg_nc_u16(const void* p) {
     return v;
 }
 
-// Decode one 32-bit word of sixteen 2-bit codes through a 4-entry int8 LUT (one PRMT per
-// four weights) and dot it with sixteen int8 activations that were pre-permuted into
-//   E0=[a0,a2,a4,a6] O0=[a1,a3,a5,a7] E1=[a8,a10,a12,a14] O1=[a9,a11,a13,a15].
-__device__ __forceinline__ int dot16(uint32_t w, uint32_t lut, uint32_t E0, uint32_t O0,
-                                     uint32_t E1, uint32_t O1, int acc) {
+// ---- device code-plane layout -------------------------------------------------------------
+// The reference packs code k of a 16-weight word at bits [2k, 2k+1] (LSB first,
+// i2s_qk256.rs:159-168). At upload every 32-bit word is bit-permuted ONCE (lossless, see
+// repack_word) so that the four PRMT selectors of a word come out in natural k order:
+//   k = 0..3  -> bits 4k          k = 4..7   -> bits 4(k-4)+2
+//   k = 8..11 -> bits 16+4(k-8)   k = 12..15 -> bits 18+4(k-12)
+// i.e. (w & 0x3333) selects k=0..3, ((w>>2) & 0x3333) k=4..7, and the same on the high half.
+__host__ __device__ __forceinline__ int code_bitpos(int k) {
+    return ((k & 8) ? 16 : 0) + ((k & 4) ? 2 : 0) + 4 * (k & 3);
+}
+__host__ __device__ __forceinline__ uint32_t repack_word(uint32_t w) {
+    uint32_t r = 0;
+    for (int k = 0; k < 16; ++k) r |= ((w >> (2 * k)) & 3u) << code_bitpos(k);
+    return r;
+}
+__device__ __forceinline__ uint32_t code_of(uint32_t w_dev, int k) { return (w_dev >> code_bitpos(k)) & 3u; }
+
+// Decode one device-layout word (sixteen 2-bit codes) through a 4-entry int8 LUT -- one PRMT
+// per four weights -- and dot it with sixteen int8 activations in natural order (a.x = k0..3).
+// The two >>16 go through IMAD.HI (FMA pipe) to keep the ALU pipe for LOP3/PRMT.
+__device__ __forceinline__ int dot16(uint32_t w, uint32_t lut, uint4 a, int acc) {
     const uint32_t x = w & 0x33333333u;
-    const uint32_t y = (w >> 2) & 0x33333333u;
-    acc = dp4a_ss(prmt(lut, 0u, x), E0, acc);
-    acc = dp4a_ss(prmt(lut, 0u, y), O0, acc);
-    acc = dp4a_ss(prmt(lut, 0u, x >> 16), E1, acc);
-    acc = dp4a_ss(prmt(lut, 0u, y >> 16), O1, acc);
+    const uint32_t y = __umulhi(w, 0x40000000u) & 0x33333333u;  // (w >> 2) & mask
+    acc = dp4a_ss(prmt(lut, 0u, x), a.x, acc);
+    acc = dp4a_ss(prmt(lut, 0u, y), a.y, acc);
+    acc = dp4a_ss(prmt(lut, 0u, __umulhi(x, 0x10000u)), a.z, acc);
+    acc = dp4a_ss(prmt(lut, 0u, __umulhi(y, 0x10000u)), a.w, acc);
     return acc;
 }
-
-// permute 16 consecutive int8 activations (as 4 words) into the E/O order dot16 expects
-__device__ __forceinline__ void permute_act16(uint4 a, uint32_t& E0, uint32_t& O0, uint32_t& E1,
-                                              uint32_t& O1) {
-    E0 = prmt(a.x, a.y, 0x6420u);
-    O0 = prmt(a.x, a.y, 0x7531u);
-    E1 = prmt(a.z, a.w, 0x6420u);
-    O1 = prmt(a.z, a.w, 0x7531u);
+// decode a device-layout word into sixteen int8 values in natural order (4 words)
+__device__ __forceinline__ uint4 decode16(uint32_t w, uint32_t lut) {
+    const uint32_t x = w & 0x33333333u;
+    const uint32_t y = __umulhi(w, 0x40000000u) & 0x33333333u;
+    return make_uint4(prmt(lut, 0u, x), prmt(lut, 0u, y), prmt(lut, 0u, __umulhi(x, 0x10000u)),
+                      prmt(lut, 0u, __umulhi(y, 0x10000u)));
 }
+
+// ---- PTX: mbarrier, 1-D bulk copy (TMA), programmatic dependent launch ----------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(void* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(void* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(void* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(void* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+// bounded wait: a lost completion traps (reported as a launch failure) instead of hanging the GPU
+__device__ __forceinline__ void mbar_wait(void* bar, uint32_t parity) {
+    for (uint32_t it = 0; !mbar_try_wait(bar, parity); ++it)
+        if (it > (1u << 28)) __trap();
+}
+// global -> shared bulk copy; size and both addresses multiples of 16 B
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32_t bytes, void* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst_smem)), "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+// PDL: let the next kernel of the stream start launching / wait for the previous one to finish
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

@@ -14,8 +14,18 @@
 #include <vector>
 
 #include "common.cuh"
+#include "decode_fused.cuh"
 
 namespace b200 {
+
+// gemv_stream.cu: 1 = shape unsupported (use the generic kernels), 0 = ok, -1 = error
+int launch_gemv_stream(const bitnet_b200_ctx*, const bitnet_b200_weight*, int M, int pro, const int8_t* q,
+                       const float* act_scale, const float* x, const float* gamma, float eps, int epi, float* y,
+                       const float* residual, int32_t* acc_out, int8_t* q_out, float* scale_out, float* normed_out,
+                       bool pdl);
+bool gemv_stream_supported(const bitnet_b200_ctx*, const bitnet_b200_weight*, int M, bool f32_prologue);
+enum { PRO_Q8 = 0, PRO_F32 = 1, PRO_RMS = 2 };
+enum { EPI_STORE = 0, EPI_RESIDUAL = 1, EPI_SWIGLU = 2 };
 
 int launch_gemv_i8(const bitnet_b200_ctx*, const bitnet_b200_weight*, const int8_t*, const float*,
                    int, float*, int32_t*, const float* residual);
@@ -239,6 +249,9 @@ struct bitnet_b200_model {
     float *kc = nullptr, *vc = nullptr;  // [L][B][NKV][max_ctx][D]
     int *pos = nullptr, *tokens = nullptr, *next = nullptr;
     float *x = nullptr, *qkv = nullptr, *att = nullptr, *gu = nullptr, *xn = nullptr, *logits = nullptr;
+    float* part_val = nullptr;  // [B, logits CTAs] per-CTA argmax partials (fused path)
+    int* part_idx = nullptr;
+    int fused = -1;             // -1 undecided, 0 generic kernels, 1 fused PDL path
     int8_t* q8 = nullptr;
     float* s8 = nullptr;
     int* next_host = nullptr;  // pinned
@@ -292,7 +305,97 @@ struct CaptureStream {
     }
 };
 
+constexpr size_t LOGITS_ROWS_PER_CTA = 64;
+
+// BITNET_B200_NO_PDL=1 launches the same kernels with ordinary stream serialisation
+static bool use_pdl() {
+    static const bool v = getenv("BITNET_B200_NO_PDL") == nullptr;
+    return v;
+}
+
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                              Args... args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = use_pdl() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
+static bool fused_supported(const bitnet_b200_model* m) {
+    const auto& c = m->cfg;
+    if (c.batch > 4 || c.hidden % 8 || c.hidden / 8 > 1024 || c.head_dim > 256) return false;
+    if (getenv("BITNET_B200_NO_FUSED")) return false;
+    const LayerW& L = m->layers[0];
+    return gemv_stream_supported(m->ctx, L.wqkv, c.batch, true) && gemv_stream_supported(m->ctx, L.wo, c.batch, true) &&
+           gemv_stream_supported(m->ctx, L.wgateup, c.batch, true) && gemv_stream_supported(m->ctx, L.wdown, c.batch, true);
+}
+
+// The fused step: per layer  [RMSNorm+quant | qkv GEMV] -> [RoPE+KV append+attention] ->
+// [quant | o GEMV + residual] -> [RMSNorm+quant | gate/up GEMV | SwiGLU] -> [quant | down GEMV +
+// residual]; then [final RMSNorm | logits | argmax partials] -> [argmax]. 5 L + 3 launches.
+static int enqueue_step_fused(bitnet_b200_model* m) {
+    const auto& c = m->cfg;
+    bitnet_b200_ctx* ctx = m->ctx;
+    cudaStream_t st = ctx->stream;
+    const int B = c.batch, H = c.hidden, D = c.head_dim, NH = c.n_heads, NKV = c.n_kv_heads;
+    const uint64_t l0 = g_launches.load();
+    B200_CUDA(launch_pdl(embed_pdl_kernel, dim3(B), dim3(256), 0, st, m->emb, m->tokens, m->x, H));
+    count_launch();
+    for (int l = 0; l < c.n_layers; ++l) {
+        const LayerW& L = m->layers[(size_t)l];
+        const size_t kvoff = (size_t)l * B * NKV * c.max_ctx * D;
+        if (launch_gemv_stream(ctx, L.wqkv, B, PRO_RMS, nullptr, nullptr, m->x, L.attn_norm, c.rms_eps, EPI_STORE,
+                               m->qkv, nullptr, nullptr, nullptr, nullptr, nullptr, use_pdl()))
+            return fail("fused decode: qkv projection rejected by the streaming GEMV");
+        B200_CUDA(launch_pdl(attn_fused_kernel, dim3(NH, B), dim3(D), (size_t)c.max_ctx * 4, st, m->qkv, m->rope_cos,
+                             m->rope_sin, m->kc + kvoff, m->vc + kvoff, m->att, m->pos, NH, NKV, D, c.max_ctx));
+        count_launch();
+        if (launch_gemv_stream(ctx, L.wo, B, PRO_F32, nullptr, nullptr, m->att, nullptr, 0.f, EPI_RESIDUAL, m->x, m->x,
+                               nullptr, nullptr, nullptr, nullptr, use_pdl()))
+            return fail("fused decode: o projection rejected by the streaming GEMV");
+        if (launch_gemv_stream(ctx, L.wgateup, B, PRO_RMS, nullptr, nullptr, m->x, L.ffn_norm, c.rms_eps, EPI_SWIGLU,
+                               m->gu, nullptr, nullptr, nullptr, nullptr, nullptr, use_pdl()))
+            return fail("fused decode: gate/up projection rejected by the streaming GEMV");
+        if (launch_gemv_stream(ctx, L.wdown, B, PRO_F32, nullptr, nullptr, m->gu, nullptr, 0.f, EPI_RESIDUAL, m->x, m->x,
+                               nullptr, nullptr, nullptr, nullptr, use_pdl()))
+            return fail("fused decode: down projection rejected by the streaming GEMV");
+    }
+    {
+        const int threads = (int)div_ceil((size_t)H / 8, 32) * 32;
+        const int rpc = (int)LOGITS_ROWS_PER_CTA;
+        const int grid = (int)div_ceil((size_t)c.vocab, (size_t)rpc);
+        const size_t smem = 2 * (size_t)(threads / 32) * 16 * 4;
+        cudaError_t e;
+        if (B == 1)
+            e = launch_pdl(logits_fused_kernel<1, 8>, dim3(grid), dim3(threads), smem, st, m->emb, m->x, m->final_norm,
+                           c.rms_eps, m->logits, m->part_val, m->part_idx, c.vocab, H, B, rpc);
+        else if (B == 2)
+            e = launch_pdl(logits_fused_kernel<2, 8>, dim3(grid), dim3(threads), smem, st, m->emb, m->x, m->final_norm,
+                           c.rms_eps, m->logits, m->part_val, m->part_idx, c.vocab, H, B, rpc);
+        else
+            e = launch_pdl(logits_fused_kernel<4, 4>, dim3(grid), dim3(threads), smem, st, m->emb, m->x, m->final_norm,
+                           c.rms_eps, m->logits, m->part_val, m->part_idx, c.vocab, H, B, rpc);
+        B200_CUDA(e);
+        count_launch();
+        B200_CUDA(launch_pdl(argmax_final_kernel, dim3(B), dim3(256), 0, st, m->part_val, m->part_idx, grid, m->next,
+                             m->tokens, m->pos));
+        count_launch();
+    }
+    m->launches_per_step = g_launches.load() - l0;
+    return 0;
+}
+
 static int enqueue_step(bitnet_b200_model* m) {
+    if (m->fused < 0) m->fused = fused_supported(m) ? 1 : 0;
+    if (m->fused) return enqueue_step_fused(m);
     const auto& c = m->cfg;
     bitnet_b200_ctx* ctx = m->ctx;
     cudaStream_t st = ctx->stream;
@@ -350,8 +453,10 @@ static int ensure_graph(bitnet_b200_model* m) {
     if (!m->have_emb || !m->have_rope || m->layers_set != m->cfg.n_layers)
         return fail("model: weights incomplete (set every layer, the embedding and the RoPE tables first)");
     const int smem = m->cfg.max_ctx * 4;
-    if (smem > 48 * 1024)
+    if (smem > 48 * 1024) {
         B200_CUDA(cudaFuncSetAttribute(attn_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        B200_CUDA(cudaFuncSetAttribute(attn_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    }
     // capture on a private stream (the legacy default stream cannot be captured), then the
     // instantiated graph is launched on the context's stream
     CaptureStream cap(m->ctx);
@@ -404,6 +509,8 @@ int bitnet_b200_model_create(bitnet_b200_ctx* ctx, const bitnet_b200_model_confi
             return -1;
         const size_t qmax = std::max(std::max(H, F), NH * D);
         if (dmalloc((void**)&m->q8, B * qmax) || dmalloc((void**)&m->s8, B * 4)) return -1;
+        const size_t nparts = div_ceil((size_t)c.vocab, LOGITS_ROWS_PER_CTA);
+        if (dmalloc((void**)&m->part_val, B * nparts * 4) || dmalloc((void**)&m->part_idx, B * nparts * 4)) return -1;
         B200_CUDA(cudaMallocHost((void**)&m->next_host, B * 4));
         B200_CUDA(cudaMallocHost((void**)&m->tok_host, B * 4));
         B200_CUDA(cudaMemsetAsync(m->kc, 0, kv * 4, ctx->stream));
@@ -430,7 +537,8 @@ void bitnet_b200_model_destroy(bitnet_b200_model* m) {
         cudaFree(L.ffn_norm);
     }
     void* ptrs[] = {m->emb, m->final_norm, m->rope_cos, m->rope_sin, m->kc, m->vc, m->pos, m->tokens,
-                    m->next, m->x, m->qkv, m->att, m->gu, m->xn, m->logits, m->q8, m->s8};
+                    m->next, m->x, m->qkv, m->att, m->gu, m->xn, m->logits, m->q8, m->s8, m->part_val,
+                    m->part_idx};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (m->next_host) cudaFreeHost(m->next_host);
@@ -591,10 +699,16 @@ int bitnet_b200_model_time_linears(bitnet_b200_model* m, int reps, float* ms_per
         int rc = 0;
         for (int l = 0; l < c.n_layers && !rc; ++l) {
             const LayerW& L = m->layers[(size_t)l];
-            rc = launch_gemv_i8(m->ctx, L.wqkv, m->q8, m->s8, B, m->qkv, nullptr, nullptr) ||
-                 launch_gemv_i8(m->ctx, L.wo, m->q8, m->s8, B, m->xn, nullptr, nullptr) ||
-                 launch_gemv_i8(m->ctx, L.wgateup, m->q8, m->s8, B, m->gu, nullptr, nullptr) ||
-                 launch_gemv_i8(m->ctx, L.wdown, m->q8, m->s8, B, m->xn, nullptr, nullptr);
+            const bitnet_b200_weight* ws[4] = {L.wqkv, L.wo, L.wgateup, L.wdown};
+            float* outs[4] = {m->qkv, m->xn, m->gu, m->xn};
+            for (int i = 0; i < 4 && !rc; ++i) {
+                int r = 1;
+                if (m->fused != 0)
+                    r = launch_gemv_stream(m->ctx, ws[i], B, PRO_Q8, m->q8, m->s8, nullptr, nullptr, 0.f, EPI_STORE,
+                                           outs[i], nullptr, nullptr, nullptr, nullptr, nullptr, use_pdl());
+                if (r == 1) r = launch_gemv_i8(m->ctx, ws[i], m->q8, m->s8, B, outs[i], nullptr, nullptr);
+                rc = r;
+            }
         }
         cudaError_t e = cudaStreamEndCapture(cap.s, &g);
         cap.restore();

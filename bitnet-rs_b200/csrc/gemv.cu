@@ -6,6 +6,8 @@
 //   (crates/bitnet-kernels/src/cpu/quantized_matmul.rs:155-200); fills the stub
 //   launch_qk256_gemv (crates/bitnet-kernels/src/cuda/qk256_gemv.rs:119-137).
 //
+// This file holds the GENERIC kernels (any K, any LUT, M up to 8 per pass); the decode fast
+// path for the model shapes is gemv_stream.cu.
 // Mapping (B200-first, not the reference's row-per-thread plan): thread t of a CTA owns the
 // 16-weight word t of EVERY row, so its sixteen int8 activations live in registers for the
 // whole kernel and a warp's weight load is one fully coalesced 128-byte line per row. Each
@@ -63,13 +65,13 @@ __global__ void __launch_bounds__(1024) gemv_i8_kernel(const GemvParams p) {
     const int nwarps = blockDim.x >> 5;
     const bool active = tid < p.nwords;
 
-    // activations: registers for the whole kernel, permuted for dot16
-    uint32_t E0[MT], O0[MT], E1[MT], O1[MT];
+    // activations: registers for the whole kernel (natural k order; the code plane was
+    // bit-permuted at upload so that dot16 decodes in that order)
+    uint4 act[MT];
 #pragma unroll
     for (int m = 0; m < MT; ++m) {
-        uint4 a = make_uint4(0, 0, 0, 0);
-        if (active && m < p.M) a = load_act16(p.q, p.K, m, tid);
-        permute_act16(a, E0[m], O0[m], E1[m], O1[m]);
+        act[m] = make_uint4(0, 0, 0, 0);
+        if (active && m < p.M) act[m] = load_act16(p.q, p.K, m, tid);
     }
 
     const int row_begin = blockIdx.x * p.rows_per_cta;
@@ -102,7 +104,7 @@ __global__ void __launch_bounds__(1024) gemv_i8_kernel(const GemvParams p) {
         for (int r = 0; r < R; ++r) {
 #pragma unroll
             for (int m = 0; m < MT; ++m) {
-                const int d = dot16(w[r], p.lut, E0[m], O0[m], E1[m], O1[m], 0);
+                const int d = dot16(w[r], p.lut, act[m], 0);
                 if (SCALED) {
                     if (WACC) {
                         // per-32 block accumulator = this half-block + the neighbouring lane's
@@ -173,7 +175,7 @@ __global__ void __launch_bounds__(1024) gemv_f32_kernel(const uint8_t* __restric
             float a0 = 0.f, a1 = 0.f;
 #pragma unroll
             for (int j = 0; j < 16; j += 2) {
-                const uint32_t c0 = (w[r] >> (2 * j)) & 3u, c1 = (w[r] >> (2 * j + 2)) & 3u;
+                const uint32_t c0 = code_of(w[r], j), c1 = code_of(w[r], j + 1);
                 const float w0 = c0 & 2u ? (c0 & 1u ? l3 : l2) : (c0 & 1u ? l1 : l0);
                 const float w1 = c1 & 2u ? (c1 & 1u ? l3 : l2) : (c1 & 1u ? l1 : l0);
                 a0 = fmaf(w0, xv[j], a0);

@@ -410,7 +410,7 @@ __global__ void split_bitnet32_kernel(const uint8_t* __restrict__ src, size_t nb
         lo |= (uint32_t)s[j] << (8 * j);
         hi |= (uint32_t)s[4 + j] << (8 * j);
     }
-    reinterpret_cast<uint2*>(codes)[b] = make_uint2(lo, hi);
+    reinterpret_cast<uint2*>(codes)[b] = make_uint2(repack_word(lo), repack_word(hi));
     const uint16_t hb = (uint16_t)(s[8] | (s[9] << 8));
     scales[b] = __ushort_as_half(hb);
     float sv = __half2float(__ushort_as_half(hb));
@@ -428,6 +428,21 @@ int launch_split_bitnet32(cudaStream_t st, const uint8_t* src, size_t nblocks, u
     split_bitnet32_kernel<<<(unsigned)div_ceil(nblocks, threads), threads, 0, st>>>(
         src, nblocks, codes, scales, scales_f32, clamp);
     B200_LAUNCH_CHECK("split_bitnet32_kernel");
+    return 0;
+}
+
+// QK256 upload: bit-permute every 32-bit word of the code plane into the device layout
+// (common.cuh, repack_word) -- lossless, same size, done once.
+__global__ void repack_codes_kernel(uint32_t* __restrict__ words, size_t nwords) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < nwords) words[i] = repack_word(words[i]);
+}
+
+int launch_repack_codes(cudaStream_t st, uint8_t* codes, size_t nbytes) {
+    const size_t nwords = nbytes / 4;
+    if (nwords == 0) return 0;
+    repack_codes_kernel<<<(unsigned)div_ceil(nwords, 256), 256, 0, st>>>(reinterpret_cast<uint32_t*>(codes), nwords);
+    B200_LAUNCH_CHECK("repack_codes_kernel");
     return 0;
 }
 

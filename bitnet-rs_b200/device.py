@@ -13,6 +13,9 @@ LAYOUT_QK256 = 0
 LAYOUT_BITNET32_F16 = 1
 SCALE_ABS_CLAMP = 0
 SCALE_RAW = 1
+EPI_STORE = 0
+EPI_RESIDUAL = 1
+EPI_SWIGLU = 2
 MAP_A = (-2, -1, 1, 2)   # i2s_qk256.rs:139-146 -- production map of both layouts
 MAP_B = (-2, -1, 0, 1)   # quantization/src/utils.rs:76-91
 MAP_C = (0, 1, 0, -1)    # kernels/src/cpu/quantized_matmul.rs:19-27
@@ -113,6 +116,25 @@ class Context:
             self._h, w._h, _dev_ptr(q, torch.int8, "q"), _dev_ptr(act_scale, torch.float32, "act_scale"),
             M, _dev_ptr(y, torch.float32, "y"), None if acc is None else acc.data_ptr()))
         return (y, acc) if want_acc else y
+
+    def fused_linear(self, w, x, gamma=None, eps=1e-5, epilogue=EPI_STORE, y=None, residual=None, want_q=False):
+        """[RMSNorm ->] act-quant -> ternary linear -> epilogue in ONE launch (decode, M <= 4)."""
+        torch = _torch()
+        M = x.shape[0]
+        if x.shape[1] != w.cols:
+            raise ValueError("x has %d columns, weight has %d" % (x.shape[1], w.cols))
+        n_out = w.rows // 2 if epilogue == EPI_SWIGLU else w.rows
+        y = torch.empty((M, n_out), dtype=torch.float32, device=x.device) if y is None else y
+        q = s = None
+        if want_q:
+            q = torch.empty((M, w.cols), dtype=torch.int8, device=x.device)
+            s = torch.empty((M,), dtype=torch.float32, device=x.device)
+        ffi.check(self._lib.bitnet_b200_fused_linear(
+            self._h, w._h, _dev_ptr(x, torch.float32, "x"),
+            None if gamma is None else _dev_ptr(gamma, torch.float32, "gamma"), C.c_float(eps), M, int(epilogue),
+            _dev_ptr(y, torch.float32, "y"), None if residual is None else _dev_ptr(residual, torch.float32, "residual"),
+            None if q is None else q.data_ptr(), None if s is None else s.data_ptr()))
+        return (y, q, s) if want_q else y
 
     def linear_f32(self, w, x, y=None):
         torch = _torch()

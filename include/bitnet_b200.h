@@ -126,6 +126,23 @@ int bitnet_b200_rmsnorm_actquant(bitnet_b200_ctx* ctx, const float* x, const flo
  * It exists so the bit-exact check can read the accumulators directly. */
 int bitnet_b200_linear_i8(bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, const int8_t* q,
                           const float* act_scale, int M, float* y, int32_t* acc_out);
+/* The decode fast path as ONE launch (gemv_stream.cu): [RMSNorm ->] per-token absmax int8
+ * quantise -> ternary linear -> epilogue. It is the composition of rmsnorm_actquant /
+ * actquant_i8 and linear_i8 above, bit for bit, with the activation work done in the GEMV's
+ * prologue ("act-quant fused with RMSNorm", here fused into the consumer so that no separate
+ * launch sits on the token's critical path). DEVICE pointers.
+ *   x [M,K] f32; gamma [K] f32 or NULL (no norm); eps as cpu::rms_norm;
+ *   epilogue BITNET_B200_EPI_STORE    y[M,N]  = act_scale * acc (* block scales)
+ *            BITNET_B200_EPI_RESIDUAL y[M,N]  = residual[M,N] + that (residual may alias y)
+ *            BITNET_B200_EPI_SWIGLU   y[M,N/2]= silu(row 2i) * row 2i+1  (gate/up rows interleaved;
+ *                                      crates/bitnet-transformer/src/lib.rs:756-789)
+ *   q_out [M,K] int8 / scale_out [M] f32: optional copies of what the prologue quantised.
+ * M <= 4 and K % 64 == 0 (BitNet32-F16: K % 256 == 0); other shapes are an error here --
+ * call the two-step API. */
+enum { BITNET_B200_EPI_STORE = 0, BITNET_B200_EPI_RESIDUAL = 1, BITNET_B200_EPI_SWIGLU = 2 };
+int bitnet_b200_fused_linear(bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, const float* x,
+                             const float* gamma, float eps, int M, int epilogue, float* y,
+                             const float* residual, int8_t* q_out, float* scale_out);
 /* f32-activation GEMV on a device-resident QK256 weight (device twin of Part 2):
  * x: [M,K] f32, y: [M,N] f32, DEVICE pointers. */
 int bitnet_b200_linear_f32(bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, const float* x,

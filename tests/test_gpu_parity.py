@@ -407,3 +407,76 @@ def test_concurrent_host_threads(b200, oracle):
     [t.start() for t in ts]
     [t.join() for t in ts]
     assert not errs, errs
+
+
+# =========================================================================================
+# the decode fast path: [RMSNorm ->] act-quant -> linear -> epilogue in one launch
+# (gemv_stream.cu). It must equal the composition of the pinned pieces bit for bit.
+# =========================================================================================
+def _silu_mul(g, u):
+    g = g.astype(np.float32)
+    return (g / (np.float32(1.0) + np.exp(-g, dtype=np.float32))) * u.astype(np.float32)
+
+
+@pytest.mark.parametrize("rows,cols", [(640, 2560), (3840, 2560), (2560, 6912), (512, 256), (100, 1024), (64, 4096)])
+@pytest.mark.parametrize("M", [1, 2, 3, 4])
+@pytest.mark.parametrize("norm", [True, False])
+def test_fused_linear_qk256(ctx, b200, oracle, rows, cols, M, norm):
+    qs = oracle.fill_bytes(rows * cols // 4, 0xB2000000 + rows + M)
+    x = oracle.fill_normal(M * cols, 77 + cols + M, 2.0).reshape(M, cols)
+    g = oracle.fill_uniform(cols, 78, 0.5, 1.5)
+    w = ctx.weight(qs, b200.LAYOUT_QK256, rows, cols)
+    y, q, s = ctx.fused_linear(w, dev(x), dev(g) if norm else None, 1e-5, want_q=True)
+    # the prologue is the two-step API's prologue, bit for bit
+    if norm:
+        q2, s2 = ctx.rmsnorm_actquant(dev(x), dev(g), 1e-5)
+    else:
+        q2, s2 = ctx.actquant_i8(dev(x))
+        rq, rs = oracle.quantize_rows_i8(x)
+        assert np.array_equal(q.cpu().numpy(), rq) and np.array_equal(s.cpu().numpy(), rs)
+    assert torch.equal(q, q2) and torch.equal(s, s2)
+    racc, ry = oracle.linear_qk256_i8(qs, rows, cols, q.cpu().numpy(), s.cpu().numpy())
+    assert np.array_equal(y.cpu().numpy(), ry)
+    # residual epilogue (in place) and SwiGLU epilogue
+    res = oracle.fill_normal(M * rows, 5).reshape(M, rows)
+    yr = dev(res)
+    ctx.fused_linear(w, dev(x), dev(g) if norm else None, 1e-5, epilogue=b200.EPI_RESIDUAL, y=yr, residual=yr)
+    assert np.array_equal(yr.cpu().numpy(), res + ry)
+    h = ctx.fused_linear(w, dev(x), dev(g) if norm else None, 1e-5, epilogue=b200.EPI_SWIGLU).cpu().numpy()
+    ref_h = _silu_mul(ry[:, 0::2], ry[:, 1::2])
+    assert h.shape == (M, rows // 2)
+    assert np.max(np.abs(h - ref_h)) <= 2e-6 * np.max(np.abs(ref_h))      # expf: device vs libm, <= 2 ulp
+
+
+@pytest.mark.parametrize("rows,cols", [(640, 2560), (2560, 6912), (64, 256)])
+@pytest.mark.parametrize("M", [1, 3])
+def test_fused_linear_bitnet32(ctx, b200, oracle, rows, cols, M):
+    data = oracle.make_bitnet32(rows, cols, 0xB2000000 + rows)
+    x = oracle.fill_normal(M * cols, 99 + rows, 2.0).reshape(M, cols)
+    g = oracle.fill_uniform(cols, 78, 0.5, 1.5)
+    w = ctx.weight(data, b200.LAYOUT_BITNET32_F16, rows, cols)
+    y, q, s = ctx.fused_linear(w, dev(x), dev(g), 1e-5, want_q=True)
+    q2, s2 = ctx.rmsnorm_actquant(dev(x), dev(g), 1e-5)
+    assert torch.equal(q, q2) and torch.equal(s, s2)
+    ry = oracle.linear_bitnet32_i8(data, rows, cols, q.cpu().numpy(), s.cpu().numpy())
+    assert _rel(y.cpu().numpy(), ry) < 1e-5
+    assert _rel(y.cpu().numpy(), oracle.linear_bitnet32_dequant(data, rows, cols, q.cpu().numpy(), s.cpu().numpy())) < 1e-3
+
+
+def test_fused_linear_edge_rows_and_errors(ctx, b200, oracle):
+    rows, cols = 64, 512
+    qs = oracle.fill_bytes(rows * cols // 4, 3)
+    w = ctx.weight(qs, b200.LAYOUT_QK256, rows, cols)
+    x = np.zeros((3, cols), np.float32)          # all-zero token -> scale 0 -> outputs 0
+    x[1, 7] = -3.0                                # single spike
+    x[2] = (np.arange(cols) % 255 - 127) * 0.5    # .5 rounding boundaries
+    y, q, s = ctx.fused_linear(w, dev(x), want_q=True)
+    rq, rs = oracle.quantize_rows_i8(x)
+    assert np.array_equal(q.cpu().numpy(), rq) and np.array_equal(s.cpu().numpy(), rs)
+    _, ry = oracle.linear_qk256_i8(qs, rows, cols, rq, rs)
+    assert np.array_equal(y.cpu().numpy(), ry) and not y[0].any().item()
+    with pytest.raises(b200.B200Error, match="1..4"):
+        ctx.fused_linear(w, torch.zeros(5, cols, device="cuda"))
+    w2 = ctx.weight(oracle.fill_bytes(4 * 128, 1), b200.LAYOUT_QK256, 4, 300)
+    with pytest.raises(b200.B200Error, match="not covered"):
+        ctx.fused_linear(w2, torch.zeros(1, 300, device="cuda"))
