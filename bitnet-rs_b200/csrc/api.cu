@@ -28,7 +28,7 @@ int fail_cuda(const char* what, cudaError_t e) {
 int launch_gemv_i8(const bitnet_b200_ctx*, const bitnet_b200_weight*, const int8_t*, const float*,
                    int, float*, int32_t*, const float* residual);
 int launch_gemv_f32(const bitnet_b200_ctx*, const bitnet_b200_weight*, const float*, int, float*);
-int launch_gemv_stream(const bitnet_b200_ctx*, const bitnet_b200_weight*, int M, int pro, const int8_t* q,
+int launch_gemv_fast(const bitnet_b200_ctx*, const bitnet_b200_weight*, int M, int pro, const int8_t* q,
                        const float* act_scale, const float* x, const float* gamma, float eps, int epi, float* y,
                        const float* residual, int32_t* acc_out, int8_t* q_out, float* scale_out, float* normed_out,
                        bool pdl);
@@ -390,8 +390,8 @@ int bitnet_b200_linear_i8(bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, con
     const bool force_gemv = acc_out && w->layout == BITNET_B200_LAYOUT_BITNET32_F16;
     if (!force_gemv && gemm_i8_supported(w, M))
         return launch_gemm_i8(ctx, w, q, act_scale, M, y, acc_out);
-    if (M <= 4 && !getenv("BITNET_B200_NO_STREAM")) {  // decode fast path (gemv_stream.cu); 1 = shape not covered
-        const int rc = launch_gemv_stream(ctx, w, M, /*PRO_Q8*/ 0, q, act_scale, nullptr, nullptr, 0.f, /*EPI_STORE*/ 0,
+    if (M <= 8 && !getenv("BITNET_B200_NO_STREAM")) {  // decode fast path (gemv_stream.cu); 1 = shape not covered
+        const int rc = launch_gemv_fast(ctx, w, M, /*PRO_Q8*/ 0, q, act_scale, nullptr, nullptr, 0.f, /*EPI_STORE*/ 0,
                                           y, nullptr, acc_out, nullptr, nullptr, nullptr,
                                           getenv("BITNET_B200_PDL_API") != nullptr);
         if (rc != 1) return rc;
@@ -403,13 +403,13 @@ int bitnet_b200_fused_linear(bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, 
                              const float* gamma, float eps, int M, int epilogue, float* y,
                              const float* residual, int8_t* q_out, float* scale_out) {
     if (!ctx || !w || !x || !y) return fail("fused_linear: NULL argument");
-    if (M <= 0 || M > 4) return fail("fused_linear: M must be in 1..4 (decode regime)");
+    if (M <= 0 || M > 8) return fail("fused_linear: M must be in 1..8 (decode regime)");
     if (epilogue < 0 || epilogue > 2) return fail("fused_linear: invalid epilogue");
     if (epilogue == BITNET_B200_EPI_RESIDUAL && !residual) return fail("fused_linear: residual is NULL");
     if (gamma && (!(eps > 0.f) || !isfinite(eps))) return fail("fused_linear: eps must be positive and finite");
     if (w->device != ctx->device) return fail("fused_linear: weight lives on another device");
     B200_CUDA(cudaSetDevice(ctx->device));
-    const int rc = launch_gemv_stream(ctx, w, M, gamma ? 2 : 1, nullptr, nullptr, x, gamma, eps, epilogue, y, residual,
+    const int rc = launch_gemv_fast(ctx, w, M, gamma ? 2 : 1, nullptr, nullptr, x, gamma, eps, epilogue, y, residual,
                                       nullptr, q_out, scale_out, nullptr, false);
     if (rc == 1) return fail("fused_linear: shape not covered by the streaming GEMV (need K % 64 == 0, BitNet32-F16 K % 256 == 0, aligned pointers)");
     return rc;

@@ -19,11 +19,11 @@
 namespace b200 {
 
 // gemv_stream.cu: 1 = shape unsupported (use the generic kernels), 0 = ok, -1 = error
-int launch_gemv_stream(const bitnet_b200_ctx*, const bitnet_b200_weight*, int M, int pro, const int8_t* q,
+int launch_gemv_fast(const bitnet_b200_ctx*, const bitnet_b200_weight*, int M, int pro, const int8_t* q,
                        const float* act_scale, const float* x, const float* gamma, float eps, int epi, float* y,
                        const float* residual, int32_t* acc_out, int8_t* q_out, float* scale_out, float* normed_out,
                        bool pdl);
-bool gemv_stream_supported(const bitnet_b200_ctx*, const bitnet_b200_weight*, int M, bool f32_prologue);
+bool gemv_fast_supported(const bitnet_b200_ctx*, const bitnet_b200_weight*, int M, bool f32_prologue);
 enum { PRO_Q8 = 0, PRO_F32 = 1, PRO_RMS = 2 };
 enum { EPI_STORE = 0, EPI_RESIDUAL = 1, EPI_SWIGLU = 2 };
 
@@ -331,11 +331,11 @@ static cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, siz
 
 static bool fused_supported(const bitnet_b200_model* m) {
     const auto& c = m->cfg;
-    if (c.batch > 4 || c.hidden % 8 || c.hidden / 8 > 1024 || c.head_dim > 256) return false;
+    if (c.batch > 8 || c.hidden % 8 || c.hidden / 8 > 1024 || c.head_dim > 256) return false;
     if (getenv("BITNET_B200_NO_FUSED")) return false;
     const LayerW& L = m->layers[0];
-    return gemv_stream_supported(m->ctx, L.wqkv, c.batch, true) && gemv_stream_supported(m->ctx, L.wo, c.batch, true) &&
-           gemv_stream_supported(m->ctx, L.wgateup, c.batch, true) && gemv_stream_supported(m->ctx, L.wdown, c.batch, true);
+    return gemv_fast_supported(m->ctx, L.wqkv, c.batch, true) && gemv_fast_supported(m->ctx, L.wo, c.batch, true) &&
+           gemv_fast_supported(m->ctx, L.wgateup, c.batch, true) && gemv_fast_supported(m->ctx, L.wdown, c.batch, true);
 }
 
 // The fused step: per layer  [RMSNorm+quant | qkv GEMV] -> [RoPE+KV append+attention] ->
@@ -352,19 +352,19 @@ static int enqueue_step_fused(bitnet_b200_model* m) {
     for (int l = 0; l < c.n_layers; ++l) {
         const LayerW& L = m->layers[(size_t)l];
         const size_t kvoff = (size_t)l * B * NKV * c.max_ctx * D;
-        if (launch_gemv_stream(ctx, L.wqkv, B, PRO_RMS, nullptr, nullptr, m->x, L.attn_norm, c.rms_eps, EPI_STORE,
+        if (launch_gemv_fast(ctx, L.wqkv, B, PRO_RMS, nullptr, nullptr, m->x, L.attn_norm, c.rms_eps, EPI_STORE,
                                m->qkv, nullptr, nullptr, nullptr, nullptr, nullptr, use_pdl()))
             return fail("fused decode: qkv projection rejected by the streaming GEMV");
         B200_CUDA(launch_pdl(attn_fused_kernel, dim3(NH, B), dim3(D), (size_t)c.max_ctx * 4, st, m->qkv, m->rope_cos,
                              m->rope_sin, m->kc + kvoff, m->vc + kvoff, m->att, m->pos, NH, NKV, D, c.max_ctx));
         count_launch();
-        if (launch_gemv_stream(ctx, L.wo, B, PRO_F32, nullptr, nullptr, m->att, nullptr, 0.f, EPI_RESIDUAL, m->x, m->x,
+        if (launch_gemv_fast(ctx, L.wo, B, PRO_F32, nullptr, nullptr, m->att, nullptr, 0.f, EPI_RESIDUAL, m->x, m->x,
                                nullptr, nullptr, nullptr, nullptr, use_pdl()))
             return fail("fused decode: o projection rejected by the streaming GEMV");
-        if (launch_gemv_stream(ctx, L.wgateup, B, PRO_RMS, nullptr, nullptr, m->x, L.ffn_norm, c.rms_eps, EPI_SWIGLU,
+        if (launch_gemv_fast(ctx, L.wgateup, B, PRO_RMS, nullptr, nullptr, m->x, L.ffn_norm, c.rms_eps, EPI_SWIGLU,
                                m->gu, nullptr, nullptr, nullptr, nullptr, nullptr, use_pdl()))
             return fail("fused decode: gate/up projection rejected by the streaming GEMV");
-        if (launch_gemv_stream(ctx, L.wdown, B, PRO_F32, nullptr, nullptr, m->gu, nullptr, 0.f, EPI_RESIDUAL, m->x, m->x,
+        if (launch_gemv_fast(ctx, L.wdown, B, PRO_F32, nullptr, nullptr, m->gu, nullptr, 0.f, EPI_RESIDUAL, m->x, m->x,
                                nullptr, nullptr, nullptr, nullptr, use_pdl()))
             return fail("fused decode: down projection rejected by the streaming GEMV");
     }
@@ -373,18 +373,25 @@ static int enqueue_step_fused(bitnet_b200_model* m) {
         const int rpc = (int)LOGITS_ROWS_PER_CTA;
         const int grid = (int)div_ceil((size_t)c.vocab, (size_t)rpc);
         const size_t smem = 2 * (size_t)(threads / 32) * 16 * 4;
-        cudaError_t e;
-        if (B == 1)
-            e = launch_pdl(logits_fused_kernel<1, 8>, dim3(grid), dim3(threads), smem, st, m->emb, m->x, m->final_norm,
-                           c.rms_eps, m->logits, m->part_val, m->part_idx, c.vocab, H, B, rpc);
-        else if (B == 2)
-            e = launch_pdl(logits_fused_kernel<2, 8>, dim3(grid), dim3(threads), smem, st, m->emb, m->x, m->final_norm,
-                           c.rms_eps, m->logits, m->part_val, m->part_idx, c.vocab, H, B, rpc);
-        else
-            e = launch_pdl(logits_fused_kernel<4, 4>, dim3(grid), dim3(threads), smem, st, m->emb, m->x, m->final_norm,
-                           c.rms_eps, m->logits, m->part_val, m->part_idx, c.vocab, H, B, rpc);
-        B200_CUDA(e);
-        count_launch();
+        for (int m0 = 0; m0 < B; m0 += 4) {
+            const int mc = B - m0 < 4 ? B - m0 : 4;
+            const float* xin = m->x + (size_t)m0 * H;
+            float* lo = m->logits + (size_t)m0 * c.vocab;
+            float* pv = m->part_val + (size_t)m0 * grid;
+            int* pi = m->part_idx + (size_t)m0 * grid;
+            cudaError_t e;
+            if (mc == 1)
+                e = launch_pdl(logits_fused_kernel<1, 8>, dim3(grid), dim3(threads), smem, st, m->emb, xin, m->final_norm,
+                               c.rms_eps, lo, pv, pi, c.vocab, H, mc, rpc);
+            else if (mc == 2)
+                e = launch_pdl(logits_fused_kernel<2, 8>, dim3(grid), dim3(threads), smem, st, m->emb, xin, m->final_norm,
+                               c.rms_eps, lo, pv, pi, c.vocab, H, mc, rpc);
+            else
+                e = launch_pdl(logits_fused_kernel<4, 4>, dim3(grid), dim3(threads), smem, st, m->emb, xin, m->final_norm,
+                               c.rms_eps, lo, pv, pi, c.vocab, H, mc, rpc);
+            B200_CUDA(e);
+            count_launch();
+        }
         B200_CUDA(launch_pdl(argmax_final_kernel, dim3(B), dim3(256), 0, st, m->part_val, m->part_idx, grid, m->next,
                              m->tokens, m->pos));
         count_launch();
@@ -704,7 +711,7 @@ int bitnet_b200_model_time_linears(bitnet_b200_model* m, int reps, float* ms_per
             for (int i = 0; i < 4 && !rc; ++i) {
                 int r = 1;
                 if (m->fused != 0)
-                    r = launch_gemv_stream(m->ctx, ws[i], B, PRO_Q8, m->q8, m->s8, nullptr, nullptr, 0.f, EPI_STORE,
+                    r = launch_gemv_fast(m->ctx, ws[i], B, PRO_Q8, m->q8, m->s8, nullptr, nullptr, 0.f, EPI_STORE,
                                            outs[i], nullptr, nullptr, nullptr, nullptr, nullptr, use_pdl());
                 if (r == 1) r = launch_gemv_i8(m->ctx, ws[i], m->q8, m->s8, B, outs[i], nullptr, nullptr);
                 rc = r;

@@ -269,16 +269,16 @@ __global__ void __launch_bounds__(MT >= 4 ? 512 : 1024) gemv_stream_kernel(const
             t1 = warp_sum(t1);
             if (lane == 0 && m < p.M) {
                 const float as = sc_s[m];
-                const float v0 = as * (float)t0, v1 = as * (float)t1;
+                const float v0 = __fmul_rn(as, (float)t0), v1 = __fmul_rn(as, (float)t1);  // no FMA contraction
                 const int row = row_begin + 2 * pr;
                 if (p.epi == EPI_SWIGLU) {
                     // rows (2i, 2i+1) = (gate_i, up_i): h_i = silu(gate) * up
-                    p.y[(size_t)m * (p.N / 2) + (row >> 1)] = (v0 / (1.0f + expf(-v0))) * v1;
+                    p.y[(size_t)m * (p.N / 2) + (row >> 1)] = __fmul_rn(v0 / (1.0f + expf(-v0)), v1);
                 } else {
                     const size_t oi = (size_t)m * p.N + row;
                     if (p.epi == EPI_RESIDUAL) {
-                        p.y[oi] = p.residual[oi] + v0;
-                        if (has1) p.y[oi + 1] = p.residual[oi + 1] + v1;
+                        p.y[oi] = __fadd_rn(p.residual[oi], v0);
+                        if (has1) p.y[oi + 1] = __fadd_rn(p.residual[oi + 1], v1);
                     } else {
                         p.y[oi] = v0;
                         if (has1) p.y[oi + 1] = v1;

@@ -419,7 +419,7 @@ def _silu_mul(g, u):
 
 
 @pytest.mark.parametrize("rows,cols", [(640, 2560), (3840, 2560), (2560, 6912), (512, 256), (100, 1024), (64, 4096)])
-@pytest.mark.parametrize("M", [1, 2, 3, 4])
+@pytest.mark.parametrize("M", [1, 2, 3, 4, 5, 8])
 @pytest.mark.parametrize("norm", [True, False])
 def test_fused_linear_qk256(ctx, b200, oracle, rows, cols, M, norm):
     qs = oracle.fill_bytes(rows * cols // 4, 0xB2000000 + rows + M)
@@ -475,8 +475,8 @@ def test_fused_linear_edge_rows_and_errors(ctx, b200, oracle):
     assert np.array_equal(q.cpu().numpy(), rq) and np.array_equal(s.cpu().numpy(), rs)
     _, ry = oracle.linear_qk256_i8(qs, rows, cols, rq, rs)
     assert np.array_equal(y.cpu().numpy(), ry) and not y[0].any().item()
-    with pytest.raises(b200.B200Error, match="1..4"):
-        ctx.fused_linear(w, torch.zeros(5, cols, device="cuda"))
+    with pytest.raises(b200.B200Error, match="1..8"):
+        ctx.fused_linear(w, torch.zeros(9, cols, device="cuda"))
     w2 = ctx.weight(oracle.fill_bytes(4 * 128, 1), b200.LAYOUT_QK256, 4, 300)
     with pytest.raises(b200.B200Error, match="not covered"):
         ctx.fused_linear(w2, torch.zeros(1, 300, device="cuda"))
