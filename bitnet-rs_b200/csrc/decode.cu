@@ -306,6 +306,8 @@ struct CaptureStream {
 };
 
 constexpr size_t LOGITS_ROWS_PER_CTA = 64;
+// scores [max_ctx] + value partials [ATTN_THREADS / (D/4)][D] = ATTN_THREADS float4
+static size_t attn_fused_smem(int max_ctx) { return (((size_t)max_ctx + 3) & ~(size_t)3) * 4 + (size_t)ATTN_THREADS * 16; }
 
 // BITNET_B200_NO_PDL=1 launches the same kernels with ordinary stream serialisation
 static bool use_pdl() {
@@ -347,24 +349,27 @@ static int enqueue_step_fused(bitnet_b200_model* m) {
     cudaStream_t st = ctx->stream;
     const int B = c.batch, H = c.hidden, D = c.head_dim, NH = c.n_heads, NKV = c.n_kv_heads;
     const uint64_t l0 = g_launches.load();
+    // timing diagnostics only (results are wrong when set): bit 0 attention, 1 logits, 2 qkv, 3 o, 4 gate/up, 5 down
+    const int skip = getenv("BITNET_B200_DIAG_SKIP") ? atoi(getenv("BITNET_B200_DIAG_SKIP")) : 0;
     B200_CUDA(launch_pdl(embed_pdl_kernel, dim3(B), dim3(256), 0, st, m->emb, m->tokens, m->x, H));
     count_launch();
     for (int l = 0; l < c.n_layers; ++l) {
         const LayerW& L = m->layers[(size_t)l];
         const size_t kvoff = (size_t)l * B * NKV * c.max_ctx * D;
-        if (launch_gemv_fast(ctx, L.wqkv, B, PRO_RMS, nullptr, nullptr, m->x, L.attn_norm, c.rms_eps, EPI_STORE,
+        if (!(skip & 4) && launch_gemv_fast(ctx, L.wqkv, B, PRO_RMS, nullptr, nullptr, m->x, L.attn_norm, c.rms_eps, EPI_STORE,
                                m->qkv, nullptr, nullptr, nullptr, nullptr, nullptr, use_pdl()))
             return fail("fused decode: qkv projection rejected by the streaming GEMV");
-        B200_CUDA(launch_pdl(attn_fused_kernel, dim3(NH, B), dim3(D), (size_t)c.max_ctx * 4, st, m->qkv, m->rope_cos,
+        if (!(skip & 1))
+        B200_CUDA(launch_pdl(attn_fused_kernel, dim3(NH, B), dim3(ATTN_THREADS), attn_fused_smem(c.max_ctx), st, m->qkv, m->rope_cos,
                              m->rope_sin, m->kc + kvoff, m->vc + kvoff, m->att, m->pos, NH, NKV, D, c.max_ctx));
         count_launch();
-        if (launch_gemv_fast(ctx, L.wo, B, PRO_F32, nullptr, nullptr, m->att, nullptr, 0.f, EPI_RESIDUAL, m->x, m->x,
+        if (!(skip & 8) && launch_gemv_fast(ctx, L.wo, B, PRO_F32, nullptr, nullptr, m->att, nullptr, 0.f, EPI_RESIDUAL, m->x, m->x,
                                nullptr, nullptr, nullptr, nullptr, use_pdl()))
             return fail("fused decode: o projection rejected by the streaming GEMV");
-        if (launch_gemv_fast(ctx, L.wgateup, B, PRO_RMS, nullptr, nullptr, m->x, L.ffn_norm, c.rms_eps, EPI_SWIGLU,
+        if (!(skip & 16) && launch_gemv_fast(ctx, L.wgateup, B, PRO_RMS, nullptr, nullptr, m->x, L.ffn_norm, c.rms_eps, EPI_SWIGLU,
                                m->gu, nullptr, nullptr, nullptr, nullptr, nullptr, use_pdl()))
             return fail("fused decode: gate/up projection rejected by the streaming GEMV");
-        if (launch_gemv_fast(ctx, L.wdown, B, PRO_F32, nullptr, nullptr, m->gu, nullptr, 0.f, EPI_RESIDUAL, m->x, m->x,
+        if (!(skip & 32) && launch_gemv_fast(ctx, L.wdown, B, PRO_F32, nullptr, nullptr, m->gu, nullptr, 0.f, EPI_RESIDUAL, m->x, m->x,
                                nullptr, nullptr, nullptr, nullptr, use_pdl()))
             return fail("fused decode: down projection rejected by the streaming GEMV");
     }
@@ -373,7 +378,7 @@ static int enqueue_step_fused(bitnet_b200_model* m) {
         const int rpc = (int)LOGITS_ROWS_PER_CTA;
         const int grid = (int)div_ceil((size_t)c.vocab, (size_t)rpc);
         const size_t smem = 2 * (size_t)(threads / 32) * 16 * 4;
-        for (int m0 = 0; m0 < B; m0 += 4) {
+        for (int m0 = 0; m0 < B && !(skip & 2); m0 += 4) {
             const int mc = B - m0 < 4 ? B - m0 : 4;
             const float* xin = m->x + (size_t)m0 * H;
             float* lo = m->logits + (size_t)m0 * c.vocab;
@@ -392,9 +397,11 @@ static int enqueue_step_fused(bitnet_b200_model* m) {
             B200_CUDA(e);
             count_launch();
         }
-        B200_CUDA(launch_pdl(argmax_final_kernel, dim3(B), dim3(256), 0, st, m->part_val, m->part_idx, grid, m->next,
-                             m->tokens, m->pos));
-        count_launch();
+        if (!(skip & 2)) {
+            B200_CUDA(launch_pdl(argmax_final_kernel, dim3(B), dim3(256), 0, st, m->part_val, m->part_idx, grid, m->next,
+                                 m->tokens, m->pos));
+            count_launch();
+        }
     }
     m->launches_per_step = g_launches.load() - l0;
     return 0;
@@ -460,10 +467,11 @@ static int ensure_graph(bitnet_b200_model* m) {
     if (!m->have_emb || !m->have_rope || m->layers_set != m->cfg.n_layers)
         return fail("model: weights incomplete (set every layer, the embedding and the RoPE tables first)");
     const int smem = m->cfg.max_ctx * 4;
-    if (smem > 48 * 1024) {
+    if (smem > 48 * 1024)
         B200_CUDA(cudaFuncSetAttribute(attn_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        B200_CUDA(cudaFuncSetAttribute(attn_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    }
+    if (attn_fused_smem(m->cfg.max_ctx) > 48 * 1024)
+        B200_CUDA(cudaFuncSetAttribute(attn_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)attn_fused_smem(m->cfg.max_ctx)));
     // capture on a private stream (the legacy default stream cannot be captured), then the
     // instantiated graph is launched on the context's stream
     CaptureStream cap(m->ctx);
@@ -498,7 +506,7 @@ int bitnet_b200_model_create(bitnet_b200_ctx* ctx, const bitnet_b200_model_confi
         if (c.n_heads % c.n_kv_heads) return fail("model_create: n_heads must be a multiple of n_kv_heads");
         if (c.head_dim % 64 || c.head_dim > 256) return fail("model_create: head_dim must be 64, 128, 192 or 256");
         if (c.hidden % 32 || c.ffn % 32 || c.hidden % 8) return fail("model_create: hidden and ffn must be multiples of 32");
-        if ((size_t)c.max_ctx * 4 > 200 * 1024) return fail("model_create: max_ctx too large for the decode attention kernel");
+        if ((size_t)c.max_ctx * 4 > 190 * 1024) return fail("model_create: max_ctx too large for the decode attention kernel");
         B200_CUDA(cudaSetDevice(ctx->device));
         std::unique_ptr<bitnet_b200_model, void (*)(bitnet_b200_model*)> m(new bitnet_b200_model(),
                                                                           bitnet_b200_model_destroy);

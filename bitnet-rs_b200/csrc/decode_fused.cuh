@@ -17,14 +17,18 @@ __global__ void embed_pdl_kernel(const __half* __restrict__ emb, const int* __re
 
 // RoPE (split-half, crates/bitnet-transformer/src/lib.rs:134-184) on q and on the new k, KV-cache
 // append (:1171-1202), GQA decode attention (:374-540): one CTA per (query head, sequence),
-// D threads. The first head of each KV group appends k/v to the cache; every head takes the
-// freshly rotated k / v of position `pos` from shared memory, so no CTA reads a cache line
-// that another CTA of this launch writes.
-__global__ void attn_fused_kernel(const float* __restrict__ qkv, const float* __restrict__ cos_t,
-                                  const float* __restrict__ sin_t, float* __restrict__ kc,
-                                  float* __restrict__ vc, float* __restrict__ att,
-                                  const int* __restrict__ pos_p, int NH, int NKV, int D, int max_ctx) {
-    extern __shared__ float sc[];  // [max_ctx]
+// ATTN_THREADS threads. The first head of each KV group appends k/v to the cache; every head
+// takes the freshly rotated k / v of position `pos` from shared memory, so no CTA reads a cache
+// line that another CTA of this launch writes.
+// Latency-shaped, not bandwidth-shaped (a decode step at short context is a chain of ~150
+// dependent launches): positions are spread over all 16 warps and every thread keeps four
+// independent cache loads in flight, in both the score pass and the value pass.
+constexpr int ATTN_THREADS = 512;
+__global__ void __launch_bounds__(ATTN_THREADS) attn_fused_kernel(
+    const float* __restrict__ qkv, const float* __restrict__ cos_t, const float* __restrict__ sin_t,
+    float* __restrict__ kc, float* __restrict__ vc, float* __restrict__ att, const int* __restrict__ pos_p, int NH,
+    int NKV, int D, int max_ctx) {
+    extern __shared__ __align__(16) float sc[];  // [max_ctx] scores, then [PG][D] value partials
     __shared__ float qs[256], ks[256], vs[256];
     __shared__ float red[32];
     pdl_launch_dependents();
@@ -61,18 +65,34 @@ __global__ void attn_fused_kernel(const float* __restrict__ qkv, const float* __
     float qr[8];
     const int per = D / 32;
     for (int j = 0; j < per; ++j) qr[j] = qs[lane + 32 * j];
+    // ---- scores: warp w takes positions w, w + nwarps, ...; four positions in flight --------
     float mx = -INFINITY;
-    for (int p = warp; p <= pos; p += nwarps) {
-        float d = 0.f;
-        if (p == pos) {
-            for (int j = 0; j < per; ++j) d = fmaf(qr[j], ks[lane + 32 * j], d);
-        } else {
-            const float* kp = kb + (size_t)p * D;
-            for (int j = 0; j < per; ++j) d = fmaf(qr[j], kp[lane + 32 * j], d);
+    for (int p0 = warp; p0 <= pos; p0 += 4 * nwarps) {
+        float d[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int p = p0 + u * nwarps;
+            d[u] = 0.f;
+            if (p < pos) {
+                const float* kp = kb + (size_t)p * D;
+                for (int j = 0; j < per; ++j) d[u] = fmaf(qr[j], __ldg(kp + lane + 32 * j), d[u]);
+            } else if (p == pos) {
+                for (int j = 0; j < per; ++j) d[u] = fmaf(qr[j], ks[lane + 32 * j], d[u]);
+            }
         }
-        d = warp_sum(d) * scale;
-        if (lane == 0) sc[p] = d;
-        mx = fmaxf(mx, d);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+            for (int u = 0; u < 4; ++u) d[u] += __shfl_xor_sync(0xffffffffu, d[u], o);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int p = p0 + u * nwarps;
+            if (p <= pos) {
+                const float v = d[u] * scale;
+                if (lane == 0) sc[p] = v;
+                mx = fmaxf(mx, v);
+            }
+        }
     }
     if (lane == 0) red[warp] = mx;
     __syncthreads();
@@ -91,11 +111,53 @@ __global__ void attn_fused_kernel(const float* __restrict__ qkv, const float* __
     sum = 0.f;
     for (int w = 0; w < nwarps; ++w) sum += red[w];
     const float inv = 1.0f / sum;
-    for (int d = tid; d < D; d += blockDim.x) {
-        float a = 0.f;
-        for (int p = 0; p < pos; ++p) a = fmaf(sc[p] * inv, vb[(size_t)p * D + d], a);
-        a = fmaf(sc[pos] * inv, vs[d], a);
-        att[((size_t)b * NH + head) * D + d] = a;
+    // ---- values: thread = (position group pg, float4 column dc); partial sums meet in smem ---
+    const int ncol = D / 4, PG = blockDim.x / ncol;
+    const int dc = tid % ncol, pg = tid / ncol;
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (pg < PG) {
+        for (int p0 = pg; p0 < pos; p0 += 4 * PG) {
+            float4 v[4];
+            float w[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int p = p0 + u * PG;
+                v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                w[u] = 0.f;
+                if (p < pos) {
+                    v[u] = __ldg(reinterpret_cast<const float4*>(vb + (size_t)p * D) + dc);
+                    w[u] = sc[p] * inv;
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                a.x = fmaf(w[u], v[u].x, a.x);
+                a.y = fmaf(w[u], v[u].y, a.y);
+                a.z = fmaf(w[u], v[u].z, a.z);
+                a.w = fmaf(w[u], v[u].w, a.w);
+            }
+        }
+    }
+    const float wl = sc[pos] * inv;
+    __syncthreads();  // all reads of sc[] done: reuse it for the partials
+    float4* part = reinterpret_cast<float4*>(sc + ((max_ctx + 3) & ~3));
+    if (pg < PG) part[pg * ncol + dc] = a;
+    __syncthreads();
+    if (tid < ncol) {
+        float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int i = 0; i < PG; ++i) {
+            const float4 v = part[i * ncol + tid];
+            t.x += v.x;
+            t.y += v.y;
+            t.z += v.z;
+            t.w += v.w;
+        }
+        const float4 vl = reinterpret_cast<const float4*>(vs)[tid];
+        t.x = fmaf(wl, vl.x, t.x);
+        t.y = fmaf(wl, vl.y, t.y);
+        t.z = fmaf(wl, vl.z, t.z);
+        t.w = fmaf(wl, vl.w, t.w);
+        reinterpret_cast<float4*>(att + ((size_t)b * NH + head) * D)[tid] = t;
     }
 }
 

@@ -1,0 +1,805 @@
+// decode_mega.cu -- one decode step of a 2B-4T-shaped ternary decoder as ONE persistent,
+// cooperative kernel (QK256 layout, batch <= 4): one CTA per SM, a dedicated producer warp that
+// streams EVERY packed weight of the step (and the f16 LM head) through a shared-memory ring with
+// 1-D bulk copies (TMA, cp.async.bulk -> mbarrier) and never stops at a phase boundary, and 16
+// consumer warps that run the phases
+//     embed | per layer: [RMSNorm+act-quant | qkv GEMV] -> [RoPE + KV append + GQA attention]
+//     -> [act-quant | o GEMV + residual] -> [RMSNorm+act-quant | gate/up GEMV | SwiGLU]
+//     -> [act-quant | down GEMV + residual] | final RMSNorm + LM head + argmax
+// separated by grid-wide barriers (one global counter, red.release / ld.acquire).
+//
+// Why: at batch 1 a 2B-4T projection is 0.25-1.4 us of HBM time, below any launch or barrier
+// latency, so a chain of per-projection kernels is latency-bound with the memory pipe idle most
+// of the time (measured: 4.3-12 us per projection launch). Here the weight stream is decoupled
+// from the dependency chain: while the consumers sit in a grid barrier or in the activation
+// prologue of phase p, the producer is already filling the ring with the tiles of phase p+1,
+// p+2, ... (up to ~1.3 layers ahead across the 148 SMs).
+//
+// Hot-path arithmetic is that of gemv_mma.cu: 2-bit codes -> 4-entry int8 LUT (PRMT) -> A fragment
+// of mma.sync.m16n8k32.s8, int8 activations as the B fragment, int32 accumulation (exact;
+// bit-identical to gemv_qk256 on integer inputs, crates/bitnet-quantization/src/i2s_qk256.rs:
+// 346-372), per-token absmax int8 quantiser (cpu/quantize.rs:32-49) and cpu::rms_norm
+// (cpu/layer_norm.rs:118-137) in the prologue. Cross-warp partial sums meet through int32
+// shared-memory atomics: integer addition is associative, so the result is order-independent.
+#include "common.cuh"
+
+namespace b200 {
+
+constexpr int MEGA_NW = 16;                         // consumer warps
+constexpr int MEGA_CONS = MEGA_NW * 32;             // consumer threads
+constexpr int MEGA_THREADS = MEGA_CONS + 32;        // + the producer warp
+constexpr int MEGA_SLOT_STEPS = 16;                 // 256-column steps per ring slot
+constexpr int MEGA_SLOT_BYTES = 16 * MEGA_SLOT_STEPS * 64;  // 16 rows x 16 steps x 64 B
+constexpr int MEGA_MAX_TILES = 16;                  // 16-row tiles per CTA per phase
+constexpr int MEGA_MAXB = 4;                        // tokens per step
+constexpr int MEGA_MAX_SLOTS = 12;
+constexpr int MEGA_MAX_LAYERS = 64;
+
+struct MegaLayer {
+    const uint8_t *wqkv, *wo, *wgu, *wdown;  // device-layout code planes [N, K/4]
+    const float *attn_norm, *ffn_norm;
+};
+
+struct MegaParams {
+    const MegaLayer* layers;
+    const __half* emb;
+    const float *final_norm, *rope_cos, *rope_sin;
+    float *kc, *vc;
+    int *pos, *tokens, *next;
+    float *x, *qkv, *att, *gu, *logits, *part_val;
+    int* part_idx;
+    const int8_t* q_fixed;   // mode 1: fixed int8 rows [B, max(H, F, NH*D)]
+    const float* s_fixed;    // mode 1: their scales
+    unsigned* bar;           // [2] grid-barrier counters, used alternately per launch
+    int parity;
+    int L, B, H, F, NH, NKV, D, V, max_ctx;
+    float eps;
+    uint32_t lut;
+    int mode;                // 0 = full decode step; 1 = the 4L ternary GEMVs only, no dependencies
+    int n_slots, act_bytes, attn_floats;
+};
+
+// ---- small PTX helpers ------------------------------------------------------------------------
+__device__ __forceinline__ void cons_sync() { asm volatile("bar.sync 1, %0;" ::"n"(MEGA_CONS) : "memory"); }
+__device__ __forceinline__ float ld_cg_f32(const float* p) {
+    float v;
+    asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(v) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ float4 ld_cg_f32x4(const float* p) {
+    float4 v;
+    asm volatile("ld.global.cg.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ int ld_cg_s32(const int* p) {
+    int v;
+    asm volatile("ld.global.cg.s32 %0, [%1];" : "=r"(v) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ void mma_s8_m16n8k32(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
+                                                uint32_t b0, uint32_t b1) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k32.row.col.s32.s8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3])
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+// q = clamp(round_half_away(v * inv), -127, 127); NaN -> 0 (Rust `as i8`)
+__device__ __forceinline__ int mega_quant_i8(float v, float inv) {
+    float r = roundf(v * inv);
+    if (r != r) return 0;
+    r = fminf(fmaxf(r, -127.f), 127.f);
+    return (int)r;
+}
+
+// Grid-wide barrier over the consumer threads of all CTAs (the kernel is launched cooperatively,
+// so all CTAs are resident). Bounded spin: a lost arrival traps instead of hanging the GPU.
+__device__ __forceinline__ void grid_sync(unsigned* ctr, unsigned& target, unsigned ncta) {
+    target += ncta;
+    cons_sync();
+    if (threadIdx.x == 0) {
+        asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(ctr) : "memory");
+        unsigned v;
+        uint32_t it = 0;
+        do {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
+            if (++it > (1u << 23)) __trap();
+        } while (v < target);
+    }
+    cons_sync();
+}
+
+// split `ns` 256-column steps into `nch` nearly equal chunks; chunk c = steps [s0, s0 + cs)
+__device__ __forceinline__ void chunk_range(int ns, int nch, int c, int& s0, int& cs) {
+    const int base = ns / nch, rem = ns - base * nch;
+    s0 = c * base + (c < rem ? c : rem);
+    cs = base + (c < rem ? 1 : 0);
+}
+
+struct MegaSmem {
+    uint64_t* full;    // [n_slots]
+    uint64_t* empty;   // [n_slots]
+    double* shd;       // [32]
+    float* shf;        // [32]
+    float* sc_s;       // [MEGA_MAXB]
+    float* bestv;      // [MEGA_NW * MEGA_MAXB]
+    int* besti;        // [MEGA_NW * MEGA_MAXB]
+    MegaLayer* layers; // [L]
+    int* acc;          // [MEGA_MAX_TILES][16][8]
+    unsigned char* act;  // int8 rows [B][K + 64]  or  f32 rows [B][H]
+    float* attn;       // scores [max_ctx] | value partials [512 float4] | q,k,v rows [3][256]
+    unsigned char* ring;
+};
+
+// ---- activation prologue: f32 rows -> (optional RMSNorm) -> int8 rows + scale in shared memory ---
+// pro: 0 = copy the fixed int8 rows (mode 1), 1 = absmax int8 quantise, 2 = RMSNorm then quantise
+__device__ __forceinline__ void mega_prologue(const MegaParams& p, const MegaSmem& sm, int pro, const float* xin,
+                                              const float* gamma, int K, int q_ld) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    int8_t* qbuf = reinterpret_cast<int8_t*>(sm.act);
+    if (pro == 0) {
+        const int vpr = K / 16;
+        for (int i = tid; i < p.B * vpr; i += MEGA_CONS) {
+            const int m = i / vpr, v = i - m * vpr;
+            *reinterpret_cast<uint4*>(qbuf + m * q_ld + v * 16) =
+                *reinterpret_cast<const uint4*>(p.q_fixed + (size_t)m * K + v * 16);
+        }
+        if (tid < p.B) sm.sc_s[tid] = p.s_fixed[tid];
+        cons_sync();
+        return;
+    }
+    constexpr int NV = 4;  // float4 per thread: K <= 16 * MEGA_CONS = 8192 per pass
+    const int ngrp = K / 4;
+    for (int m = 0; m < p.B; ++m) {
+        for (int g0 = 0; g0 < ngrp; g0 += NV * MEGA_CONS) {  // one pass for K <= 8192
+            // (K > 8192 takes several passes over a row: the reductions below are then per pass,
+            //  which is wrong -- the host only selects this kernel when K <= 8192.)
+            float4 v[NV];
+#pragma unroll
+            for (int j = 0; j < NV; ++j) {
+                const int g = g0 + tid + j * MEGA_CONS;
+                v[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (g < ngrp) v[j] = ld_cg_f32x4(xin + (size_t)m * K + 4 * g);
+            }
+            if (pro == 2) {
+                double ss = 0.0;
+#pragma unroll
+                for (int j = 0; j < NV; ++j)
+                    ss += (double)v[j].x * (double)v[j].x + (double)v[j].y * (double)v[j].y +
+                          (double)v[j].z * (double)v[j].z + (double)v[j].w * (double)v[j].w;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+                if (lane == 0) sm.shd[warp] = ss;
+                cons_sync();
+                double tot = 0.0;
+#pragma unroll
+                for (int wv = 0; wv < MEGA_NW; ++wv) tot += sm.shd[wv];
+                const float ms = (float)(tot / (double)K);
+                const float inv_rms = 1.0f / sqrtf(ms + p.eps);
+#pragma unroll
+                for (int j = 0; j < NV; ++j) {
+                    const int g = g0 + tid + j * MEGA_CONS;
+                    if (g < ngrp) {
+                        const float4 gm = __ldg(reinterpret_cast<const float4*>(gamma) + g);
+                        v[j].x = v[j].x * inv_rms * gm.x;
+                        v[j].y = v[j].y * inv_rms * gm.y;
+                        v[j].z = v[j].z * inv_rms * gm.z;
+                        v[j].w = v[j].w * inv_rms * gm.w;
+                    }
+                }
+            }
+            float amax = 0.f;
+#pragma unroll
+            for (int j = 0; j < NV; ++j)
+                amax = fmaxf(amax, fmaxf(fmaxf(fabsf(v[j].x), fabsf(v[j].y)), fmaxf(fabsf(v[j].z), fabsf(v[j].w))));
+            amax = warp_max(amax);
+            if (lane == 0) sm.shf[warp] = amax;
+            cons_sync();
+            amax = 0.f;
+#pragma unroll
+            for (int wv = 0; wv < MEGA_NW; ++wv) amax = fmaxf(amax, sm.shf[wv]);
+            const float sc = amax == 0.f ? 0.f : amax / 127.f;
+            const float inv = amax == 0.f ? 0.f : 1.0f / sc;
+            if (tid == 0) sm.sc_s[m] = sc;
+#pragma unroll
+            for (int j = 0; j < NV; ++j) {
+                const int g = g0 + tid + j * MEGA_CONS;
+                if (g < ngrp) {
+                    uint32_t wq = 0;
+                    if (amax != 0.f)
+                        wq = (uint32_t)(uint8_t)mega_quant_i8(v[j].x, inv) | ((uint32_t)(uint8_t)mega_quant_i8(v[j].y, inv) << 8) |
+                             ((uint32_t)(uint8_t)mega_quant_i8(v[j].z, inv) << 16) |
+                             ((uint32_t)(uint8_t)mega_quant_i8(v[j].w, inv) << 24);
+                    reinterpret_cast<uint32_t*>(qbuf + m * q_ld)[g] = wq;
+                }
+            }
+            cons_sync();  // shd/shf reusable; qbuf + sc_s visible
+        }
+    }
+}
+
+// ---- one ternary GEMV phase (consumer side) ------------------------------------------------------
+// epi: 0 store, 1 residual add (out may alias resid), 2 SwiGLU on interleaved (gate, up) rows
+__device__ __forceinline__ void mega_gemv_phase(const MegaParams& p, const MegaSmem& sm, const uint8_t* /*w*/, int N, int K,
+                                                int pro, const float* xin, const float* gamma, int epi, float* out,
+                                                const float* resid, uint32_t& n, int& tcount) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g = lane >> 2, t = lane & 3;
+    const int G = gridDim.x, cta = blockIdx.x;
+    const int NT = (N + 15) >> 4, ns = K >> 8, nch = (ns + MEGA_SLOT_STEPS - 1) / MEGA_SLOT_STEPS;
+    const int q_ld = K + 64;
+    const int first = (cta - tcount + G) % G;
+    for (int i = tid; i < MEGA_MAX_TILES * 128; i += MEGA_CONS) sm.acc[i] = 0;
+    mega_prologue(p, sm, pro, xin, gamma, K, q_ld);  // ends with a consumer barrier
+
+    const bool tok = g < p.B;
+    const int8_t* qrow = reinterpret_cast<const int8_t*>(sm.act) + g * q_ld + 64 * t;
+    int nloc = 0;
+    for (int tile = first; tile < NT; tile += G, ++nloc) {
+        int c[4] = {0, 0, 0, 0};
+        bool have = false;
+        for (int ch = 0; ch < nch; ++ch, ++n) {
+            int s0, cs;
+            chunk_range(ns, nch, ch, s0, cs);
+            const uint32_t slot = n % (uint32_t)p.n_slots;
+            mbar_wait(&sm.full[slot], (n / (uint32_t)p.n_slots) & 1u);
+            const unsigned char* base = sm.ring + (size_t)slot * MEGA_SLOT_BYTES;
+            const int rowb = cs * 64;
+            // warp w takes the steps with (tile-local step index) == w (mod MEGA_NW), offset per tile
+            int s = s0 + ((warp - (nloc * ns + s0)) % MEGA_NW + MEGA_NW) % MEGA_NW;
+            for (; s < s0 + cs; s += MEGA_NW) {
+                const unsigned char* wr = base + (size_t)g * rowb + (s - s0) * 64 + 16 * t;
+                const uint4 wg = *reinterpret_cast<const uint4*>(wr);
+                const uint4 wh = *reinterpret_cast<const uint4*>(wr + 8 * rowb);
+                const uint32_t wgs[4] = {wg.x, wg.y, wg.z, wg.w};
+                const uint32_t whs[4] = {wh.x, wh.y, wh.z, wh.w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    uint4 b = make_uint4(0, 0, 0, 0);
+                    if (tok) b = *reinterpret_cast<const uint4*>(qrow + s * 256 + 16 * j);
+                    const uint4 dg = decode16(wgs[j], p.lut);
+                    const uint4 dh = decode16(whs[j], p.lut);
+                    mma_s8_m16n8k32(c, dg.x, dh.x, dg.y, dh.y, b.x, b.y);
+                    mma_s8_m16n8k32(c, dg.z, dh.z, dg.w, dh.w, b.z, b.w);
+                }
+                have = true;
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&sm.empty[slot]);
+        }
+        if (have) {
+            // lane (g, t): c[0] (row g, token 2t), c[1] (row g, 2t+1), c[2] (row g+8, 2t), c[3] (row g+8, 2t+1)
+            int* a = sm.acc + nloc * 128;
+            if (2 * t < p.B) {
+                atomicAdd(a + g * 8 + 2 * t, c[0]);
+                atomicAdd(a + (g + 8) * 8 + 2 * t, c[2]);
+            }
+            if (2 * t + 1 < p.B) {
+                atomicAdd(a + g * 8 + 2 * t + 1, c[1]);
+                atomicAdd(a + (g + 8) * 8 + 2 * t + 1, c[3]);
+            }
+        }
+    }
+    cons_sync();
+    // ---- epilogue ---------------------------------------------------------------------------
+    if (epi == 2) {
+        const int half = N >> 1;
+        for (int e = tid; e < nloc * 8 * p.B; e += MEGA_CONS) {
+            const int m = e / (nloc * 8), rr = e - m * (nloc * 8), i = rr >> 3, j = rr & 7;
+            const int row = (first + i * G) * 16 + 2 * j;
+            if (row + 1 < N) {
+                const float as = sm.sc_s[m];
+                const float v0 = __fmul_rn(as, (float)sm.acc[i * 128 + (2 * j) * 8 + m]);
+                const float v1 = __fmul_rn(as, (float)sm.acc[i * 128 + (2 * j + 1) * 8 + m]);
+                out[(size_t)m * half + (row >> 1)] = __fmul_rn(v0 / (1.0f + expf(-v0)), v1);
+            }
+        }
+    } else {
+        for (int e = tid; e < nloc * 16 * p.B; e += MEGA_CONS) {
+            const int m = e / (nloc * 16), rr = e - m * (nloc * 16), i = rr >> 4, r = rr & 15;
+            const int row = (first + i * G) * 16 + r;
+            if (row < N) {
+                const float v = __fmul_rn(sm.sc_s[m], (float)sm.acc[i * 128 + r * 8 + m]);
+                const size_t oi = (size_t)m * N + row;
+                out[oi] = epi == 1 ? __fadd_rn(ld_cg_f32(resid + oi), v) : v;
+            }
+        }
+    }
+    tcount = (tcount + NT) % G;
+}
+
+// ---- RoPE + KV append + GQA decode attention for one (head, sequence); consumer threads only ---
+// (crates/bitnet-transformer/src/lib.rs:134-184, 374-540, 1171-1202; same arithmetic as
+// attn_fused_kernel in decode_fused.cuh)
+__device__ __forceinline__ void mega_attention(const MegaParams& p, const MegaSmem& sm, int head, int b, int pos,
+                                               float* kc, float* vc) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int D = p.D, NH = p.NH, NKV = p.NKV, half = D / 2, max_ctx = p.max_ctx;
+    float* sc = sm.attn;
+    float4* part = reinterpret_cast<float4*>(sm.attn + ((max_ctx + 3) & ~3));
+    float* qs = reinterpret_cast<float*>(part + MEGA_CONS);
+    float* ks = qs + 256;
+    float* vs = ks + 256;
+    const int group = NH / NKV, g = head / group;
+    const float* row = p.qkv + (size_t)b * (NH + 2 * NKV) * D;
+    float* kb = kc + ((size_t)b * NKV + g) * max_ctx * D;
+    float* vb = vc + ((size_t)b * NKV + g) * max_ctx * D;
+    if (tid < half) {
+        const float c = __ldg(p.rope_cos + (size_t)pos * half + tid), s = __ldg(p.rope_sin + (size_t)pos * half + tid);
+        const float* qh = row + (size_t)head * D;
+        const float* kh = row + (size_t)(NH + g) * D;
+        const float* vh = row + (size_t)(NH + NKV + g) * D;
+        const float qa = ld_cg_f32(qh + tid), qb = ld_cg_f32(qh + tid + half);
+        const float ka = ld_cg_f32(kh + tid), kbv = ld_cg_f32(kh + tid + half);
+        qs[tid] = qa * c - qb * s;
+        qs[tid + half] = qa * s + qb * c;
+        const float k0 = ka * c - kbv * s, k1 = ka * s + kbv * c;
+        ks[tid] = k0;
+        ks[tid + half] = k1;
+        const float v0 = ld_cg_f32(vh + tid), v1 = ld_cg_f32(vh + tid + half);
+        vs[tid] = v0;
+        vs[tid + half] = v1;
+        if (head % group == 0) {
+            kb[(size_t)pos * D + tid] = k0;
+            kb[(size_t)pos * D + tid + half] = k1;
+            vb[(size_t)pos * D + tid] = v0;
+            vb[(size_t)pos * D + tid + half] = v1;
+        }
+    }
+    cons_sync();
+    const float scale = 1.0f / sqrtf((float)D);
+    float qr[8];
+    const int per = D / 32;
+    for (int j = 0; j < per; ++j) qr[j] = qs[lane + 32 * j];
+    float mx = -INFINITY;
+    for (int p0 = warp; p0 <= pos; p0 += 4 * MEGA_NW) {
+        float d[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int pp = p0 + u * MEGA_NW;
+            d[u] = 0.f;
+            if (pp < pos) {
+                const float* kp = kb + (size_t)pp * D;
+                for (int j = 0; j < per; ++j) d[u] = fmaf(qr[j], __ldg(kp + lane + 32 * j), d[u]);
+            } else if (pp == pos) {
+                for (int j = 0; j < per; ++j) d[u] = fmaf(qr[j], ks[lane + 32 * j], d[u]);
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+            for (int u = 0; u < 4; ++u) d[u] += __shfl_xor_sync(0xffffffffu, d[u], o);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int pp = p0 + u * MEGA_NW;
+            if (pp <= pos) {
+                const float v = d[u] * scale;
+                if (lane == 0) sc[pp] = v;
+                mx = fmaxf(mx, v);
+            }
+        }
+    }
+    if (lane == 0) sm.shf[warp] = mx;
+    cons_sync();
+    mx = sm.shf[0];
+#pragma unroll
+    for (int w = 1; w < MEGA_NW; ++w) mx = fmaxf(mx, sm.shf[w]);
+    cons_sync();
+    float sum = 0.f;
+    for (int pp = tid; pp <= pos; pp += MEGA_CONS) {
+        const float e = expf(sc[pp] - mx);
+        sc[pp] = e;
+        sum += e;
+    }
+    sum = warp_sum(sum);
+    if (lane == 0) sm.shf[warp] = sum;
+    cons_sync();
+    sum = 0.f;
+#pragma unroll
+    for (int w = 0; w < MEGA_NW; ++w) sum += sm.shf[w];
+    const float inv = 1.0f / sum;
+    const int ncol = D / 4, PG = MEGA_CONS / ncol;
+    const int dc = tid % ncol, pg = tid / ncol;
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (pg < PG) {
+        for (int p0 = pg; p0 < pos; p0 += 4 * PG) {
+            float4 v[4];
+            float w[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int pp = p0 + u * PG;
+                v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                w[u] = 0.f;
+                if (pp < pos) {
+                    v[u] = __ldg(reinterpret_cast<const float4*>(vb + (size_t)pp * D) + dc);
+                    w[u] = sc[pp] * inv;
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                a.x = fmaf(w[u], v[u].x, a.x);
+                a.y = fmaf(w[u], v[u].y, a.y);
+                a.z = fmaf(w[u], v[u].z, a.z);
+                a.w = fmaf(w[u], v[u].w, a.w);
+            }
+        }
+    }
+    const float wl = sc[pos] * inv;
+    if (pg < PG) part[pg * ncol + dc] = a;
+    cons_sync();
+    if (tid < ncol) {
+        float4 tt = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int i = 0; i < PG; ++i) {
+            const float4 v = part[i * ncol + tid];
+            tt.x += v.x;
+            tt.y += v.y;
+            tt.z += v.z;
+            tt.w += v.w;
+        }
+        const float4 vl = reinterpret_cast<const float4*>(vs)[tid];
+        tt.x = fmaf(wl, vl.x, tt.x);
+        tt.y = fmaf(wl, vl.y, tt.y);
+        tt.z = fmaf(wl, vl.z, tt.z);
+        tt.w = fmaf(wl, vl.w, tt.w);
+        reinterpret_cast<float4*>(p.att + ((size_t)b * NH + head) * D)[tid] = tt;
+    }
+    cons_sync();  // the attention scratch may be reused by the next (head, sequence) of this CTA
+}
+
+// ---- LM head: final RMSNorm, tied-embedding logits (f16 table through the ring), argmax partials
+__device__ __forceinline__ void mega_logits_phase(const MegaParams& p, const MegaSmem& sm, uint32_t& n) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int H = p.H, V = p.V, G = gridDim.x, cta = blockIdx.x;
+    float* xn = reinterpret_cast<float*>(sm.act);  // [B][H]
+    // final RMSNorm (cpu::rms_norm) of every token row into shared memory
+    for (int m = 0; m < p.B; ++m) {
+        double ss = 0.0;
+        for (int k = tid; k < H; k += MEGA_CONS) {
+            const float v = ld_cg_f32(p.x + (size_t)m * H + k);
+            xn[m * H + k] = v;
+            ss += (double)v * (double)v;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+        if (lane == 0) sm.shd[warp] = ss;
+        cons_sync();
+        double tot = 0.0;
+#pragma unroll
+        for (int wv = 0; wv < MEGA_NW; ++wv) tot += sm.shd[wv];
+        const float ms = (float)(tot / (double)H);
+        const float inv_rms = 1.0f / sqrtf(ms + p.eps);
+        for (int k = tid; k < H; k += MEGA_CONS) xn[m * H + k] = xn[m * H + k] * inv_rms * __ldg(p.final_norm + k);
+        cons_sync();
+    }
+    const int rpc = (V + G - 1) / G;
+    const int r0 = min(V, cta * rpc), r1 = min(V, r0 + rpc);
+    const int RL = MEGA_SLOT_BYTES / (H * 2);
+    float best[MEGA_MAXB];
+    int besti[MEGA_MAXB];
+#pragma unroll
+    for (int m = 0; m < MEGA_MAXB; ++m) {
+        best[m] = -INFINITY;
+        besti[m] = 0x7fffffff;
+    }
+    const int nvec = H / 256;  // uint4 (8 halves) per lane per row
+    int j = 0;                 // row index within this CTA
+    for (int rr = r0; rr < r1; rr += RL, ++n) {
+        const int nr = min(RL, r1 - rr);
+        const uint32_t slot = n % (uint32_t)p.n_slots;
+        mbar_wait(&sm.full[slot], (n / (uint32_t)p.n_slots) & 1u);
+        const unsigned char* base = sm.ring + (size_t)slot * MEGA_SLOT_BYTES;
+        for (int r = 0; r < nr; ++r, ++j) {
+            if (j % MEGA_NW != warp) continue;
+            const uint4* wrow = reinterpret_cast<const uint4*>(base + (size_t)r * H * 2);
+            float acc[MEGA_MAXB];
+#pragma unroll
+            for (int m = 0; m < MEGA_MAXB; ++m) acc[m] = 0.f;
+            for (int i = 0; i < nvec; ++i) {
+                const uint4 wv = wrow[lane + 32 * i];
+                const __half2* hp = reinterpret_cast<const __half2*>(&wv);
+                float f[8];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const float2 tt = __half22float2(hp[q]);
+                    f[2 * q] = tt.x;
+                    f[2 * q + 1] = tt.y;
+                }
+#pragma unroll
+                for (int m = 0; m < MEGA_MAXB; ++m) {
+                    if (m < p.B) {
+                        const float4 xa = *reinterpret_cast<const float4*>(xn + m * H + 8 * (lane + 32 * i));
+                        const float4 xb = *reinterpret_cast<const float4*>(xn + m * H + 8 * (lane + 32 * i) + 4);
+                        float a = acc[m];
+                        a = fmaf(f[0], xa.x, a);
+                        a = fmaf(f[1], xa.y, a);
+                        a = fmaf(f[2], xa.z, a);
+                        a = fmaf(f[3], xa.w, a);
+                        a = fmaf(f[4], xb.x, a);
+                        a = fmaf(f[5], xb.y, a);
+                        a = fmaf(f[6], xb.z, a);
+                        a = fmaf(f[7], xb.w, a);
+                        acc[m] = a;
+                    }
+                }
+            }
+#pragma unroll
+            for (int m = 0; m < MEGA_MAXB; ++m) {
+                if (m < p.B) {
+                    const float tot = warp_sum(acc[m]);
+                    const int row = rr + r;
+                    if (lane == 0) p.logits[(size_t)m * V + row] = tot;
+                    if (tot > best[m]) {  // a warp sees its rows in increasing order
+                        best[m] = tot;
+                        besti[m] = row;
+                    }
+                }
+            }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.empty[slot]);
+    }
+    if (lane == 0) {
+#pragma unroll
+        for (int m = 0; m < MEGA_MAXB; ++m) {
+            sm.bestv[warp * MEGA_MAXB + m] = best[m];
+            sm.besti[warp * MEGA_MAXB + m] = besti[m];
+        }
+    }
+    cons_sync();
+    if (tid < p.B) {
+        float bv = -INFINITY;
+        int bi = 0x7fffffff;
+        for (int w = 0; w < MEGA_NW; ++w) {
+            const float cv = sm.bestv[w * MEGA_MAXB + tid];
+            const int ci = sm.besti[w * MEGA_MAXB + tid];
+            if (cv > bv || (cv == bv && ci < bi)) {
+                bv = cv;
+                bi = ci;
+            }
+        }
+        p.part_val[(size_t)tid * G + cta] = bv;
+        p.part_idx[(size_t)tid * G + cta] = bi;
+    }
+}
+
+// ---- the producer warp: every weight byte of the step, in consumption order ----------------------
+__device__ __forceinline__ void mega_producer(const MegaParams& p, const MegaSmem& sm) {
+    const int lane = threadIdx.x & 31;
+    const int G = gridDim.x, cta = blockIdx.x;
+    uint32_t n = 0;
+    int tcount = 0;
+    const uint32_t NS = (uint32_t)p.n_slots;
+    for (int l = 0; l < p.L; ++l) {
+        const MegaLayer& L = sm.layers[l];
+        for (int op = 0; op < 4; ++op) {
+            const uint8_t* w = op == 0 ? L.wqkv : (op == 1 ? L.wo : (op == 2 ? L.wgu : L.wdown));
+            const int N = op == 0 ? (p.NH + 2 * p.NKV) * p.D : (op == 1 ? p.H : (op == 2 ? 2 * p.F : p.H));
+            const int K = op == 1 ? p.NH * p.D : (op == 3 ? p.F : p.H);
+            const int NT = (N + 15) >> 4, ns = K >> 8, nch = (ns + MEGA_SLOT_STEPS - 1) / MEGA_SLOT_STEPS;
+            const size_t stride = (size_t)K >> 2;
+            for (int tile = (cta - tcount + G) % G; tile < NT; tile += G) {
+                const int nr = min(16, N - tile * 16);
+                for (int ch = 0; ch < nch; ++ch, ++n) {
+                    int s0, cs;
+                    chunk_range(ns, nch, ch, s0, cs);
+                    const uint32_t slot = n % NS;
+                    unsigned char* dst = sm.ring + (size_t)slot * MEGA_SLOT_BYTES;
+                    if (lane == 0) {
+                        if (n >= NS) mbar_wait(&sm.empty[slot], ((n / NS) - 1u) & 1u);
+                        mbar_expect_tx(&sm.full[slot], (uint32_t)(nr * cs * 64));
+                    }
+                    __syncwarp();
+                    if (nch == 1) {
+                        if (lane == 0) bulk_g2s(dst, w + (size_t)tile * 16 * stride, (uint32_t)(nr * cs * 64), &sm.full[slot]);
+                    } else if (lane < nr) {
+                        bulk_g2s(dst + (size_t)lane * cs * 64, w + ((size_t)tile * 16 + lane) * stride + (size_t)s0 * 64,
+                                 (uint32_t)(cs * 64), &sm.full[slot]);
+                    }
+                }
+            }
+            tcount = (tcount + NT) % G;
+        }
+    }
+    if (p.mode == 0) {
+        const int rpc = (p.V + G - 1) / G;
+        const int r0 = min(p.V, cta * rpc), r1 = min(p.V, r0 + rpc);
+        const int RL = MEGA_SLOT_BYTES / (p.H * 2);
+        for (int rr = r0; rr < r1; rr += RL, ++n) {
+            const int nr = min(RL, r1 - rr);
+            const uint32_t slot = n % NS;
+            if (lane == 0) {
+                if (n >= NS) mbar_wait(&sm.empty[slot], ((n / NS) - 1u) & 1u);
+                const uint32_t bytes = (uint32_t)nr * (uint32_t)p.H * 2u;
+                mbar_expect_tx(&sm.full[slot], bytes);
+                bulk_g2s(sm.ring + (size_t)slot * MEGA_SLOT_BYTES, p.emb + (size_t)rr * p.H, bytes, &sm.full[slot]);
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(MEGA_THREADS, 1) decode_mega_kernel(const __grid_constant__ MegaParams p) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const int G = gridDim.x, cta = blockIdx.x;
+    // ---- shared memory carve-up (must match mega_smem_bytes) -----------------------------------
+    MegaSmem sm;
+    size_t off = 0;
+    sm.full = reinterpret_cast<uint64_t*>(smem_raw + off);
+    off += MEGA_MAX_SLOTS * 8;
+    sm.empty = reinterpret_cast<uint64_t*>(smem_raw + off);
+    off += MEGA_MAX_SLOTS * 8;
+    sm.shd = reinterpret_cast<double*>(smem_raw + off);
+    off += 32 * 8;
+    sm.shf = reinterpret_cast<float*>(smem_raw + off);
+    off += 32 * 4;
+    sm.sc_s = reinterpret_cast<float*>(smem_raw + off);
+    off += 32;
+    sm.bestv = reinterpret_cast<float*>(smem_raw + off);
+    off += MEGA_NW * MEGA_MAXB * 4;
+    sm.besti = reinterpret_cast<int*>(smem_raw + off);
+    off += MEGA_NW * MEGA_MAXB * 4;
+    sm.layers = reinterpret_cast<MegaLayer*>(smem_raw + off);
+    off += (size_t)MEGA_MAX_LAYERS * sizeof(MegaLayer);
+    sm.acc = reinterpret_cast<int*>(smem_raw + off);
+    off += MEGA_MAX_TILES * 128 * 4;
+    off = (off + 127) & ~(size_t)127;
+    sm.act = smem_raw + off;
+    off += (size_t)p.act_bytes;
+    off = (off + 127) & ~(size_t)127;
+    sm.attn = reinterpret_cast<float*>(smem_raw + off);
+    off += (size_t)p.attn_floats * 4;
+    off = (off + 127) & ~(size_t)127;
+    sm.ring = smem_raw + off;
+
+    if (tid == 0) {
+        for (int s = 0; s < p.n_slots; ++s) {
+            mbar_init(&sm.full[s], 1);
+            mbar_init(&sm.empty[s], MEGA_NW);
+        }
+        mbar_fence_init();
+        if (cta == 0) p.bar[p.parity ^ 1] = 0u;  // the counter of the NEXT launch (its last user has finished)
+    }
+    for (int i = tid; i < p.L * (int)(sizeof(MegaLayer) / 8); i += MEGA_THREADS)
+        reinterpret_cast<uint64_t*>(sm.layers)[i] = reinterpret_cast<const uint64_t*>(p.layers)[i];
+    __syncthreads();  // the only CTA-wide barrier: from here on the producer warp runs free
+
+    if (warp == MEGA_NW) {
+        mega_producer(p, sm);
+        return;
+    }
+
+    // ---- consumers ------------------------------------------------------------------------------
+    unsigned* ctr = p.bar + p.parity;
+    unsigned target = 0;
+    uint32_t n = 0;
+    int tcount = 0;
+    const int H = p.H, F = p.F, D = p.D, NH = p.NH, NKV = p.NKV, B = p.B;
+    const int QD = NH * D, QKV = (NH + 2 * NKV) * D;
+    if (p.mode == 1) {
+        // roofline leg: the 4L ternary GEMVs with fixed int8 inputs, no dependencies, no barriers
+        for (int l = 0; l < p.L; ++l) {
+            const MegaLayer& L = sm.layers[l];
+            mega_gemv_phase(p, sm, L.wqkv, QKV, H, 0, nullptr, nullptr, 0, p.qkv, nullptr, n, tcount);
+            mega_gemv_phase(p, sm, L.wo, H, QD, 0, nullptr, nullptr, 0, p.att, nullptr, n, tcount);
+            mega_gemv_phase(p, sm, L.wgu, 2 * F, H, 0, nullptr, nullptr, 2, p.gu, nullptr, n, tcount);
+            mega_gemv_phase(p, sm, L.wdown, H, F, 0, nullptr, nullptr, 0, p.att, nullptr, n, tcount);
+            cons_sync();
+        }
+        return;
+    }
+    const int pos = ld_cg_s32(p.pos);
+    // embed: x[b] = f32(emb[token[b]]), spread over the grid
+    for (int i = cta * MEGA_CONS + tid; i < B * H; i += G * MEGA_CONS) {
+        const int b = i / H, k = i - b * H;
+        p.x[i] = __half2float(p.emb[(size_t)ld_cg_s32(p.tokens + b) * H + k]);
+    }
+    grid_sync(ctr, target, G);
+    for (int l = 0; l < p.L; ++l) {
+        const MegaLayer& L = sm.layers[l];
+        const size_t kvoff = (size_t)l * B * NKV * p.max_ctx * D;
+        mega_gemv_phase(p, sm, L.wqkv, QKV, H, 2, p.x, L.attn_norm, 0, p.qkv, nullptr, n, tcount);
+        grid_sync(ctr, target, G);
+        for (int task = cta; task < NH * B; task += G) mega_attention(p, sm, task % NH, task / NH, pos, p.kc + kvoff, p.vc + kvoff);
+        grid_sync(ctr, target, G);
+        mega_gemv_phase(p, sm, L.wo, H, QD, 1, p.att, nullptr, 1, p.x, p.x, n, tcount);
+        grid_sync(ctr, target, G);
+        mega_gemv_phase(p, sm, L.wgu, 2 * F, H, 2, p.x, L.ffn_norm, 2, p.gu, nullptr, n, tcount);
+        grid_sync(ctr, target, G);
+        mega_gemv_phase(p, sm, L.wdown, H, F, 1, p.gu, nullptr, 1, p.x, p.x, n, tcount);
+        grid_sync(ctr, target, G);
+    }
+    mega_logits_phase(p, sm, n);
+    grid_sync(ctr, target, G);
+    // greedy argmax over the per-CTA partials (lowest index on ties); feed the token back, advance
+    if (cta == 0 && warp < B) {
+        const int b = warp, lane = tid & 31;
+        float best = -INFINITY;
+        int idx = 0x7fffffff;
+        for (int i = lane; i < G; i += 32) {
+            const float v = ld_cg_f32(p.part_val + (size_t)b * G + i);
+            const int vi = ld_cg_s32(p.part_idx + (size_t)b * G + i);
+            if (v > best || (v == best && vi < idx)) {
+                best = v;
+                idx = vi;
+            }
+        }
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+            if (ov > best || (ov == best && oi < idx)) {
+                best = ov;
+                idx = oi;
+            }
+        }
+        if (lane == 0) {
+            if (idx == 0x7fffffff) idx = 0;
+            p.next[b] = idx;
+            p.tokens[b] = idx;
+            if (b == 0) *p.pos = pos + 1;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+static size_t mega_fixed_smem(int act_bytes, int attn_floats) {
+    size_t off = MEGA_MAX_SLOTS * 16 + 32 * 8 + 32 * 4 + 32 + 2 * MEGA_NW * MEGA_MAXB * 4 +
+                 (size_t)MEGA_MAX_LAYERS * sizeof(MegaLayer) + MEGA_MAX_TILES * 128 * 4;
+    off = (off + 127) & ~(size_t)127;
+    off += (size_t)act_bytes;
+    off = (off + 127) & ~(size_t)127;
+    off += (size_t)attn_floats * 4;
+    off = (off + 127) & ~(size_t)127;
+    return off;
+}
+
+// Fills the shape-derived fields of `p` (n_slots, act_bytes, attn_floats) and returns the dynamic
+// shared memory the launch needs, or 0 when the shape is not covered by this kernel.
+size_t mega_plan(MegaParams* p, int num_sms) {
+    const int QD = p->NH * p->D;
+    if (p->B < 1 || p->B > MEGA_MAXB || p->L > MEGA_MAX_LAYERS) return 0;
+    if (p->H % 256 || p->F % 256 || QD % 256) return 0;          // whole 256-column steps, no tails
+    if (p->H > 8192 || p->F > 8192 || QD > 8192) return 0;       // one prologue pass per row
+    if (p->D % 32 || p->D > 256 || MEGA_CONS % (p->D / 4)) return 0;
+    if (p->H * 2 > MEGA_SLOT_BYTES) return 0;                    // one LM-head row per slot at least
+    if (((p->NH + 2 * p->NKV) * p->D) % 2 || (2 * p->F) % 16) return 0;
+    const int kmax = p->H > p->F ? (p->H > QD ? p->H : QD) : (p->F > QD ? p->F : QD);
+    const int tiles_max = ((2 * p->F + 15) / 16 + num_sms - 1) / num_sms + 1;
+    if (tiles_max > MEGA_MAX_TILES) return 0;
+    int act = p->B * (kmax + 64);
+    if (p->B * p->H * 4 > act) act = p->B * p->H * 4;
+    p->act_bytes = (act + 15) & ~15;
+    p->attn_floats = ((p->max_ctx + 3) & ~3) + MEGA_CONS * 4 + 3 * 256 + 16;
+    const size_t fixed = mega_fixed_smem(p->act_bytes, p->attn_floats);
+    const size_t cap = 227 * 1024;
+    if (fixed + 3 * (size_t)MEGA_SLOT_BYTES > cap) return 0;
+    int slots = (int)((cap - fixed) / MEGA_SLOT_BYTES);
+    if (slots > MEGA_MAX_SLOTS) slots = MEGA_MAX_SLOTS;
+    p->n_slots = slots;
+    return fixed + (size_t)slots * MEGA_SLOT_BYTES;
+}
+
+int launch_decode_mega(const MegaParams& p, size_t smem, int num_sms, cudaStream_t st) {
+    static bool attr_set[16] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 16 && !attr_set[dev]) {
+        B200_CUDA(cudaFuncSetAttribute(decode_mega_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        attr_set[dev] = true;
+    }
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)num_sms);
+    cfg.blockDim = dim3(MEGA_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeCooperative;  // all CTAs resident: the grid barrier cannot deadlock
+    attr[0].val.cooperative = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    B200_CUDA(cudaLaunchKernelEx(&cfg, decode_mega_kernel, p));
+    count_launch();
+    return 0;
+}
+
+}  // namespace b200
