@@ -10,11 +10,13 @@
 // The whole step (about 10 launches per layer) is captured once into a CUDA graph; the
 // position lives in device memory so the same graph replays for every token, and the greedy
 // token is fed back on device so a decode loop needs no host round trip.
+#include <cstdio>
 #include <memory>
 #include <vector>
 
 #include "common.cuh"
 #include "decode_fused.cuh"
+#include "decode_mega.h"
 
 namespace b200 {
 
@@ -252,6 +254,12 @@ struct bitnet_b200_model {
     float* part_val = nullptr;  // [B, logits CTAs] per-CTA argmax partials (fused path)
     int* part_idx = nullptr;
     int fused = -1;             // -1 undecided, 0 generic kernels, 1 fused PDL path
+    int mega = -1;              // -1 undecided, 0 no, 1 the persistent one-kernel step (decode_mega.cu)
+    MegaLayer* mega_layers = nullptr;  // device table
+    unsigned* mega_bar = nullptr;      // [2] grid-barrier counters
+    int mega_parity = 0;
+    size_t mega_smem = 0;
+    MegaParams mega_p{};
     int8_t* q8 = nullptr;
     float* s8 = nullptr;
     int* next_host = nullptr;  // pinned
@@ -462,6 +470,71 @@ static int enqueue_step(bitnet_b200_model* m) {
     return 0;
 }
 
+// The persistent one-kernel step covers QK256 models with batch <= 4 (decode_mega.cu);
+// BITNET_B200_NO_MEGA=1 keeps the per-projection graph.
+static int mega_setup(bitnet_b200_model* m) {
+    if (m->mega >= 0) return 0;
+    m->mega = 0;
+    const auto& c = m->cfg;
+    if (getenv("BITNET_B200_NO_MEGA") || c.layout != BITNET_B200_LAYOUT_QK256) return 0;
+    if (!m->have_emb || !m->have_rope || m->layers_set != c.n_layers) return 0;
+    int coop = 0;
+    cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, m->ctx->device);
+    if (!coop) return 0;
+    MegaParams& p = m->mega_p;
+    p = MegaParams{};
+    p.L = c.n_layers; p.B = c.batch; p.H = c.hidden; p.F = c.ffn; p.NH = c.n_heads; p.NKV = c.n_kv_heads;
+    p.D = c.head_dim; p.V = c.vocab; p.max_ctx = c.max_ctx; p.eps = c.rms_eps;
+    m->mega_smem = mega_plan(&p, m->ctx->num_sms);
+    if (!m->mega_smem) return 0;
+    std::vector<MegaLayer> tab((size_t)c.n_layers);
+    for (int l = 0; l < c.n_layers; ++l) {
+        const LayerW& L = m->layers[(size_t)l];
+        for (const bitnet_b200_weight* w : {L.wqkv, L.wo, L.wgateup, L.wdown})
+            if (w->code_stride != w->cols / 4 || w->lut_word != m->layers[0].wqkv->lut_word) return 0;
+        tab[(size_t)l] = MegaLayer{L.wqkv->codes, L.wo->codes, L.wgateup->codes, L.wdown->codes, L.attn_norm, L.ffn_norm};
+    }
+    if (dmalloc((void**)&m->mega_layers, tab.size() * sizeof(MegaLayer)) || dmalloc((void**)&m->mega_bar, 8)) return -1;
+    cudaStream_t st = m->ctx->stream;
+    B200_CUDA(cudaMemcpyAsync(m->mega_layers, tab.data(), tab.size() * sizeof(MegaLayer), cudaMemcpyHostToDevice, st));
+    B200_CUDA(cudaMemsetAsync(m->mega_bar, 0, 8, st));
+    B200_CUDA(cudaStreamSynchronize(st));
+    p.layers = m->mega_layers;
+    p.emb = m->emb; p.final_norm = m->final_norm; p.rope_cos = m->rope_cos; p.rope_sin = m->rope_sin;
+    p.kc = m->kc; p.vc = m->vc; p.pos = m->pos; p.tokens = m->tokens; p.next = m->next;
+    p.x = m->x; p.qkv = m->qkv; p.att = m->att; p.gu = m->gu; p.logits = m->logits;
+    p.part_val = m->part_val; p.part_idx = m->part_idx;
+    p.q_fixed = m->q8; p.s_fixed = m->s8; p.bar = m->mega_bar;
+    p.lut = m->layers[0].wqkv->lut_word;
+    if (getenv("BITNET_B200_MEGA_PROF")) {  // diagnostics: per-phase globaltimer stamps of CTA 0, dumped at destroy
+        if (dmalloc((void**)&p.prof, 16384 * 8)) return -1;
+        B200_CUDA(cudaMemset(p.prof, 0, 16384 * 8));
+    }
+    m->mega_parity = 0;
+    m->mega = 1;
+    m->launches_per_step = 1;
+    return 0;
+}
+
+static int mega_launch(bitnet_b200_model* m, int mode) {
+    MegaParams p = m->mega_p;
+    p.mode = mode;
+    p.parity = m->mega_parity;
+    m->mega_parity ^= 1;
+    return launch_decode_mega(p, m->mega_smem, m->ctx->num_sms, m->ctx->stream);
+}
+
+// one decode step on the context's stream: the persistent kernel, or a replay of the step graph
+static int ensure_graph(bitnet_b200_model* m);
+static int step_launch(bitnet_b200_model* m) {
+    if (mega_setup(m)) return -1;
+    if (m->mega == 1) return mega_launch(m, 0);
+    if (ensure_graph(m)) return -1;
+    B200_CUDA(cudaGraphLaunch(m->graph, m->ctx->stream));
+    count_launch(m->launches_per_step);
+    return 0;
+}
+
 static int ensure_graph(bitnet_b200_model* m) {
     if (m->graph) return 0;
     if (!m->have_emb || !m->have_rope || m->layers_set != m->cfg.n_layers)
@@ -524,7 +597,7 @@ int bitnet_b200_model_create(bitnet_b200_ctx* ctx, const bitnet_b200_model_confi
             return -1;
         const size_t qmax = std::max(std::max(H, F), NH * D);
         if (dmalloc((void**)&m->q8, B * qmax) || dmalloc((void**)&m->s8, B * 4)) return -1;
-        const size_t nparts = div_ceil((size_t)c.vocab, LOGITS_ROWS_PER_CTA);
+        const size_t nparts = std::max(div_ceil((size_t)c.vocab, LOGITS_ROWS_PER_CTA), (size_t)ctx->num_sms);
         if (dmalloc((void**)&m->part_val, B * nparts * 4) || dmalloc((void**)&m->part_idx, B * nparts * 4)) return -1;
         B200_CUDA(cudaMallocHost((void**)&m->next_host, B * 4));
         B200_CUDA(cudaMallocHost((void**)&m->tok_host, B * 4));
@@ -543,6 +616,21 @@ int bitnet_b200_model_create(bitnet_b200_ctx* ctx, const bitnet_b200_model_confi
 void bitnet_b200_model_destroy(bitnet_b200_model* m) {
     if (!m) return;
     if (m->graph) cudaGraphExecDestroy(m->graph);
+    if (m->mega_p.prof) {
+        std::vector<unsigned long long> h(16384);
+        if (cudaMemcpy(h.data(), m->mega_p.prof, h.size() * 8, cudaMemcpyDeviceToHost) == cudaSuccess)
+            if (FILE* f = fopen(getenv("BITNET_B200_MEGA_PROF") ? getenv("BITNET_B200_MEGA_PROF") : "/dev/null", "w")) {
+                for (size_t i = 0; i < 8192 && h[i]; ++i) fprintf(f, "%llu\n", h[i] - h[0]);
+                for (size_t i = 14000; i < 14064; ++i)
+                    if (h[i]) fprintf(f, "@ %zu %llu\n", i - 14000, h[i] - h[14000]);
+                for (size_t i = 8192; i < 14000; ++i)
+                    if (h[i]) fprintf(f, "# %zu %llu %llu\n", i - 8192, h[i] >> 32, h[i] & 0xffffffffull);
+                fclose(f);
+            }
+        cudaFree(m->mega_p.prof);
+    }
+    if (m->mega_layers) cudaFree(m->mega_layers);
+    if (m->mega_bar) cudaFree(m->mega_bar);
     for (auto& L : m->layers) {
         bitnet_b200_weight_destroy(L.wqkv);
         bitnet_b200_weight_destroy(L.wo);
@@ -573,7 +661,7 @@ int bitnet_b200_model_set_layer(bitnet_b200_model* m, int layer, const void* wq,
             return fail("model_set_layer: NULL argument");
         const auto& c = m->cfg;
         if (layer < 0 || layer >= c.n_layers) return fail("model_set_layer: layer out of range");
-        if (m->graph) return fail("model_set_layer: the step graph is already built");
+        if (m->graph || m->mega == 1) return fail("model_set_layer: the decode step is already built");
         B200_CUDA(cudaSetDevice(m->ctx->device));
         LayerW& L = m->layers[(size_t)layer];
         const bool fresh = L.wqkv == nullptr;
@@ -639,7 +727,6 @@ int bitnet_b200_model_decode(bitnet_b200_model* m, const int32_t* tokens, int32_
     try {
         if (!m || !tokens || !next_tokens) return fail("model_decode: NULL argument");
         B200_CUDA(cudaSetDevice(m->ctx->device));
-        if (ensure_graph(m)) return -1;
         cudaStream_t st = m->ctx->stream;
         const size_t B = (size_t)m->cfg.batch;
         for (size_t b = 0; b < B; ++b) {
@@ -647,8 +734,7 @@ int bitnet_b200_model_decode(bitnet_b200_model* m, const int32_t* tokens, int32_
             m->tok_host[b] = tokens[b];
         }
         B200_CUDA(cudaMemcpyAsync(m->tokens, m->tok_host, B * 4, cudaMemcpyHostToDevice, st));
-        B200_CUDA(cudaGraphLaunch(m->graph, st));
-        count_launch(m->launches_per_step);
+        if (step_launch(m)) return -1;
         B200_CUDA(cudaMemcpyAsync(m->next_host, m->next, B * 4, cudaMemcpyDeviceToHost, st));
         if (logits_out)
             B200_CUDA(cudaMemcpyAsync(logits_out, m->logits, B * (size_t)m->cfg.vocab * 4, cudaMemcpyDeviceToHost, st));
@@ -666,11 +752,8 @@ int bitnet_b200_model_decode(bitnet_b200_model* m, const int32_t* tokens, int32_
 int bitnet_b200_model_decode_device(bitnet_b200_model* m, int n_steps) {
     if (!m || n_steps < 0) return fail("model_decode_device: bad argument");
     B200_CUDA(cudaSetDevice(m->ctx->device));
-    if (ensure_graph(m)) return -1;
-    for (int i = 0; i < n_steps; ++i) {
-        B200_CUDA(cudaGraphLaunch(m->graph, m->ctx->stream));
-        count_launch(m->launches_per_step);
-    }
+    for (int i = 0; i < n_steps; ++i)
+        if (step_launch(m)) return -1;
     return 0;
 }
 
@@ -705,6 +788,28 @@ int bitnet_b200_model_time_linears(bitnet_b200_model* m, int reps, float* ms_per
         const auto& c = m->cfg;
         cudaStream_t st = m->ctx->stream;
         const int B = c.batch;
+        if (mega_setup(m)) return -1;
+        if (m->mega == 1) {
+            // the persistent kernel restricted to its 4L ternary GEMV phases (fixed int8 inputs, no
+            // barriers): one launch streams every packed ternary weight of the model once
+            cudaEvent_t e0, e1;
+            cudaEventCreate(&e0);
+            cudaEventCreate(&e1);
+            int rc = mega_launch(m, 1);  // warm-up pass
+            cudaEventRecord(e0, st);
+            for (int i = 0; i < reps && !rc; ++i) rc = mega_launch(m, 1);
+            cudaEventRecord(e1, st);
+            cudaError_t e = cudaStreamSynchronize(st);
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, e0, e1);
+            cudaEventDestroy(e0);
+            cudaEventDestroy(e1);
+            if (rc) return -1;
+            if (e != cudaSuccess) return fail_cuda("model_time_linears", e);
+            *ms_per_pass = ms / (float)reps;
+            *launches_per_pass = 1;
+            return 0;
+        }
         cudaGraph_t g = nullptr;
         cudaGraphExec_t ge = nullptr;
         const uint64_t l0 = g_launches.load();

@@ -21,7 +21,7 @@
 // 346-372), per-token absmax int8 quantiser (cpu/quantize.rs:32-49) and cpu::rms_norm
 // (cpu/layer_norm.rs:118-137) in the prologue. Cross-warp partial sums meet through int32
 // shared-memory atomics: integer addition is associative, so the result is order-independent.
-#include "common.cuh"
+#include "decode_mega.h"
 
 namespace b200 {
 
@@ -34,30 +34,6 @@ constexpr int MEGA_MAX_TILES = 16;                  // 16-row tiles per CTA per 
 constexpr int MEGA_MAXB = 4;                        // tokens per step
 constexpr int MEGA_MAX_SLOTS = 12;
 constexpr int MEGA_MAX_LAYERS = 64;
-
-struct MegaLayer {
-    const uint8_t *wqkv, *wo, *wgu, *wdown;  // device-layout code planes [N, K/4]
-    const float *attn_norm, *ffn_norm;
-};
-
-struct MegaParams {
-    const MegaLayer* layers;
-    const __half* emb;
-    const float *final_norm, *rope_cos, *rope_sin;
-    float *kc, *vc;
-    int *pos, *tokens, *next;
-    float *x, *qkv, *att, *gu, *logits, *part_val;
-    int* part_idx;
-    const int8_t* q_fixed;   // mode 1: fixed int8 rows [B, max(H, F, NH*D)]
-    const float* s_fixed;    // mode 1: their scales
-    unsigned* bar;           // [2] grid-barrier counters, used alternately per launch
-    int parity;
-    int L, B, H, F, NH, NKV, D, V, max_ctx;
-    float eps;
-    uint32_t lut;
-    int mode;                // 0 = full decode step; 1 = the 4L ternary GEMVs only, no dependencies
-    int n_slots, act_bytes, attn_floats;
-};
 
 // ---- small PTX helpers ------------------------------------------------------------------------
 __device__ __forceinline__ void cons_sync() { asm volatile("bar.sync 1, %0;" ::"n"(MEGA_CONS) : "memory"); }
@@ -83,12 +59,33 @@ __device__ __forceinline__ void mma_s8_m16n8k32(int (&c)[4], uint32_t a0, uint32
         : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3])
         : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
-// q = clamp(round_half_away(v * inv), -127, 127); NaN -> 0 (Rust `as i8`)
+// q = clamp(round_half_away(v * inv), -127, 127); NaN -> 0 (Rust `as i8`). Round-half-away as
+// trunc(y + copysign(0.5 - 2^-25, y)): identical to roundf(y) for every float |y| <= 200 (checked
+// exhaustively on the CPU, tests/test_oracle_golden.py::test_round_half_away_trick), 4 instructions
+// instead of ~12; cvt.rzi maps NaN to 0 and saturates +-inf, the clamp does the rest.
 __device__ __forceinline__ int mega_quant_i8(float v, float inv) {
-    float r = roundf(v * inv);
-    if (r != r) return 0;
-    r = fminf(fmaxf(r, -127.f), 127.f);
-    return (int)r;
+    const float y = v * inv;
+    const float h = __uint_as_float(0x3effffffu | (__float_as_uint(y) & 0x80000000u));
+    const int r = __float2int_rz(__fadd_rn(y, h));
+    return max(-127, min(127, r));
+}
+
+// diagnostics: CTA 0 / thread 0 appends a globaltimer stamp (ns) when p.prof is set
+__device__ __forceinline__ void prof_stamp(const MegaParams& p, int& pi) {
+    if (p.prof && blockIdx.x == 0 && threadIdx.x == 0 && pi < 16384) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+        p.prof[pi] = t;
+    }
+    ++pi;
+}
+
+// producer-side wait: sleeps between probes (the ring is deep, the producer is never latency-critical)
+__device__ __forceinline__ void mbar_wait_backoff(void* bar, uint32_t parity) {
+    for (uint32_t it = 0; !mbar_try_wait(bar, parity); ++it) {
+        __nanosleep(200);
+        if (it > (1u << 24)) __trap();
+    }
 }
 
 // Grid-wide barrier over the consumer threads of all CTAs (the kernel is launched cooperatively,
@@ -102,7 +99,7 @@ __device__ __forceinline__ void grid_sync(unsigned* ctr, unsigned& target, unsig
         uint32_t it = 0;
         do {
             asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
-            if (++it > (1u << 23)) __trap();
+            if (++it > (1u << 24)) __trap();
         } while (v < target);
     }
     cons_sync();
@@ -131,180 +128,240 @@ struct MegaSmem {
 };
 
 // ---- activation prologue: f32 rows -> (optional RMSNorm) -> int8 rows + scale in shared memory ---
-// pro: 0 = copy the fixed int8 rows (mode 1), 1 = absmax int8 quantise, 2 = RMSNorm then quantise
-__device__ __forceinline__ void mega_prologue(const MegaParams& p, const MegaSmem& sm, int pro, const float* xin,
-                                              const float* gamma, int K, int q_ld) {
+// pro: 0 = copy the fixed int8 rows (mode 1), 1 = absmax int8 quantise, 2 = RMSNorm then quantise.
+// NV = float4 groups per thread (K <= 16 * NV * MEGA_CONS... i.e. 2 -> K <= 4096, 4 -> K <= 8192).
+template <int NV>
+__device__ __forceinline__ void mega_prologue_rows(const MegaParams& p, const MegaSmem& sm, int pro, const float* xin,
+                                                   const float* gamma, int K, int q_ld) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     int8_t* qbuf = reinterpret_cast<int8_t*>(sm.act);
-    if (pro == 0) {
-        const int vpr = K / 16;
-        for (int i = tid; i < p.B * vpr; i += MEGA_CONS) {
-            const int m = i / vpr, v = i - m * vpr;
-            *reinterpret_cast<uint4*>(qbuf + m * q_ld + v * 16) =
-                *reinterpret_cast<const uint4*>(p.q_fixed + (size_t)m * K + v * 16);
+    const int ngrp = K >> 2;
+    for (int m = 0; m < p.B; ++m) {
+        float4 v[NV];
+#pragma unroll
+        for (int j = 0; j < NV; ++j) {
+            const int g = tid + j * MEGA_CONS;
+            v[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (g < ngrp) v[j] = ld_cg_f32x4(xin + (size_t)m * K + 4 * g);
         }
+        if (pro == 2) {
+            double ss = 0.0;
+#pragma unroll
+            for (int j = 0; j < NV; ++j)
+                ss += (double)v[j].x * (double)v[j].x + (double)v[j].y * (double)v[j].y +
+                      (double)v[j].z * (double)v[j].z + (double)v[j].w * (double)v[j].w;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+            if (lane == 0) sm.shd[warp] = ss;
+            cons_sync();
+            double tot = 0.0;
+#pragma unroll
+            for (int wv = 0; wv < MEGA_NW; ++wv) tot += sm.shd[wv];
+            const float ms = (float)(tot / (double)K);
+            const float inv_rms = 1.0f / sqrtf(ms + p.eps);
+#pragma unroll
+            for (int j = 0; j < NV; ++j) {
+                const int g = tid + j * MEGA_CONS;
+                if (g < ngrp) {
+                    const float4 gm = __ldg(reinterpret_cast<const float4*>(gamma) + g);
+                    v[j].x = v[j].x * inv_rms * gm.x;
+                    v[j].y = v[j].y * inv_rms * gm.y;
+                    v[j].z = v[j].z * inv_rms * gm.z;
+                    v[j].w = v[j].w * inv_rms * gm.w;
+                }
+            }
+        }
+        float amax = 0.f;
+#pragma unroll
+        for (int j = 0; j < NV; ++j)
+            amax = fmaxf(amax, fmaxf(fmaxf(fabsf(v[j].x), fabsf(v[j].y)), fmaxf(fabsf(v[j].z), fabsf(v[j].w))));
+        amax = warp_max(amax);
+        if (lane == 0) sm.shf[warp] = amax;
+        cons_sync();
+        amax = 0.f;
+#pragma unroll
+        for (int wv = 0; wv < MEGA_NW; ++wv) amax = fmaxf(amax, sm.shf[wv]);
+        const float sc = amax == 0.f ? 0.f : amax / 127.f;
+        const float inv = amax == 0.f ? 0.f : 1.0f / sc;
+        if (tid == 0) sm.sc_s[m] = sc;
+#pragma unroll
+        for (int j = 0; j < NV; ++j) {
+            const int g = tid + j * MEGA_CONS;
+            if (g < ngrp) {
+                uint32_t wq = 0;
+                if (amax != 0.f)
+                    wq = (uint32_t)(uint8_t)mega_quant_i8(v[j].x, inv) | ((uint32_t)(uint8_t)mega_quant_i8(v[j].y, inv) << 8) |
+                         ((uint32_t)(uint8_t)mega_quant_i8(v[j].z, inv) << 16) |
+                         ((uint32_t)(uint8_t)mega_quant_i8(v[j].w, inv) << 24);
+                reinterpret_cast<uint32_t*>(qbuf + m * q_ld)[g] = wq;
+            }
+        }
+        cons_sync();  // shd/shf reusable; qbuf + sc_s visible
+    }
+}
+
+__device__ __forceinline__ void mega_prologue(const MegaParams& p, const MegaSmem& sm, int pro, const float* xin,
+                                           const float* gamma, int K, int q_ld) {
+    const int tid = threadIdx.x;
+    if (pro == 0) {
+        int8_t* qbuf = reinterpret_cast<int8_t*>(sm.act);
+        const int vpr = K >> 4;
+        for (int m = 0; m < p.B; ++m)
+            for (int v = tid; v < vpr; v += MEGA_CONS)
+                *reinterpret_cast<uint4*>(qbuf + m * q_ld + v * 16) =
+                    *reinterpret_cast<const uint4*>(p.q_fixed + (size_t)m * K + v * 16);
         if (tid < p.B) sm.sc_s[tid] = p.s_fixed[tid];
         cons_sync();
         return;
     }
-    constexpr int NV = 4;  // float4 per thread: K <= 16 * MEGA_CONS = 8192 per pass
-    const int ngrp = K / 4;
-    for (int m = 0; m < p.B; ++m) {
-        for (int g0 = 0; g0 < ngrp; g0 += NV * MEGA_CONS) {  // one pass for K <= 8192
-            // (K > 8192 takes several passes over a row: the reductions below are then per pass,
-            //  which is wrong -- the host only selects this kernel when K <= 8192.)
-            float4 v[NV];
-#pragma unroll
-            for (int j = 0; j < NV; ++j) {
-                const int g = g0 + tid + j * MEGA_CONS;
-                v[j] = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (g < ngrp) v[j] = ld_cg_f32x4(xin + (size_t)m * K + 4 * g);
-            }
-            if (pro == 2) {
-                double ss = 0.0;
-#pragma unroll
-                for (int j = 0; j < NV; ++j)
-                    ss += (double)v[j].x * (double)v[j].x + (double)v[j].y * (double)v[j].y +
-                          (double)v[j].z * (double)v[j].z + (double)v[j].w * (double)v[j].w;
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
-                if (lane == 0) sm.shd[warp] = ss;
-                cons_sync();
-                double tot = 0.0;
-#pragma unroll
-                for (int wv = 0; wv < MEGA_NW; ++wv) tot += sm.shd[wv];
-                const float ms = (float)(tot / (double)K);
-                const float inv_rms = 1.0f / sqrtf(ms + p.eps);
-#pragma unroll
-                for (int j = 0; j < NV; ++j) {
-                    const int g = g0 + tid + j * MEGA_CONS;
-                    if (g < ngrp) {
-                        const float4 gm = __ldg(reinterpret_cast<const float4*>(gamma) + g);
-                        v[j].x = v[j].x * inv_rms * gm.x;
-                        v[j].y = v[j].y * inv_rms * gm.y;
-                        v[j].z = v[j].z * inv_rms * gm.z;
-                        v[j].w = v[j].w * inv_rms * gm.w;
-                    }
-                }
-            }
-            float amax = 0.f;
-#pragma unroll
-            for (int j = 0; j < NV; ++j)
-                amax = fmaxf(amax, fmaxf(fmaxf(fabsf(v[j].x), fabsf(v[j].y)), fmaxf(fabsf(v[j].z), fabsf(v[j].w))));
-            amax = warp_max(amax);
-            if (lane == 0) sm.shf[warp] = amax;
-            cons_sync();
-            amax = 0.f;
-#pragma unroll
-            for (int wv = 0; wv < MEGA_NW; ++wv) amax = fmaxf(amax, sm.shf[wv]);
-            const float sc = amax == 0.f ? 0.f : amax / 127.f;
-            const float inv = amax == 0.f ? 0.f : 1.0f / sc;
-            if (tid == 0) sm.sc_s[m] = sc;
-#pragma unroll
-            for (int j = 0; j < NV; ++j) {
-                const int g = g0 + tid + j * MEGA_CONS;
-                if (g < ngrp) {
-                    uint32_t wq = 0;
-                    if (amax != 0.f)
-                        wq = (uint32_t)(uint8_t)mega_quant_i8(v[j].x, inv) | ((uint32_t)(uint8_t)mega_quant_i8(v[j].y, inv) << 8) |
-                             ((uint32_t)(uint8_t)mega_quant_i8(v[j].z, inv) << 16) |
-                             ((uint32_t)(uint8_t)mega_quant_i8(v[j].w, inv) << 24);
-                    reinterpret_cast<uint32_t*>(qbuf + m * q_ld)[g] = wq;
-                }
-            }
-            cons_sync();  // shd/shf reusable; qbuf + sc_s visible
-        }
-    }
+    if (K <= 8 * MEGA_CONS) mega_prologue_rows<2>(p, sm, pro, xin, gamma, K, q_ld);
+    else mega_prologue_rows<4>(p, sm, pro, xin, gamma, K, q_ld);  // K <= 8192 (mega_plan)
 }
 
 // ---- one ternary GEMV phase (consumer side) ------------------------------------------------------
+// Ring position of a consumer warp / of the producer: slot index and phase parity, advanced chunk
+// by chunk (all parties walk the same chunk sequence).
+struct RingPos {
+    uint32_t slot, par;
+};
+__device__ __forceinline__ void ring_advance(RingPos& r, uint32_t n_slots) {
+    if (++r.slot == n_slots) {
+        r.slot = 0;
+        r.par ^= 1u;
+    }
+}
+
+// One task = 16 weight rows x 256 columns (1 KB of codes): 8 IMMAs over PRMT-decoded fragments.
+__device__ __forceinline__ void mega_task(const unsigned char* wr, int rowb, const int8_t* qk, bool tok, uint32_t lut,
+                                          int (&c)[4]) {
+    const uint4 wg = *reinterpret_cast<const uint4*>(wr);
+    const uint4 wh = *reinterpret_cast<const uint4*>(wr + 8 * rowb);
+    uint4 b[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        b[j] = make_uint4(0, 0, 0, 0);
+        if (tok) b[j] = *reinterpret_cast<const uint4*>(qk + 16 * j);
+    }
+    int c0[4] = {0, 0, 0, 0}, c1[4] = {0, 0, 0, 0};  // two independent accumulation chains
+    const uint32_t wgs[4] = {wg.x, wg.y, wg.z, wg.w};
+    const uint32_t whs[4] = {wh.x, wh.y, wh.z, wh.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const uint4 dg = decode16(wgs[j], lut);
+        const uint4 dh = decode16(whs[j], lut);
+        mma_s8_m16n8k32(c0, dg.x, dh.x, dg.y, dh.y, b[j].x, b[j].y);
+        mma_s8_m16n8k32(c1, dg.z, dh.z, dg.w, dh.w, b[j].z, b[j].w);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) c[i] = c0[i] + c1[i];
+}
+
 // epi: 0 store, 1 residual add (out may alias resid), 2 SwiGLU on interleaved (gate, up) rows
-__device__ __forceinline__ void mega_gemv_phase(const MegaParams& p, const MegaSmem& sm, const uint8_t* /*w*/, int N, int K,
-                                                int pro, const float* xin, const float* gamma, int epi, float* out,
-                                                const float* resid, uint32_t& n, int& tcount) {
+__device__ __forceinline__ void mega_gemv_phase(const MegaParams& p, const MegaSmem& sm, int N, int K, int pro,
+                                             const float* xin, const float* gamma, int epi, float* out,
+                                             const float* resid, RingPos& rp, int& tcount, int& pi) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, t = lane & 3;
+    prof_stamp(p, pi);  // phase start
     const int G = gridDim.x, cta = blockIdx.x;
-    const int NT = (N + 15) >> 4, ns = K >> 8, nch = (ns + MEGA_SLOT_STEPS - 1) / MEGA_SLOT_STEPS;
+    const int NT = (N + 15) >> 4, ns = K >> 8, nch = ns > MEGA_SLOT_STEPS ? 2 : 1;
+    const int split = nch == 2 ? (ns + 1) >> 1 : ns;  // chunk 0 = steps [0, split), chunk 1 = [split, ns)
     const int q_ld = K + 64;
-    const int first = (cta - tcount + G) % G;
-    for (int i = tid; i < MEGA_MAX_TILES * 128; i += MEGA_CONS) sm.acc[i] = 0;
+    int first = cta - tcount;  // tcount < G
+    if (first < 0) first += G;
+    int nloc = 0;
+    for (int tt = first; tt < NT; tt += G) ++nloc;
+    const uint32_t NS = (uint32_t)p.n_slots;
+    for (int i = tid; i < nloc * 128; i += MEGA_CONS) sm.acc[i] = 0;
     mega_prologue(p, sm, pro, xin, gamma, K, q_ld);  // ends with a consumer barrier
+    prof_stamp(p, pi);  // prologue done
 
+    // tasks (local tile i, step s) are dealt round-robin to the 16 warps: q = i * ns + s = warp, warp + 16, ...
     const bool tok = g < p.B;
     const int8_t* qrow = reinterpret_cast<const int8_t*>(sm.act) + g * q_ld + 64 * t;
-    int nloc = 0;
-    for (int tile = first; tile < NT; tile += G, ++nloc) {
-        int c[4] = {0, 0, 0, 0};
-        bool have = false;
-        for (int ch = 0; ch < nch; ++ch, ++n) {
-            int s0, cs;
-            chunk_range(ns, nch, ch, s0, cs);
-            const uint32_t slot = n % (uint32_t)p.n_slots;
-            mbar_wait(&sm.full[slot], (n / (uint32_t)p.n_slots) & 1u);
-            const unsigned char* base = sm.ring + (size_t)slot * MEGA_SLOT_BYTES;
-            const int rowb = cs * 64;
-            // warp w takes the steps with (tile-local step index) == w (mod MEGA_NW), offset per tile
-            int s = s0 + ((warp - (nloc * ns + s0)) % MEGA_NW + MEGA_NW) % MEGA_NW;
-            for (; s < s0 + cs; s += MEGA_NW) {
-                const unsigned char* wr = base + (size_t)g * rowb + (s - s0) * 64 + 16 * t;
-                const uint4 wg = *reinterpret_cast<const uint4*>(wr);
-                const uint4 wh = *reinterpret_cast<const uint4*>(wr + 8 * rowb);
-                const uint32_t wgs[4] = {wg.x, wg.y, wg.z, wg.w};
-                const uint32_t whs[4] = {wh.x, wh.y, wh.z, wh.w};
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    uint4 b = make_uint4(0, 0, 0, 0);
-                    if (tok) b = *reinterpret_cast<const uint4*>(qrow + s * 256 + 16 * j);
-                    const uint4 dg = decode16(wgs[j], p.lut);
-                    const uint4 dh = decode16(whs[j], p.lut);
-                    mma_s8_m16n8k32(c, dg.x, dh.x, dg.y, dh.y, b.x, b.y);
-                    mma_s8_m16n8k32(c, dg.z, dh.z, dg.w, dh.w, b.z, b.w);
-                }
-                have = true;
-            }
+    const uint32_t lut = p.lut;
+    const int nchunks = nloc * nch;
+    RingPos r = rp;
+    int ci = 0, i = 0, s = warp;
+    bool waited = false;
+    while (s >= ns) {
+        s -= ns;
+        ++i;
+    }
+    while (i < nloc) {
+        const int ch = s >= split ? 1 : 0;
+        const int ct = i * nch + ch;
+        while (ci < ct) {  // done with the chunks before this task's: hand their slots back
             __syncwarp();
-            if (lane == 0) mbar_arrive(&sm.empty[slot]);
+            if (lane == 0) mbar_arrive(&sm.empty[r.slot]);
+            ring_advance(r, NS);
+            ++ci;
+            waited = false;
         }
-        if (have) {
-            // lane (g, t): c[0] (row g, token 2t), c[1] (row g, 2t+1), c[2] (row g+8, 2t), c[3] (row g+8, 2t+1)
-            int* a = sm.acc + nloc * 128;
-            if (2 * t < p.B) {
-                atomicAdd(a + g * 8 + 2 * t, c[0]);
-                atomicAdd(a + (g + 8) * 8 + 2 * t, c[2]);
-            }
-            if (2 * t + 1 < p.B) {
-                atomicAdd(a + g * 8 + 2 * t + 1, c[1]);
-                atomicAdd(a + (g + 8) * 8 + 2 * t + 1, c[3]);
-            }
+        if (!waited) {
+            mbar_wait(&sm.full[r.slot], r.par);
+            waited = true;
+        }
+        const int s0 = ch ? split : 0, cs = ch ? ns - split : split;
+        const int rowb = cs * 64;
+        const unsigned char* wr = sm.ring + (size_t)r.slot * MEGA_SLOT_BYTES + (size_t)g * rowb + (s - s0) * 64 + 16 * t;
+        int c[4];
+        mega_task(wr, rowb, qrow + s * 256, tok, lut, c);
+        // lane (g, t): c[0] (row g, token 2t), c[1] (row g, 2t+1), c[2] (row g+8, 2t), c[3] (row g+8, 2t+1)
+        int* a = sm.acc + i * 128;
+        if (2 * t < p.B) {
+            atomicAdd(a + g * 8 + 2 * t, c[0]);
+            atomicAdd(a + (g + 8) * 8 + 2 * t, c[2]);
+        }
+        if (2 * t + 1 < p.B) {
+            atomicAdd(a + g * 8 + 2 * t + 1, c[1]);
+            atomicAdd(a + (g + 8) * 8 + 2 * t + 1, c[3]);
+        }
+        s += MEGA_NW;
+        while (s >= ns) {
+            s -= ns;
+            ++i;
         }
     }
+    while (ci < nchunks) {
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.empty[r.slot]);
+        ring_advance(r, NS);
+        ++ci;
+    }
+    rp = r;
     cons_sync();
+    prof_stamp(p, pi);  // tiles done
     // ---- epilogue ---------------------------------------------------------------------------
     if (epi == 2) {
         const int half = N >> 1;
-        for (int e = tid; e < nloc * 8 * p.B; e += MEGA_CONS) {
-            const int m = e / (nloc * 8), rr = e - m * (nloc * 8), i = rr >> 3, j = rr & 7;
-            const int row = (first + i * G) * 16 + 2 * j;
+        for (int m = 0; m < p.B; ++m)
+        for (int rr = tid; rr < nloc * 8; rr += MEGA_CONS) {
+            const int ii = rr >> 3, j = rr & 7;
+            const int row = (first + ii * G) * 16 + 2 * j;
             if (row + 1 < N) {
                 const float as = sm.sc_s[m];
-                const float v0 = __fmul_rn(as, (float)sm.acc[i * 128 + (2 * j) * 8 + m]);
-                const float v1 = __fmul_rn(as, (float)sm.acc[i * 128 + (2 * j + 1) * 8 + m]);
+                const float v0 = __fmul_rn(as, (float)sm.acc[ii * 128 + (2 * j) * 8 + m]);
+                const float v1 = __fmul_rn(as, (float)sm.acc[ii * 128 + (2 * j + 1) * 8 + m]);
                 out[(size_t)m * half + (row >> 1)] = __fmul_rn(v0 / (1.0f + expf(-v0)), v1);
             }
         }
     } else {
-        for (int e = tid; e < nloc * 16 * p.B; e += MEGA_CONS) {
-            const int m = e / (nloc * 16), rr = e - m * (nloc * 16), i = rr >> 4, r = rr & 15;
-            const int row = (first + i * G) * 16 + r;
+        for (int m = 0; m < p.B; ++m)
+        for (int rr = tid; rr < nloc * 16; rr += MEGA_CONS) {
+            const int ii = rr >> 4, rw = rr & 15;
+            const int row = (first + ii * G) * 16 + rw;
             if (row < N) {
-                const float v = __fmul_rn(sm.sc_s[m], (float)sm.acc[i * 128 + r * 8 + m]);
+                const float v = __fmul_rn(sm.sc_s[m], (float)sm.acc[ii * 128 + rw * 8 + m]);
                 const size_t oi = (size_t)m * N + row;
                 out[oi] = epi == 1 ? __fadd_rn(ld_cg_f32(resid + oi), v) : v;
             }
         }
     }
-    tcount = (tcount + NT) % G;
+    tcount += NT;
+    while (tcount >= G) tcount -= G;
+    prof_stamp(p, pi);  // epilogue done
+    if (p.mode == 1) cons_sync();  // no grid barrier follows: order the epilogue against the next phase's prologue
 }
 
 // ---- RoPE + KV append + GQA decode attention for one (head, sequence); consumer threads only ---
@@ -445,8 +502,98 @@ __device__ __forceinline__ void mega_attention(const MegaParams& p, const MegaSm
     cons_sync();  // the attention scratch may be reused by the next (head, sequence) of this CTA
 }
 
+// rows [r0, r1) of the LM head against NB token rows in shared memory; row j of the CTA goes to warp j % 16
+template <int NB>
+__device__ __forceinline__ void mega_logits_rows(const MegaParams& p, const MegaSmem& sm, const float* xn, int r0, int r1,
+                                                 int RL, RingPos& rp) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int H = p.H, V = p.V, nvec = H >> 8, nrows = r1 - r0;
+    const uint32_t NS = (uint32_t)p.n_slots;
+    int nchunks = 0;
+    for (int rr = 0; rr < nrows; rr += RL) ++nchunks;
+    float best[NB];
+    int besti[NB];
+#pragma unroll
+    for (int m = 0; m < NB; ++m) {
+        best[m] = -INFINITY;
+        besti[m] = 0x7fffffff;
+    }
+    RingPos r = rp;
+    int ci = 0, cbase = 0;  // current chunk and its first row
+    bool waited = false;
+    for (int j = warp; j < nrows; j += MEGA_NW) {
+        while (j >= cbase + RL) {  // done with the chunks before this row's
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&sm.empty[r.slot]);
+            ring_advance(r, NS);
+            ++ci;
+            cbase += RL;
+            waited = false;
+        }
+        if (!waited) {
+            mbar_wait(&sm.full[r.slot], r.par);
+            waited = true;
+        }
+        const uint4* wrow = reinterpret_cast<const uint4*>(sm.ring + (size_t)r.slot * MEGA_SLOT_BYTES + (size_t)(j - cbase) * H * 2);
+        float acc[NB];
+#pragma unroll
+        for (int m = 0; m < NB; ++m) acc[m] = 0.f;
+#pragma unroll 2
+        for (int i = 0; i < nvec; ++i) {
+            const uint4 wv = wrow[lane + 32 * i];
+            const __half2* hp = reinterpret_cast<const __half2*>(&wv);
+            float f[8];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const float2 tt = __half22float2(hp[q]);
+                f[2 * q] = tt.x;
+                f[2 * q + 1] = tt.y;
+            }
+#pragma unroll
+            for (int m = 0; m < NB; ++m) {
+                const float4 xa = *reinterpret_cast<const float4*>(xn + m * H + 8 * (lane + 32 * i));
+                const float4 xb = *reinterpret_cast<const float4*>(xn + m * H + 8 * (lane + 32 * i) + 4);
+                float a = acc[m];
+                a = fmaf(f[0], xa.x, a);
+                a = fmaf(f[1], xa.y, a);
+                a = fmaf(f[2], xa.z, a);
+                a = fmaf(f[3], xa.w, a);
+                a = fmaf(f[4], xb.x, a);
+                a = fmaf(f[5], xb.y, a);
+                a = fmaf(f[6], xb.z, a);
+                a = fmaf(f[7], xb.w, a);
+                acc[m] = a;
+            }
+        }
+        const int row = r0 + j;
+#pragma unroll
+        for (int m = 0; m < NB; ++m) {
+            const float tot = warp_sum(acc[m]);
+            if (lane == 0) p.logits[(size_t)m * V + row] = tot;
+            if (tot > best[m]) {  // a warp sees its rows in increasing order
+                best[m] = tot;
+                besti[m] = row;
+            }
+        }
+    }
+    while (ci < nchunks) {
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.empty[r.slot]);
+        ring_advance(r, NS);
+        ++ci;
+    }
+    rp = r;
+    if (lane == 0) {
+#pragma unroll
+        for (int m = 0; m < NB; ++m) {
+            sm.bestv[warp * MEGA_MAXB + m] = best[m];
+            sm.besti[warp * MEGA_MAXB + m] = besti[m];
+        }
+    }
+}
+
 // ---- LM head: final RMSNorm, tied-embedding logits (f16 table through the ring), argmax partials
-__device__ __forceinline__ void mega_logits_phase(const MegaParams& p, const MegaSmem& sm, uint32_t& n) {
+__device__ __forceinline__ void mega_logits_phase(const MegaParams& p, const MegaSmem& sm, RingPos& rp) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int H = p.H, V = p.V, G = gridDim.x, cta = blockIdx.x;
     float* xn = reinterpret_cast<float*>(sm.act);  // [B][H]
@@ -473,76 +620,11 @@ __device__ __forceinline__ void mega_logits_phase(const MegaParams& p, const Meg
     const int rpc = (V + G - 1) / G;
     const int r0 = min(V, cta * rpc), r1 = min(V, r0 + rpc);
     const int RL = MEGA_SLOT_BYTES / (H * 2);
-    float best[MEGA_MAXB];
-    int besti[MEGA_MAXB];
-#pragma unroll
-    for (int m = 0; m < MEGA_MAXB; ++m) {
-        best[m] = -INFINITY;
-        besti[m] = 0x7fffffff;
-    }
-    const int nvec = H / 256;  // uint4 (8 halves) per lane per row
-    int j = 0;                 // row index within this CTA
-    for (int rr = r0; rr < r1; rr += RL, ++n) {
-        const int nr = min(RL, r1 - rr);
-        const uint32_t slot = n % (uint32_t)p.n_slots;
-        mbar_wait(&sm.full[slot], (n / (uint32_t)p.n_slots) & 1u);
-        const unsigned char* base = sm.ring + (size_t)slot * MEGA_SLOT_BYTES;
-        for (int r = 0; r < nr; ++r, ++j) {
-            if (j % MEGA_NW != warp) continue;
-            const uint4* wrow = reinterpret_cast<const uint4*>(base + (size_t)r * H * 2);
-            float acc[MEGA_MAXB];
-#pragma unroll
-            for (int m = 0; m < MEGA_MAXB; ++m) acc[m] = 0.f;
-            for (int i = 0; i < nvec; ++i) {
-                const uint4 wv = wrow[lane + 32 * i];
-                const __half2* hp = reinterpret_cast<const __half2*>(&wv);
-                float f[8];
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const float2 tt = __half22float2(hp[q]);
-                    f[2 * q] = tt.x;
-                    f[2 * q + 1] = tt.y;
-                }
-#pragma unroll
-                for (int m = 0; m < MEGA_MAXB; ++m) {
-                    if (m < p.B) {
-                        const float4 xa = *reinterpret_cast<const float4*>(xn + m * H + 8 * (lane + 32 * i));
-                        const float4 xb = *reinterpret_cast<const float4*>(xn + m * H + 8 * (lane + 32 * i) + 4);
-                        float a = acc[m];
-                        a = fmaf(f[0], xa.x, a);
-                        a = fmaf(f[1], xa.y, a);
-                        a = fmaf(f[2], xa.z, a);
-                        a = fmaf(f[3], xa.w, a);
-                        a = fmaf(f[4], xb.x, a);
-                        a = fmaf(f[5], xb.y, a);
-                        a = fmaf(f[6], xb.z, a);
-                        a = fmaf(f[7], xb.w, a);
-                        acc[m] = a;
-                    }
-                }
-            }
-#pragma unroll
-            for (int m = 0; m < MEGA_MAXB; ++m) {
-                if (m < p.B) {
-                    const float tot = warp_sum(acc[m]);
-                    const int row = rr + r;
-                    if (lane == 0) p.logits[(size_t)m * V + row] = tot;
-                    if (tot > best[m]) {  // a warp sees its rows in increasing order
-                        best[m] = tot;
-                        besti[m] = row;
-                    }
-                }
-            }
-        }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&sm.empty[slot]);
-    }
-    if (lane == 0) {
-#pragma unroll
-        for (int m = 0; m < MEGA_MAXB; ++m) {
-            sm.bestv[warp * MEGA_MAXB + m] = best[m];
-            sm.besti[warp * MEGA_MAXB + m] = besti[m];
-        }
+    switch (p.B) {
+        case 1: mega_logits_rows<1>(p, sm, xn, r0, r1, RL, rp); break;
+        case 2: mega_logits_rows<2>(p, sm, xn, r0, r1, RL, rp); break;
+        case 3: mega_logits_rows<3>(p, sm, xn, r0, r1, RL, rp); break;
+        default: mega_logits_rows<4>(p, sm, xn, r0, r1, RL, rp); break;
     }
     cons_sync();
     if (tid < p.B) {
@@ -584,7 +666,7 @@ __device__ __forceinline__ void mega_producer(const MegaParams& p, const MegaSme
                     const uint32_t slot = n % NS;
                     unsigned char* dst = sm.ring + (size_t)slot * MEGA_SLOT_BYTES;
                     if (lane == 0) {
-                        if (n >= NS) mbar_wait(&sm.empty[slot], ((n / NS) - 1u) & 1u);
+                        if (n >= NS) mbar_wait_backoff(&sm.empty[slot], ((n / NS) - 1u) & 1u);
                         mbar_expect_tx(&sm.full[slot], (uint32_t)(nr * cs * 64));
                     }
                     __syncwarp();
@@ -607,7 +689,7 @@ __device__ __forceinline__ void mega_producer(const MegaParams& p, const MegaSme
             const int nr = min(RL, r1 - rr);
             const uint32_t slot = n % NS;
             if (lane == 0) {
-                if (n >= NS) mbar_wait(&sm.empty[slot], ((n / NS) - 1u) & 1u);
+                if (n >= NS) mbar_wait_backoff(&sm.empty[slot], ((n / NS) - 1u) & 1u);
                 const uint32_t bytes = (uint32_t)nr * (uint32_t)p.H * 2u;
                 mbar_expect_tx(&sm.full[slot], bytes);
                 bulk_g2s(sm.ring + (size_t)slot * MEGA_SLOT_BYTES, p.emb + (size_t)rr * p.H, bytes, &sm.full[slot]);
@@ -670,45 +752,52 @@ __global__ void __launch_bounds__(MEGA_THREADS, 1) decode_mega_kernel(const __gr
     // ---- consumers ------------------------------------------------------------------------------
     unsigned* ctr = p.bar + p.parity;
     unsigned target = 0;
-    uint32_t n = 0;
-    int tcount = 0;
+    RingPos rp{0u, 0u};
+    int tcount = 0, pi = 0;
     const int H = p.H, F = p.F, D = p.D, NH = p.NH, NKV = p.NKV, B = p.B;
     const int QD = NH * D, QKV = (NH + 2 * NKV) * D;
-    if (p.mode == 1) {
-        // roofline leg: the 4L ternary GEMVs with fixed int8 inputs, no dependencies, no barriers
-        for (int l = 0; l < p.L; ++l) {
-            const MegaLayer& L = sm.layers[l];
-            mega_gemv_phase(p, sm, L.wqkv, QKV, H, 0, nullptr, nullptr, 0, p.qkv, nullptr, n, tcount);
-            mega_gemv_phase(p, sm, L.wo, H, QD, 0, nullptr, nullptr, 0, p.att, nullptr, n, tcount);
-            mega_gemv_phase(p, sm, L.wgu, 2 * F, H, 0, nullptr, nullptr, 2, p.gu, nullptr, n, tcount);
-            mega_gemv_phase(p, sm, L.wdown, H, F, 0, nullptr, nullptr, 0, p.att, nullptr, n, tcount);
-            cons_sync();
+    const bool full = p.mode == 0;  // mode 1 = roofline leg: the 4L ternary GEMVs only, fixed int8 inputs, no barriers
+    int pos = 0;
+    if (full) {
+        pos = ld_cg_s32(p.pos);
+        // embed: x[b] = f32(emb[token[b]]), spread over the grid
+        for (int i = cta * MEGA_CONS + tid; i < B * H; i += G * MEGA_CONS) {
+            const int b = i / H, k = i - b * H;
+            p.x[i] = __half2float(p.emb[(size_t)ld_cg_s32(p.tokens + b) * H + k]);
         }
-        return;
+        grid_sync(ctr, target, G);
     }
-    const int pos = ld_cg_s32(p.pos);
-    // embed: x[b] = f32(emb[token[b]]), spread over the grid
-    for (int i = cta * MEGA_CONS + tid; i < B * H; i += G * MEGA_CONS) {
-        const int b = i / H, k = i - b * H;
-        p.x[i] = __half2float(p.emb[(size_t)ld_cg_s32(p.tokens + b) * H + k]);
-    }
-    grid_sync(ctr, target, G);
+    // ONE call site per phase kind (the bodies are inlined once): op 0 qkv, 1 attention, 2 o, 3 gate/up, 4 down
     for (int l = 0; l < p.L; ++l) {
         const MegaLayer& L = sm.layers[l];
-        const size_t kvoff = (size_t)l * B * NKV * p.max_ctx * D;
-        mega_gemv_phase(p, sm, L.wqkv, QKV, H, 2, p.x, L.attn_norm, 0, p.qkv, nullptr, n, tcount);
-        grid_sync(ctr, target, G);
-        for (int task = cta; task < NH * B; task += G) mega_attention(p, sm, task % NH, task / NH, pos, p.kc + kvoff, p.vc + kvoff);
-        grid_sync(ctr, target, G);
-        mega_gemv_phase(p, sm, L.wo, H, QD, 1, p.att, nullptr, 1, p.x, p.x, n, tcount);
-        grid_sync(ctr, target, G);
-        mega_gemv_phase(p, sm, L.wgu, 2 * F, H, 2, p.x, L.ffn_norm, 2, p.gu, nullptr, n, tcount);
-        grid_sync(ctr, target, G);
-        mega_gemv_phase(p, sm, L.wdown, H, F, 1, p.gu, nullptr, 1, p.x, p.x, n, tcount);
-        grid_sync(ctr, target, G);
+        for (int op = 0; op < 5; ++op) {
+            if (op == 1) {
+                if (!full) continue;
+                const size_t kvoff = (size_t)l * B * NKV * p.max_ctx * D;
+                prof_stamp(p, pi);  // attention start
+                for (int task = cta; task < NH * B; task += G)
+                    mega_attention(p, sm, task % NH, task / NH, pos, p.kc + kvoff, p.vc + kvoff);
+                prof_stamp(p, pi);  // attention done
+                grid_sync(ctr, target, G);
+                continue;
+            }
+            const int N = op == 0 ? QKV : (op == 3 ? 2 * F : H);
+            const int K = op == 2 ? QD : (op == 4 ? F : H);
+            const int pro = !full ? 0 : ((op == 0 || op == 3) ? 2 : 1);
+            const float* xin = op == 2 ? p.att : (op == 4 ? p.gu : p.x);
+            const float* gamma = op == 0 ? L.attn_norm : L.ffn_norm;
+            const int epi = op == 3 ? 2 : ((full && (op == 2 || op == 4)) ? 1 : 0);
+            float* out = op == 0 ? p.qkv : (op == 3 ? p.gu : p.x);
+            mega_gemv_phase(p, sm, N, K, pro, xin, gamma, epi, out, p.x, rp, tcount, pi);
+            if (full) grid_sync(ctr, target, G);
+        }
     }
-    mega_logits_phase(p, sm, n);
+    if (!full) return;
+    prof_stamp(p, pi);
+    mega_logits_phase(p, sm, rp);
+    prof_stamp(p, pi);
     grid_sync(ctr, target, G);
+    prof_stamp(p, pi);
     // greedy argmax over the per-CTA partials (lowest index on ties); feed the token back, advance
     if (cta == 0 && warp < B) {
         const int b = warp, lane = tid & 31;

@@ -1,0 +1,37 @@
+// decode_mega.h -- parameters of the persistent decode-step kernel (decode_mega.cu), shared with
+// the model object in decode.cu.
+#pragma once
+#include "common.cuh"
+
+namespace b200 {
+
+struct MegaLayer {
+    const uint8_t *wqkv, *wo, *wgu, *wdown;  // device-layout code planes [N, K/4]
+    const float *attn_norm, *ffn_norm;
+};
+
+struct MegaParams {
+    const MegaLayer* layers;
+    const __half* emb;
+    const float *final_norm, *rope_cos, *rope_sin;
+    float *kc, *vc;
+    int *pos, *tokens, *next;
+    float *x, *qkv, *att, *gu, *logits, *part_val;
+    int* part_idx;
+    const int8_t* q_fixed;   // mode 1: fixed int8 rows [B, max(H, F, NH*D)]
+    const float* s_fixed;    // mode 1: their scales
+    unsigned* bar;           // [2] grid-barrier counters, used alternately per launch
+    int parity;
+    int L, B, H, F, NH, NKV, D, V, max_ctx;
+    float eps;
+    uint32_t lut;
+    int mode;                // 0 = full decode step; 1 = the 4L ternary GEMVs only, no dependencies
+    int n_slots, act_bytes, attn_floats;
+    unsigned long long* prof;  // optional [16384] globaltimer stamps of CTA 0 (diagnostics), or nullptr
+};
+
+// decode_mega.cu
+size_t mega_plan(MegaParams* p, int num_sms);  // 0 = shape not covered
+int launch_decode_mega(const MegaParams& p, size_t smem, int num_sms, cudaStream_t st);
+
+}  // namespace b200

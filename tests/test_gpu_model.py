@@ -86,5 +86,5 @@ def test_device_loop_equals_host_loop(b200, oracle):
     assert np.array_equal(gm.get_tokens(), seq_host[-1])
     assert gm.launches_per_step > 0
     ms, n = gm.time_linears(3)
-    assert n == 4 * shape.n_layers and ms > 0
+    assert n in (1, 4 * shape.n_layers) and ms > 0  # 1 = the persistent one-kernel step
     gm.close()
