@@ -246,6 +246,45 @@ def test_linear_qk256_model_shapes(ctx, b200, oracle, rows, cols, M):
     assert torch.equal(y2, y)
 
 
+# ---- M > 16: the tcgen05 kind::i8 GEMM (gemm_tcgen05.cu); same bit-exact bar as the GEMV -------
+@pytest.mark.parametrize("rows,cols,M", [
+    (128, 128, 128), (128, 256, 17), (8, 256, 64), (130, 1024, 129), (256, 512, 300), (100, 1024, 33),
+    (640, 2560, 64), (3840, 2560, 128), (2560, 6912, 64), (6912, 2560, 130), (2560, 2560, 512), (1024, 14336, 64),
+])
+def test_linear_qk256_gemm_tcgen05(ctx, b200, oracle, rows, cols, M):
+    qs, q, s = _qk256_case(oracle, rows, cols, M, rows + cols + M)
+    w = ctx.weight(qs, b200.LAYOUT_QK256, rows, cols)
+    y, acc = ctx.linear_i8(w, dev(q), dev(s), want_acc=True)
+    racc, ry = oracle.linear_qk256_i8(qs, rows, cols, q, s)
+    assert np.array_equal(acc.cpu().numpy(), racc)
+    assert np.array_equal(y.cpu().numpy(), ry)
+    y2 = ctx.linear_i8(w, dev(q), dev(s))
+    assert torch.equal(y2, y)
+
+
+@pytest.mark.parametrize("lut_name", ["MAP_B", "MAP_C"])
+def test_linear_qk256_gemm_other_code_maps(ctx, b200, oracle, lut_name):
+    rows, cols, M = 192, 1024, 70
+    qs, q, s = _qk256_case(oracle, rows, cols, M, 9)
+    lut = getattr(oracle, lut_name)
+    w = ctx.weight(qs, b200.LAYOUT_QK256, rows, cols, lut=lut)
+    _, acc = ctx.linear_i8(w, dev(q), dev(s), want_acc=True)
+    racc, _ = oracle.linear_qk256_i8(qs, rows, cols, q, s, lut)
+    assert np.array_equal(acc.cpu().numpy(), racc)
+
+
+def test_linear_qk256_gemm_extreme_activations(ctx, b200, oracle):
+    # every activation +-127 and every code +-2 over K = 14336: |acc| = 3 641 344, the F5 bound, in int32 TMEM
+    rows, cols, M = 128, 14336, 64
+    qs = np.where(np.arange(rows * cols // 4) % 2 == 0, 0xFF, 0x00).astype(np.uint8)
+    q = np.where(np.arange(M * cols).reshape(M, cols) % 3 == 0, -127, 127).astype(np.int8)
+    s = np.ones(M, np.float32)
+    w = ctx.weight(qs, b200.LAYOUT_QK256, rows, cols)
+    _, acc = ctx.linear_i8(w, dev(q), dev(s), want_acc=True)
+    racc, _ = oracle.linear_qk256_i8(qs, rows, cols, q, s)
+    assert np.array_equal(acc.cpu().numpy(), racc)
+
+
 @pytest.mark.parametrize("lut_name", ["MAP_B", "MAP_C"])
 def test_linear_qk256_other_code_maps(ctx, b200, oracle, lut_name):
     rows, cols, M = 64, 1024, 3
