@@ -585,3 +585,18 @@ def test_splitmix_generator_is_stable(oracle):
     # fixed bytes so the CPU and GPU harnesses can regenerate identical inputs
     assert oracle.fill_bytes(8, 0).tolist() == list(int(0xE220A8397B1DCDAF).to_bytes(8, "little"))
     assert oracle.fill_bytes(16, 1234567)[8:].tolist() == oracle.fill_bytes(24, 1234567)[8:16].tolist()
+
+
+def test_round_half_away_trick():
+    """The device quantiser rounds with trunc(y + copysign(0.5 - 2^-25, y)) (decode_mega.cu,
+    mega_quant_i8): it must equal round-half-away-from-zero (Rust f32::round, cpu/quantize.rs:44)
+    for EVERY float with |y| <= 130 -- checked exhaustively, both signs."""
+    half_m = np.nextafter(np.float32(0.5), np.float32(0))
+    hi = int(np.float32(130.0).view(np.uint32))
+    step = 1 << 24
+    for lo in range(0, hi + 1, step):
+        y = np.arange(lo, min(lo + step, hi + 1), dtype=np.uint32).view(np.float32)
+        for ys in (y, -y):
+            ref = np.sign(ys) * np.floor(np.abs(ys).astype(np.float64) + 0.5)
+            got = np.trunc((ys + np.copysign(half_m, ys)).astype(np.float32))
+            assert np.array_equal(ref.astype(np.float32), got)

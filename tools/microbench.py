@@ -58,6 +58,7 @@ def main():
     ap.add_argument("--layouts", default="qk256,bitnet32")
     ap.add_argument("--iters", type=int, default=200)
     ap.add_argument("--l2mb", type=int, default=300)
+    ap.add_argument("--no-actquant", action="store_true")
     args = ap.parse_args()
     ctx = b2.Context(0)
     peak = 6548.5
@@ -80,10 +81,12 @@ def main():
                 alg = wbytes + M * cols + 4 * M + 4 * M * rows
                 print(json.dumps({"kernel": "linear_i8", "layout": lname, "shape": sname, "N": rows, "K": cols,
                                   "M": M, "us": round(us, 3), "alg_bytes": alg,
-                                  "GBs": round(alg / us / 1e3, 1), "frac_of_measured_peak": round(alg / us / 1e3 / peak, 4),
+                                  "TOPS": round(2.0 * M * rows * cols / us / 1e6, 1), "GBs": round(alg / us / 1e3, 1), "frac_of_measured_peak": round(alg / us / 1e3 / peak, 4),
                                   "weight_copies": len(ws)}), flush=True)
             del ws
             torch.cuda.empty_cache()
+    if args.no_actquant:
+        return
     # act-quant
     for K in (2560, 6912):
         for M in (1, 16, 4096):
