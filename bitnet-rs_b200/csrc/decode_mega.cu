@@ -61,7 +61,7 @@ __device__ __forceinline__ void mma_s8_m16n8k32(int (&c)[4], uint32_t a0, uint32
 }
 // q = clamp(round_half_away(v * inv), -127, 127); NaN -> 0 (Rust `as i8`). Round-half-away as
 // trunc(y + copysign(0.5 - 2^-25, y)): identical to roundf(y) for every float |y| <= 200 (checked
-// exhaustively on the CPU, tests/test_oracle_golden.py::test_round_half_away_trick), 4 instructions
+// exhaustively on the CPU, tests: test_round_half_away_trick), 4 instructions
 // instead of ~12; cvt.rzi maps NaN to 0 and saturates +-inf, the clamp does the rest.
 __device__ __forceinline__ int mega_quant_i8(float v, float inv) {
     const float y = v * inv;
