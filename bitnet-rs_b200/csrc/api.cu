@@ -268,6 +268,8 @@ void bitnet_b200_ctx_destroy(bitnet_b200_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     if (ctx->workspace) cudaFree(ctx->workspace);
+    if (ctx->gemm_scratch) cudaFree(ctx->gemm_scratch);
+    if (ctx->gemm_counters) cudaFree(ctx->gemm_counters);
     delete ctx;
 }
 

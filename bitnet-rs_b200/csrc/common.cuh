@@ -47,6 +47,8 @@ struct bitnet_b200_ctx {
     cudaStream_t stream = nullptr;
     int num_sms = 148;
     int* workspace = nullptr;  // small device scratch (tile counters etc.)
+    int32_t* gemm_scratch = nullptr;  // split-K int32 partials of the tcgen05 GEMM (gemm_tcgen05.cu)
+    int* gemm_counters = nullptr;     // split-K ticket counters, zero between launches
 };
 
 struct bitnet_b200_weight {

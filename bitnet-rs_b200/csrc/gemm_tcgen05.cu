@@ -1,6 +1,6 @@
-// gemm_tcgen05.cu -- the batched / prefill regime of the ternary linear (M > 16): a dense
+// gemm_tcgen05.cu -- the batched / prefill regime of the ternary linear (M > 8): a dense
 // contraction on the 5th-generation tensor cores, tcgen05.mma kind::i8 with the int32 accumulator
-// in tensor memory (TMEM). QK256 layout.
+// in tensor memory (TMEM), operands fed by TMA. QK256 layout.
 //
 // Replaces, for device-resident packed weights and int8 activations, what the reference does with
 // an f32 candle GEMM over load-time-dequantised weights (crates/bitnet-models/src/formats/gguf/
@@ -9,39 +9,62 @@
 // quantized_matmul.rs:282-303) for the packed layout. Result: acc[m,n] = sum_k q[m,k]*LUT[code(n,k)]
 // in int32 -- bit-identical to gemv_qk256 on the same integers -- and y = act_scale[m] * acc.
 //
-// Shape of the kernel (one CTA = one 128 x 128 output tile, 2 CTAs resident per SM):
-//   * warps 0-3 (128 threads) are the operand producers. Thread t owns weight row n0+t and
-//     activation row m0+t of the tile: per 128-wide K block it reads its row's 32 bytes of packed
-//     codes, pushes them through the 4-entry int8 LUT (one PRMT per four weights, common.cuh)
-//     and writes 128 int8 into shared memory in the canonical K-major SWIZZLE_128B layout that
-//     the UMMA descriptor names; the int8 activation row goes next to it, same layout.
-//     The 2-bit weights are expanded ONCE per CTA and reused by all 128 token rows of the tile.
-//   * warp 4 is the MMA issuer: one elected lane waits for a stage (mbarrier), issues four
-//     tcgen05.mma (K = 32 each) accumulating into TMEM, and releases the stage with
-//     tcgen05.commit -> mbarrier. 3-stage ring, 32 KB per stage.
-//   * the producer warps then become the epilogue: tcgen05.ld (32 lanes x 32 columns per warp
-//     and instruction) -> act_scale * float(acc) -> 128-byte row segments of y.
+// Shape of the kernel (persistent, one CTA per SM, 15 warps with fixed roles):
+//   * the WEIGHTS are the A operand (UMMA M = 128 weight rows per tile), the TOKENS the B operand
+//     (UMMA N = BN = up to 256 tokens): one expansion of a 128 x 128 block of 2-bit codes feeds
+//     128 x BN x 128 MACs, and the accumulator sits in TMEM as [weight row = lane][token = column],
+//     so the epilogue's stores of y[m, n0 .. n0+31] are 128-byte coalesced per warp;
+//   * warp 0  : TMA producer of the int8 token tiles  (2-D tensor map over q[M,K], box 128 B x BN rows,
+//               SWIZZLE_128B; rows beyond M are zero-filled by the TMA unit -> ragged M costs nothing);
+//   * warp 14 : TMA producer of the packed 2-bit codes (box 128 B x 128 rows = 512 k of 128 rows, 16 KB,
+//               SWIZZLE_128B), its own deeper ring: in the small-M regime this is the HBM stream;
+//   * warps 6-13: decoders. Thread = (weight row, 64-k half): one conflict-free 128-bit shared load of
+//               packed codes, four PRMT LUT decodes (common.cuh), four 128-bit stores into the
+//               canonical K-major SWIZZLE_128B operand tile, fence.proxy.async, mbarrier arrive;
+//   * warp 1  : MMA issuer: one elected lane issues four tcgen05.mma (K = 32 each) per 128-k block and
+//               frees the stage with tcgen05.commit -> mbarrier; two TMEM accumulator stages
+//               (2 x 256 columns) so the epilogue of tile i overlaps the main loop of tile i+1;
+//   * warps 2-5: epilogue: tcgen05.ld (32 lanes x 32 columns) -> act_scale * float(acc) -> y.
+//   * small M (few output tiles): split-K over CTAs so that all 148 SMs stream weights; int32
+//     partials go to an L2-resident scratch, the last CTA of a tile (ticket counter) sums them --
+//     integer addition, so the result is independent of arrival order and stays bit-exact.
+#include <cuda.h>
+
+#include <mutex>
+
 #include "common.cuh"
 
 namespace b200 {
 
-constexpr int GEMM_BM = 128, GEMM_BN = 128, GEMM_BK = 128;  // int8 elements; BK = one 128-byte swizzle row
-constexpr int GEMM_STAGES = 3;
-constexpr int GEMM_TILE_BYTES = GEMM_BM * GEMM_BK;          // 16 KB per operand per stage
-constexpr int GEMM_THREADS = 160;                           // 4 producer/epilogue warps + 1 MMA warp
-constexpr int GEMM_SMEM = GEMM_STAGES * 2 * GEMM_TILE_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/;
+constexpr int G_ROWS = 128;               // weight rows per tile (UMMA M)
+constexpr int G_BK = 128;                 // int8 k per block = one 128-byte swizzle row
+constexpr int G_PKQ = 4;                  // k-blocks per packed-code stage (128 B of codes per row)
+constexpr int G_NAB = 4;                  // operand stages (decoded A + token B)
+constexpr int G_A_BYTES = G_ROWS * G_BK;  // 16 KB decoded weights per stage
+constexpr int G_PK_BYTES = G_ROWS * 128;  // 16 KB packed codes per stage
+constexpr int G_THREADS = 15 * 32;
+constexpr int G_DEC_WARP0 = 6, G_DEC_THREADS = 256;
+constexpr int G_BAR_BYTES = 512;
+constexpr size_t G_SCRATCH_BYTES = 40u << 20;  // split-K partials (ctx-owned)
+constexpr int G_MAX_TILE_COUNTERS = 8192;
 
 struct GemmParams {
-    const uint8_t* codes;   // [N, K/4] device layout
-    const int8_t* q;        // [M, K]
-    const float* act_scale; // [M]
-    float* y;               // [M, N]
-    int32_t* acc_out;       // optional [M, N]
+    const float* act_scale;  // [M]
+    float* y;                // [M, N]
+    int32_t* acc_out;        // optional [M, N]
+    int32_t* scratch;        // split-K partials
+    int* counters;           // split-K tickets, zero between launches
     uint32_t lut;
     int M, N, K;
+    int BN;        // tokens per tile (multiple of 16, <= 256)
+    int n_rt;      // weight-row tiles
+    int n_mt;      // token tiles
+    int S;         // split-K factor
+    int n_pk;      // packed-code stages
+    int n_items;   // n_rt * n_mt * S
 };
 
-// ---- tcgen05 / TMEM PTX ---------------------------------------------------------------------
+// ---- tcgen05 / TMEM / TMA PTX -----------------------------------------------------------------
 __device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t ncols) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(ncols)
                  : "memory");
@@ -80,6 +103,16 @@ __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&r)[32])
         : "memory");
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
+// 2-D tiled TMA load: box at (c0 = innermost byte coordinate, c1 = row) -> shared, completes on mbar
+__device__ __forceinline__ void tma_load_2d(void* dst_smem, const CUtensorMap* tm, int c0, int c1, void* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(smem_u32(dst_smem)), "l"(tm), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* tm) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(tm) : "memory");
+}
 
 // Shared-memory matrix descriptor of a K-major operand tile in the canonical SWIZZLE_128B layout
 // (rows of 128 bytes, 8-row atoms of 1024 bytes, 16-byte chunk index XOR (row & 7)):
@@ -95,158 +128,365 @@ __device__ __forceinline__ uint32_t umma_idesc_i8(int m, int n) {
     return (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
 
-// byte offset of 16-byte chunk c (0..7) of row r inside a [rows x 128 B] SWIZZLE_128B tile
-__device__ __forceinline__ uint32_t sw128_off(int r, int c) {
-    return (uint32_t)((r >> 3) * 1024 + (r & 7) * 128 + ((c ^ (r & 7)) << 4));
+// running ring position -> (stage, parity)
+struct Ring {
+    uint32_t n, stages;
+    __device__ __forceinline__ Ring(uint32_t s) : n(0), stages(s) {}
+    __device__ __forceinline__ uint32_t stage() const { return n % stages; }
+    __device__ __forceinline__ uint32_t parity() const { return (n / stages) & 1u; }
+    __device__ __forceinline__ void next() { ++n; }
+};
+
+struct Item {
+    int row0, m0, kb0, kb1, tile, split;
+};
+__device__ __forceinline__ Item item_of(const GemmParams& p, int it) {
+    Item r;
+    r.split = it % p.S;
+    r.tile = it / p.S;
+    const int rt = r.tile % p.n_rt, mt = r.tile / p.n_rt;
+    const int nkb = p.K / G_BK;
+    r.row0 = rt * G_ROWS;
+    r.m0 = mt * p.BN;
+    r.kb0 = (int)(((long long)nkb * r.split) / p.S);
+    r.kb1 = (int)(((long long)nkb * (r.split + 1)) / p.S);
+    return r;
 }
 
-__global__ void __launch_bounds__(GEMM_THREADS) gemm_i8_tcgen05_kernel(const GemmParams p) {
+__global__ void __launch_bounds__(G_THREADS, 1)
+gemm_i8_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_codes, const __grid_constant__ CUtensorMap tm_q,
+                       const GemmParams p) {
     extern __shared__ unsigned char gsm_raw[];
     // 1024-byte alignment: the swizzle pattern is a function of the absolute shared address
-    unsigned char* tiles = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(gsm_raw) + 1023) & ~(uintptr_t)1023);
-    uint64_t* full = reinterpret_cast<uint64_t*>(tiles + GEMM_STAGES * 2 * GEMM_TILE_BYTES);  // [STAGES]
-    uint64_t* empty = full + GEMM_STAGES;                                                       // [STAGES]
-    uint64_t* tmem_full = empty + GEMM_STAGES;                                                  // [1]
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+    unsigned char* base = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(gsm_raw) + 1023) & ~(uintptr_t)1023);
+    const uint32_t ab_stage_bytes = (uint32_t)G_A_BYTES + (uint32_t)p.BN * 128u;
+    unsigned char* pk_base = base + (size_t)G_NAB * ab_stage_bytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(pk_base + (size_t)p.n_pk * G_PK_BYTES);
+    uint64_t* pk_full = bars;            // [8]
+    uint64_t* pk_empty = bars + 8;       // [8]
+    uint64_t* a_full = bars + 16;        // [4]
+    uint64_t* b_full = bars + 20;        // [4]
+    uint64_t* ab_empty = bars + 24;      // [4]
+    uint64_t* tmem_full = bars + 28;     // [2]
+    uint64_t* tmem_empty = bars + 30;    // [2]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 32);
+    volatile int* ticket_s = reinterpret_cast<volatile int*>(tmem_slot + 1);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int n0 = blockIdx.x * GEMM_BN, m0 = blockIdx.y * GEMM_BM;
-    const int nkb = p.K / GEMM_BK;
 
     if (tid == 0) {
-        for (int s = 0; s < GEMM_STAGES; ++s) {
-            mbar_init(&full[s], 128);  // every producer thread arrives
-            mbar_init(&empty[s], 1);   // one tcgen05.commit
+        for (int s = 0; s < 8; ++s) {
+            mbar_init(&pk_full[s], 1);
+            mbar_init(&pk_empty[s], G_DEC_THREADS);
         }
-        mbar_init(tmem_full, 1);
+        for (int s = 0; s < G_NAB; ++s) {
+            mbar_init(&a_full[s], G_DEC_THREADS);
+            mbar_init(&b_full[s], 1);
+            mbar_init(&ab_empty[s], 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&tmem_full[s], 1);
+            mbar_init(&tmem_empty[s], 128);
+        }
         mbar_fence_init();
     }
-    if (warp == 4) tmem_alloc(tmem_slot, GEMM_BN);  // 128 columns x 128 lanes of int32
+    if (warp == 0 && lane == 0) tma_prefetch_desc(&tm_q);
+    if (warp == 14 && lane == 0) tma_prefetch_desc(&tm_codes);
+    if (warp == 1) tmem_alloc(tmem_slot, 512);  // two accumulator stages of 256 columns
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_d = *tmem_slot;
 
-    if (warp < 4) {
-        // ================= producers: thread t fills row t of the B (weights) and A (activations) tiles
-        const int n = n0 + tid, m = m0 + tid;
-        const bool nv = n < p.N, mv = m < p.M;
-        const uint8_t* wrow = p.codes + (size_t)(nv ? n : 0) * (size_t)(p.K >> 2);
-        const int8_t* arow = p.q + (size_t)(mv ? m : 0) * (size_t)p.K;
-        for (int kb = 0; kb < nkb; ++kb) {
-            const int s = kb % GEMM_STAGES;
-            if (kb >= GEMM_STAGES) mbar_wait(&empty[s], (uint32_t)((kb / GEMM_STAGES) - 1) & 1u);
-            unsigned char* a_tile = tiles + (size_t)s * 2 * GEMM_TILE_BYTES;
-            unsigned char* b_tile = a_tile + GEMM_TILE_BYTES;
-            // weights: 128 codes = 32 bytes -> 128 int8
-            uint4 w0 = make_uint4(0, 0, 0, 0), w1 = w0;
-            if (nv) {
-                w0 = ldg_nc_u128(wrow + (size_t)kb * 32);
-                w1 = ldg_nc_u128(wrow + (size_t)kb * 32 + 16);
-            }
-            uint4 av[8];
-#pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                av[c] = make_uint4(0, 0, 0, 0);
-                if (mv) av[c] = ldg_nc_u128(arow + (size_t)kb * GEMM_BK + c * 16);
-            }
-            const uint32_t ws[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
-#pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                uint4 d = make_uint4(0, 0, 0, 0);
-                if (nv) d = decode16(ws[c], p.lut);
-                *reinterpret_cast<uint4*>(b_tile + sw128_off(tid, c)) = d;
-            }
-#pragma unroll
-            for (int c = 0; c < 8; ++c) *reinterpret_cast<uint4*>(a_tile + sw128_off(tid, c)) = av[c];
-            fence_proxy_async_smem();  // generic-proxy stores -> visible to the tensor core (async proxy)
-            mbar_arrive(&full[s]);
-        }
-        // ================= epilogue: TMEM -> registers -> y
-        mbar_wait(tmem_full, 0);
-        tc_fence_after();
-        const float as = mv ? p.act_scale[m] : 0.f;
-        for (int c0 = 0; c0 < GEMM_BN; c0 += 32) {
-            uint32_t r[32];
-            tmem_ld_32x32(tmem_d + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, r);
-            if (mv) {
-                float* yr = p.y + (size_t)m * p.N + n0 + c0;
-                int32_t* ar = p.acc_out ? p.acc_out + (size_t)m * p.N + n0 + c0 : nullptr;
-                if (n0 + c0 + 32 <= p.N && ((reinterpret_cast<uintptr_t>(yr) & 15) == 0)) {
-#pragma unroll
-                    for (int j = 0; j < 32; j += 4)
-                        *reinterpret_cast<float4*>(yr + j) =
-                            make_float4(__fmul_rn(as, (float)(int)r[j]), __fmul_rn(as, (float)(int)r[j + 1]),
-                                        __fmul_rn(as, (float)(int)r[j + 2]), __fmul_rn(as, (float)(int)r[j + 3]));
-                } else {
-#pragma unroll
-                    for (int j = 0; j < 32; ++j)
-                        if (n0 + c0 + j < p.N) yr[j] = __fmul_rn(as, (float)(int)r[j]);
-                }
-                if (ar) {
-#pragma unroll
-                    for (int j = 0; j < 32; ++j)
-                        if (n0 + c0 + j < p.N) ar[j] = (int)r[j];
+    if (warp == 0) {
+        // ================= TMA producer: int8 token tiles (B operand) =================
+        if (lane == 0) {
+            Ring ab(G_NAB);
+            const uint32_t bytes = (uint32_t)p.BN * 128u;
+            for (int it = blockIdx.x; it < p.n_items; it += gridDim.x) {
+                const Item w = item_of(p, it);
+                for (int kb = w.kb0; kb < w.kb1; ++kb) {
+                    const uint32_t s = ab.stage();
+                    mbar_wait(&ab_empty[s], ab.parity() ^ 1u);
+                    mbar_expect_tx(&b_full[s], bytes);
+                    tma_load_2d(base + (size_t)s * ab_stage_bytes + G_A_BYTES, &tm_q, kb * G_BK, w.m0, &b_full[s]);
+                    ab.next();
                 }
             }
         }
-        tc_fence_before();
-    } else {
-        // ================= MMA issuer (warp 4): one elected lane
-        const uint32_t idesc = umma_idesc_i8(GEMM_BM, GEMM_BN);
-        for (int kb = 0; kb < nkb; ++kb) {
-            const int s = kb % GEMM_STAGES;
-            mbar_wait(&full[s], (uint32_t)(kb / GEMM_STAGES) & 1u);
+    } else if (warp == 14) {
+        // ================= TMA producer: packed 2-bit codes (the HBM stream) =================
+        if (lane == 0) {
+            Ring pk((uint32_t)p.n_pk);
+            for (int it = blockIdx.x; it < p.n_items; it += gridDim.x) {
+                const Item w = item_of(p, it);
+                for (int kb = w.kb0; kb < w.kb1; kb += G_PKQ) {
+                    const uint32_t s = pk.stage();
+                    mbar_wait(&pk_empty[s], pk.parity() ^ 1u);
+                    mbar_expect_tx(&pk_full[s], (uint32_t)G_PK_BYTES);
+                    tma_load_2d(pk_base + (size_t)s * G_PK_BYTES, &tm_codes, kb * (G_BK / 4), w.row0, &pk_full[s]);
+                    pk.next();
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ================= MMA issuer =================
+        const uint32_t idesc = umma_idesc_i8(G_ROWS, p.BN);
+        Ring ab(G_NAB);
+        uint32_t nacc = 0;
+        for (int it = blockIdx.x; it < p.n_items; it += gridDim.x, ++nacc) {
+            const Item w = item_of(p, it);
+            const uint32_t acc = nacc & 1u;
+            mbar_wait(&tmem_empty[acc], ((nacc >> 1) & 1u) ^ 1u);
             tc_fence_after();
-            if (lane == 0) {
-                const uint32_t a_addr = smem_u32(tiles + (size_t)s * 2 * GEMM_TILE_BYTES);
-                const uint64_t adesc = umma_desc_sw128(a_addr), bdesc = umma_desc_sw128(a_addr + GEMM_TILE_BYTES);
+            const uint32_t d_addr = tmem_d + acc * 256u;
+            for (int kb = w.kb0; kb < w.kb1; ++kb) {
+                const uint32_t s = ab.stage();
+                mbar_wait(&a_full[s], ab.parity());
+                mbar_wait(&b_full[s], ab.parity());
+                tc_fence_after();
+                if (lane == 0) {
+                    const uint32_t a_addr = smem_u32(base + (size_t)s * ab_stage_bytes);
+                    const uint64_t adesc = umma_desc_sw128(a_addr), bdesc = umma_desc_sw128(a_addr + G_A_BYTES);
 #pragma unroll
-                for (int k = 0; k < GEMM_BK / 32; ++k)  // +32 bytes along K = +2 in the (>>4) address field
-                    umma_i8(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (uint32_t)(kb | k));
-                umma_commit(&empty[s]);                       // stage reusable once these MMAs have read it
-                if (kb == nkb - 1) umma_commit(tmem_full);    // accumulator complete
+                    for (int k = 0; k < G_BK / 32; ++k)  // +32 bytes along K = +2 in the (>>4) address field
+                        umma_i8(d_addr, adesc + 2 * k, bdesc + 2 * k, idesc, (uint32_t)((kb - w.kb0) | k));
+                    umma_commit(&ab_empty[s]);                     // stage reusable once these MMAs have read it
+                    if (kb == w.kb1 - 1) umma_commit(&tmem_full[acc]);  // accumulator complete
+                }
+                __syncwarp();
+                ab.next();
             }
-            __syncwarp();
         }
-        tc_fence_before();
+    } else if (warp >= G_DEC_WARP0 && warp < G_DEC_WARP0 + 8) {
+        // ================= decoders: packed codes -> int8 A tile (SWIZZLE_128B, K-major) =================
+        const int dw = warp - G_DEC_WARP0;
+        const int r = dw * 16 + (lane & 15);   // weight row of the tile; a quarter-warp = 8 consecutive rows
+        const int half = lane >> 4;            // which 64 k of the 128-k block
+        const uint32_t rx = (uint32_t)(r & 7);
+        const uint32_t row_off = (uint32_t)r * 128u;
+        uint32_t a_off[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) a_off[j] = row_off + ((((uint32_t)(half * 4 + j)) ^ rx) << 4);
+        Ring ab(G_NAB), pk((uint32_t)p.n_pk);
+        for (int it = blockIdx.x; it < p.n_items; it += gridDim.x) {
+            const Item w = item_of(p, it);
+            for (int kb = w.kb0; kb < w.kb1; ++kb) {
+                const int rel = (kb - w.kb0) & (G_PKQ - 1);
+                const uint32_t ps = pk.stage();
+                if (rel == 0) mbar_wait(&pk_full[ps], pk.parity());
+                const uint4 cw = *reinterpret_cast<const uint4*>(pk_base + (size_t)ps * G_PK_BYTES + row_off +
+                                                                 ((((uint32_t)(2 * rel + half)) ^ rx) << 4));
+                const uint4 d0 = decode16(cw.x, p.lut), d1 = decode16(cw.y, p.lut);
+                const uint4 d2 = decode16(cw.z, p.lut), d3 = decode16(cw.w, p.lut);
+                const uint32_t s = ab.stage();
+                mbar_wait(&ab_empty[s], ab.parity() ^ 1u);
+                unsigned char* a_tile = base + (size_t)s * ab_stage_bytes;
+                *reinterpret_cast<uint4*>(a_tile + a_off[0]) = d0;
+                *reinterpret_cast<uint4*>(a_tile + a_off[1]) = d1;
+                *reinterpret_cast<uint4*>(a_tile + a_off[2]) = d2;
+                *reinterpret_cast<uint4*>(a_tile + a_off[3]) = d3;
+                fence_proxy_async_smem();  // generic-proxy stores -> visible to the tensor core (async proxy)
+                mbar_arrive(&a_full[s]);
+                ab.next();
+                if (rel == G_PKQ - 1 || kb == w.kb1 - 1) {
+                    mbar_arrive(&pk_empty[ps]);
+                    pk.next();
+                }
+            }
+        }
+    } else {
+        // ================= epilogue (warps 2-5): TMEM -> registers -> y =================
+        const int qd = warp & 3;                 // TMEM lane quarter this warp may read
+        const int nl = qd * 32 + lane;           // weight row within the tile
+        const int etid = (warp - 2) * 32 + lane; // 0..127
+        uint32_t nacc = 0;
+        for (int it = blockIdx.x; it < p.n_items; it += gridDim.x, ++nacc) {
+            const Item w = item_of(p, it);
+            const uint32_t acc = nacc & 1u;
+            const int n = w.row0 + nl;
+            const bool nv = n < p.N;
+            const int mv = min(p.BN, p.M - w.m0);  // valid token columns of this tile
+            mbar_wait(&tmem_full[acc], (nacc >> 1) & 1u);
+            tc_fence_after();
+            const uint32_t t_addr = tmem_d + ((uint32_t)(qd * 32) << 16) + acc * 256u;
+            if (p.S == 1) {
+                for (int c0 = 0; c0 < mv; c0 += 32) {
+                    uint32_t r[32];
+                    tmem_ld_32x32(t_addr + (uint32_t)c0, r);
+                    if (nv) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            const int m = w.m0 + c0 + j;
+                            if (c0 + j < mv) {
+                                const size_t oi = (size_t)m * p.N + n;
+                                p.y[oi] = __fmul_rn(__ldg(p.act_scale + m), (float)(int)r[j]);
+                                if (p.acc_out) p.acc_out[oi] = (int)r[j];
+                            }
+                        }
+                    }
+                }
+                tc_fence_before();
+                mbar_arrive(&tmem_empty[acc]);
+            } else {
+                // split-K: post this CTA's int32 partial [token][128 rows], then the last arrival sums
+                int32_t* mine = p.scratch + ((size_t)w.tile * p.S + w.split) * ((size_t)p.BN * G_ROWS);
+                for (int c0 = 0; c0 < mv; c0 += 32) {
+                    uint32_t r[32];
+                    tmem_ld_32x32(t_addr + (uint32_t)c0, r);
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (c0 + j < mv) __stcg(mine + (size_t)(c0 + j) * G_ROWS + nl, (int)r[j]);
+                }
+                tc_fence_before();
+                mbar_arrive(&tmem_empty[acc]);
+                __threadfence();
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                if (etid == 0) *ticket_s = atomicAdd(p.counters + w.tile, 1);
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                const int ticket = *ticket_s;
+                if (ticket == p.S - 1) {
+                    __threadfence();
+                    const int32_t* t0 = p.scratch + (size_t)w.tile * p.S * ((size_t)p.BN * G_ROWS) + nl;
+                    for (int c = 0; c < mv; c += 4) {
+                        int sum[4] = {0, 0, 0, 0};
+                        for (int sp = 0; sp < p.S; ++sp) {
+                            const int32_t* ps = t0 + (size_t)sp * ((size_t)p.BN * G_ROWS);
+#pragma unroll
+                            for (int j = 0; j < 4; ++j)
+                                if (c + j < mv) sum[j] += __ldcg(ps + (size_t)(c + j) * G_ROWS);
+                        }
+                        if (nv) {
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) {
+                                if (c + j < mv) {
+                                    const int m = w.m0 + c + j;
+                                    const size_t oi = (size_t)m * p.N + n;
+                                    p.y[oi] = __fmul_rn(__ldg(p.act_scale + m), (float)sum[j]);
+                                    if (p.acc_out) p.acc_out[oi] = sum[j];
+                                }
+                            }
+                        }
+                    }
+                    if (etid == 0) p.counters[w.tile] = 0;  // self-cleaning: next launch starts from zero
+                }
+                asm volatile("bar.sync 1, 128;" ::: "memory");  // ticket_s is reused by the next item
+            }
+        }
     }
+    tc_fence_before();
     __syncthreads();
-    if (warp == 4) {
+    if (warp == 1) {
         tc_fence_after();
-        tmem_dealloc(tmem_d, GEMM_BN);
+        tmem_dealloc(tmem_d, 512);
     }
 }
+
+// ---- host side ------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = []() -> EncodeTiledFn {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess ||
+            qres != cudaDriverEntryPointSuccess)
+            return nullptr;
+        return reinterpret_cast<EncodeTiledFn>(p);
+    }();
+    return fn;
+}
+
+// uint8 matrix [rows, inner] with a row pitch in bytes; box = 128 bytes x box_rows, SWIZZLE_128B;
+// out-of-range rows / bytes read as zero
+static int make_map_2d(CUtensorMap* tm, const void* ptr, size_t inner, size_t rows, size_t pitch, int box_rows) {
+    EncodeTiledFn fn = encode_tiled_fn();
+    if (!fn) return fail("linear_i8 GEMM: cuTensorMapEncodeTiled is not available from this driver");
+    const cuuint64_t gdim[2] = {(cuuint64_t)inner, (cuuint64_t)rows};
+    const cuuint64_t gstr[1] = {(cuuint64_t)pitch};
+    const cuuint32_t box[2] = {128u, (cuuint32_t)box_rows};
+    const cuuint32_t estr[2] = {1u, 1u};
+    const CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void*>(ptr), gdim, gstr, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail("linear_i8 GEMM: cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")");
+    return 0;
+}
+
+int gemm_min_m = 9;  // test/bench knob: smallest M routed to the tcgen05 kernel
 
 bool gemm_i8_supported(const bitnet_b200_weight* w, int M) {
     static const bool off = getenv("BITNET_B200_NO_GEMM") != nullptr;
     if (off) return false;
-    return w->layout == BITNET_B200_LAYOUT_QK256 && M > 16 && w->cols % GEMM_BK == 0 && w->code_stride == w->cols / 4;
+    return w->layout == BITNET_B200_LAYOUT_QK256 && M >= gemm_min_m && w->cols % G_BK == 0 &&
+           w->code_stride == w->cols / 4 && div_ceil(w->rows, G_ROWS) * div_ceil((size_t)M, 256) <= G_MAX_TILE_COUNTERS;
 }
+
+int gemm_split_override = 0;  // test knob: force a split-K factor (0 = heuristic)
 
 int launch_gemm_i8(const bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, const int8_t* q, const float* act_scale,
                    int M, float* y, int32_t* acc_out) {
     if (!gemm_i8_supported(w, M)) return fail("linear_i8 GEMM: shape not covered by the tcgen05 kernel");
     if (reinterpret_cast<uintptr_t>(q) & 15) return fail("linear_i8 GEMM: q must be 16-byte aligned");
+    if (!ctx->gemm_scratch || !ctx->gemm_counters) {
+        // first GEMM on this context: allocate the split-K scratch (cudaMalloc is illegal under graph capture,
+        // so a captured step must have run once eagerly before -- every harness here warms up first)
+        cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+        cudaStreamIsCapturing(ctx->stream, &cs);
+        if (cs != cudaStreamCaptureStatusNone)
+            return fail("linear_i8 GEMM: run the M > 8 path once on this context before capturing it into a CUDA graph");
+        static std::mutex mu;
+        std::lock_guard<std::mutex> lk(mu);
+        auto* c = const_cast<bitnet_b200_ctx*>(ctx);
+        if (!c->gemm_counters) {
+            B200_CUDA(cudaMalloc(&c->gemm_counters, G_MAX_TILE_COUNTERS * sizeof(int)));
+            B200_CUDA(cudaMemsetAsync(c->gemm_counters, 0, G_MAX_TILE_COUNTERS * sizeof(int), ctx->stream));
+        }
+        if (!c->gemm_scratch) B200_CUDA(cudaMalloc(&c->gemm_scratch, G_SCRATCH_BYTES));
+    }
     GemmParams p{};
-    p.codes = w->codes;
-    p.q = q;
     p.act_scale = act_scale;
     p.y = y;
     p.acc_out = acc_out;
+    p.scratch = ctx->gemm_scratch;
+    p.counters = ctx->gemm_counters;
     p.lut = w->lut_word;
     p.M = M;
     p.N = (int)w->rows;
     p.K = (int)w->cols;
+    p.n_mt = (int)div_ceil((size_t)M, 256);
+    p.BN = (int)(div_ceil(div_ceil((size_t)M, (size_t)p.n_mt), 16) * 16);
+    p.n_rt = (int)div_ceil(w->rows, G_ROWS);
+    const int tiles = p.n_rt * p.n_mt, nkb = p.K / G_BK;
+    int S = 1;
+    if (tiles < ctx->num_sms * 3 / 4) {
+        S = ctx->num_sms / tiles;
+        if (S > nkb / 2) S = nkb / 2;
+    }
+    if (gemm_split_override > 0) S = gemm_split_override;
+    if (S > nkb) S = nkb;
+    while (S > 1 && (size_t)tiles * S * p.BN * G_ROWS * 4 > G_SCRATCH_BYTES) --S;
+    if (S < 1) S = 1;
+    p.S = S;
+    p.n_pk = p.BN > 128 ? 2 : 5;
+    p.n_items = tiles * S;
+    const size_t smem = (size_t)G_NAB * (G_A_BYTES + (size_t)p.BN * 128) + (size_t)p.n_pk * G_PK_BYTES + 1024 + G_BAR_BYTES;
+
+    CUtensorMap tm_codes, tm_q;
+    if (make_map_2d(&tm_codes, w->codes, w->code_stride, w->rows, w->code_stride, G_ROWS)) return -1;
+    if (make_map_2d(&tm_q, q, (size_t)p.K, (size_t)M, (size_t)p.K, p.BN)) return -1;
+
     static bool attr_set[16] = {};
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 16 && !attr_set[dev]) {
-        B200_CUDA(cudaFuncSetAttribute(gemm_i8_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM));
+        B200_CUDA(cudaFuncSetAttribute(gemm_i8_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         attr_set[dev] = true;
     }
-    dim3 grid((unsigned)div_ceil((size_t)p.N, GEMM_BN), (unsigned)div_ceil((size_t)M, GEMM_BM));
-    gemm_i8_tcgen05_kernel<<<grid, GEMM_THREADS, GEMM_SMEM, ctx->stream>>>(p);
+    const int grid = p.n_items < ctx->num_sms ? p.n_items : ctx->num_sms;
+    gemm_i8_tcgen05_kernel<<<grid, G_THREADS, smem, ctx->stream>>>(tm_codes, tm_q, p);
     B200_LAUNCH_CHECK("gemm_i8_tcgen05_kernel");
     return 0;
 }

@@ -250,6 +250,8 @@ def test_linear_qk256_model_shapes(ctx, b200, oracle, rows, cols, M):
 @pytest.mark.parametrize("rows,cols,M", [
     (128, 128, 128), (128, 256, 17), (8, 256, 64), (130, 1024, 129), (256, 512, 300), (100, 1024, 33),
     (640, 2560, 64), (3840, 2560, 128), (2560, 6912, 64), (6912, 2560, 130), (2560, 2560, 512), (1024, 14336, 64),
+    (384, 128, 40), (2560, 2560, 257), (6912, 2560, 1000), (3840, 2560, 9), (2560, 6912, 12), (4096, 512, 64),
+    (13824, 2560, 2048),
 ])
 def test_linear_qk256_gemm_tcgen05(ctx, b200, oracle, rows, cols, M):
     qs, q, s = _qk256_case(oracle, rows, cols, M, rows + cols + M)
