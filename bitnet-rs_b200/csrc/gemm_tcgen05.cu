@@ -25,9 +25,9 @@
 //               frees the stage with tcgen05.commit -> mbarrier; two TMEM accumulator stages
 //               (2 x 256 columns) so the epilogue of tile i overlaps the main loop of tile i+1;
 //   * warps 2-5: epilogue: tcgen05.ld (32 lanes x 32 columns) -> act_scale * float(acc) -> y.
-//   * small M (few output tiles): split-K over CTAs so that all 148 SMs stream weights; int32
-//     partials go to an L2-resident scratch, the last CTA of a tile (ticket counter) sums them --
-//     integer addition, so the result is independent of arrival order and stays bit-exact.
+//   * small M (few output tiles): split-K over CTAs so that all 148 SMs stream weights; the int32
+//     partials meet in an L2-resident block through RED.ADD, the last CTA of a tile (ticket counter)
+//     scales it into y -- integer addition, so the result is independent of arrival order, bit-exact.
 #include <cuda.h>
 
 #include <mutex>
@@ -39,13 +39,14 @@ namespace b200 {
 constexpr int G_ROWS = 128;               // weight rows per tile (UMMA M)
 constexpr int G_BK = 128;                 // int8 k per block = one 128-byte swizzle row
 constexpr int G_PKQ = 4;                  // k-blocks per packed-code stage (128 B of codes per row)
-constexpr int G_NAB = 4;                  // operand stages (decoded A + token B)
+constexpr int G_NA = 4;                   // decoded-weight (A operand) stages
+constexpr int G_NB_MAX = 16;              // token (B operand) stages: as many as fit, L2 latency is hidden here
 constexpr int G_A_BYTES = G_ROWS * G_BK;  // 16 KB decoded weights per stage
 constexpr int G_PK_BYTES = G_ROWS * 128;  // 16 KB packed codes per stage
 constexpr int G_THREADS = 15 * 32;
-constexpr int G_DEC_WARP0 = 6, G_DEC_THREADS = 256;
-constexpr int G_BAR_BYTES = 512;
-constexpr size_t G_SCRATCH_BYTES = 40u << 20;  // split-K partials (ctx-owned)
+constexpr int G_DEC_WARP0 = 6, G_DEC_WARPS = 8;
+constexpr int G_BAR_BYTES = 1024;
+constexpr size_t G_SCRATCH_BYTES = 16u << 20;  // split-K accumulation blocks (ctx-owned, zero between launches)
 constexpr int G_MAX_TILE_COUNTERS = 8192;
 
 struct GemmParams {
@@ -61,6 +62,7 @@ struct GemmParams {
     int n_mt;      // token tiles
     int S;         // split-K factor
     int n_pk;      // packed-code stages
+    int n_b;       // token stages
     int n_items;   // n_rt * n_mt * S
 };
 
@@ -129,12 +131,19 @@ __device__ __forceinline__ uint32_t umma_idesc_i8(int m, int n) {
 }
 
 // running ring position -> (stage, parity)
+// (kept incremental: a runtime modulo per k-block costs ~30 dependent instructions, and the single
+// MMA-issuing thread is the critical path of the whole CTA)
 struct Ring {
-    uint32_t n, stages;
-    __device__ __forceinline__ Ring(uint32_t s) : n(0), stages(s) {}
-    __device__ __forceinline__ uint32_t stage() const { return n % stages; }
-    __device__ __forceinline__ uint32_t parity() const { return (n / stages) & 1u; }
-    __device__ __forceinline__ void next() { ++n; }
+    uint32_t s, ph, stages;
+    __device__ __forceinline__ Ring(uint32_t n) : s(0), ph(0), stages(n) {}
+    __device__ __forceinline__ uint32_t stage() const { return s; }
+    __device__ __forceinline__ uint32_t parity() const { return ph; }
+    __device__ __forceinline__ void next() {
+        if (++s == stages) {
+            s = 0;
+            ph ^= 1u;
+        }
+    }
 };
 
 struct Item {
@@ -159,35 +168,29 @@ gemm_i8_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_codes, const __gri
     extern __shared__ unsigned char gsm_raw[];
     // 1024-byte alignment: the swizzle pattern is a function of the absolute shared address
     unsigned char* base = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(gsm_raw) + 1023) & ~(uintptr_t)1023);
-    const uint32_t ab_stage_bytes = (uint32_t)G_A_BYTES + (uint32_t)p.BN * 128u;
-    unsigned char* pk_base = base + (size_t)G_NAB * ab_stage_bytes;
+    const uint32_t b_stage_bytes = (uint32_t)p.BN * 128u;
+    unsigned char* b_base = base + (size_t)G_NA * G_A_BYTES;
+    unsigned char* pk_base = b_base + (size_t)p.n_b * b_stage_bytes;
     uint64_t* bars = reinterpret_cast<uint64_t*>(pk_base + (size_t)p.n_pk * G_PK_BYTES);
-    uint64_t* pk_full = bars;            // [8]
-    uint64_t* pk_empty = bars + 8;       // [8]
-    uint64_t* a_full = bars + 16;        // [4]
-    uint64_t* b_full = bars + 20;        // [4]
-    uint64_t* ab_empty = bars + 24;      // [4]
-    uint64_t* tmem_full = bars + 28;     // [2]
-    uint64_t* tmem_empty = bars + 30;    // [2]
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 32);
+    uint64_t* pk_full = bars;            // [8]   count 1 (TMA tx)
+    uint64_t* pk_empty = bars + 8;       // [8]   count 8 (decoder warps)
+    uint64_t* a_full = bars + 16;        // [4]   count 8
+    uint64_t* a_empty = bars + 20;       // [4]   count 1 (tcgen05.commit)
+    uint64_t* tmem_full = bars + 24;     // [2]   count 1
+    uint64_t* tmem_empty = bars + 26;    // [2]   count 4 (epilogue warps)
+    uint64_t* b_full = bars + 32;        // [16]  count 1 (TMA tx)
+    uint64_t* b_empty = bars + 48;       // [16]  count 1 (tcgen05.commit)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 64);
     volatile int* ticket_s = reinterpret_cast<volatile int*>(tmem_slot + 1);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
-    if (tid == 0) {
-        for (int s = 0; s < 8; ++s) {
-            mbar_init(&pk_full[s], 1);
-            mbar_init(&pk_empty[s], G_DEC_THREADS);
-        }
-        for (int s = 0; s < G_NAB; ++s) {
-            mbar_init(&a_full[s], G_DEC_THREADS);
-            mbar_init(&b_full[s], 1);
-            mbar_init(&ab_empty[s], 1);
-        }
-        for (int s = 0; s < 2; ++s) {
-            mbar_init(&tmem_full[s], 1);
-            mbar_init(&tmem_empty[s], 128);
-        }
+    if (warp == 2 || warp == 3) {  // one barrier per thread
+        const int i = tid - 64;
+        uint32_t cnt = 1;
+        if (i >= 8 && i < 20) cnt = (uint32_t)G_DEC_WARPS;  // one elected arrival per decoder warp
+        if (i == 26 || i == 27) cnt = 4u;                    // one per epilogue warp
+        mbar_init(&bars[i], cnt);
         mbar_fence_init();
     }
     if (warp == 0 && lane == 0) tma_prefetch_desc(&tm_q);
@@ -201,16 +204,15 @@ gemm_i8_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_codes, const __gri
     if (warp == 0) {
         // ================= TMA producer: int8 token tiles (B operand) =================
         if (lane == 0) {
-            Ring ab(G_NAB);
-            const uint32_t bytes = (uint32_t)p.BN * 128u;
+            Ring rb((uint32_t)p.n_b);
             for (int it = blockIdx.x; it < p.n_items; it += gridDim.x) {
                 const Item w = item_of(p, it);
                 for (int kb = w.kb0; kb < w.kb1; ++kb) {
-                    const uint32_t s = ab.stage();
-                    mbar_wait(&ab_empty[s], ab.parity() ^ 1u);
-                    mbar_expect_tx(&b_full[s], bytes);
-                    tma_load_2d(base + (size_t)s * ab_stage_bytes + G_A_BYTES, &tm_q, kb * G_BK, w.m0, &b_full[s]);
-                    ab.next();
+                    const uint32_t s = rb.stage();
+                    mbar_wait(&b_empty[s], rb.parity() ^ 1u);
+                    mbar_expect_tx(&b_full[s], b_stage_bytes);
+                    tma_load_2d(b_base + (size_t)s * b_stage_bytes, &tm_q, kb * G_BK, w.m0, &b_full[s]);
+                    rb.next();
                 }
             }
         }
@@ -230,34 +232,43 @@ gemm_i8_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_codes, const __gri
             }
         }
     } else if (warp == 1) {
-        // ================= MMA issuer =================
-        const uint32_t idesc = umma_idesc_i8(G_ROWS, p.BN);
-        Ring ab(G_NAB);
-        uint32_t nacc = 0;
-        for (int it = blockIdx.x; it < p.n_items; it += gridDim.x, ++nacc) {
-            const Item w = item_of(p, it);
-            const uint32_t acc = nacc & 1u;
-            mbar_wait(&tmem_empty[acc], ((nacc >> 1) & 1u) ^ 1u);
-            tc_fence_after();
-            const uint32_t d_addr = tmem_d + acc * 256u;
-            for (int kb = w.kb0; kb < w.kb1; ++kb) {
-                const uint32_t s = ab.stage();
-                mbar_wait(&a_full[s], ab.parity());
-                mbar_wait(&b_full[s], ab.parity());
+        // ================= MMA issuer: ONE thread runs the whole loop (waits, issue, commits) =================
+        if (lane == 0) {
+            const uint32_t idesc = umma_idesc_i8(G_ROWS, p.BN);
+            const uint64_t adesc0 = umma_desc_sw128(smem_u32(base));
+            const uint64_t bdesc0 = umma_desc_sw128(smem_u32(b_base));
+            const uint32_t b_step = b_stage_bytes >> 4;  // descriptor address field is in 16-byte units
+            Ring ra(G_NA), rb((uint32_t)p.n_b);
+            uint32_t acc = 0, acc_ph = 0;
+            for (int it = blockIdx.x; it < p.n_items; it += gridDim.x) {
+                const Item w = item_of(p, it);
+                mbar_wait(&tmem_empty[acc], acc_ph ^ 1u);
                 tc_fence_after();
-                if (lane == 0) {
-                    const uint32_t a_addr = smem_u32(base + (size_t)s * ab_stage_bytes);
-                    const uint64_t adesc = umma_desc_sw128(a_addr), bdesc = umma_desc_sw128(a_addr + G_A_BYTES);
-#pragma unroll
-                    for (int k = 0; k < G_BK / 32; ++k)  // +32 bytes along K = +2 in the (>>4) address field
-                        umma_i8(d_addr, adesc + 2 * k, bdesc + 2 * k, idesc, (uint32_t)((kb - w.kb0) | k));
-                    umma_commit(&ab_empty[s]);                     // stage reusable once these MMAs have read it
-                    if (kb == w.kb1 - 1) umma_commit(&tmem_full[acc]);  // accumulator complete
+                const uint32_t d_addr = tmem_d + acc * 256u;
+                uint32_t accumulate = 0;
+                for (int kb = w.kb0; kb < w.kb1; ++kb) {
+                    const uint32_t sa = ra.stage(), sb = rb.stage();
+                    mbar_wait(&b_full[sb], rb.parity());
+                    mbar_wait(&a_full[sa], ra.parity());
+                    tc_fence_after();
+                    const uint64_t adesc = adesc0 + (uint64_t)(sa * (uint32_t)(G_A_BYTES >> 4));
+                    const uint64_t bdesc = bdesc0 + (uint64_t)(sb * b_step);
+                    umma_i8(d_addr, adesc, bdesc, idesc, accumulate);  // +32 bytes along K = +2 in the address field
+                    umma_i8(d_addr, adesc + 2, bdesc + 2, idesc, 1u);
+                    umma_i8(d_addr, adesc + 4, bdesc + 4, idesc, 1u);
+                    umma_i8(d_addr, adesc + 6, bdesc + 6, idesc, 1u);
+                    accumulate = 1u;
+                    umma_commit(&a_empty[sa]);  // stages reusable once these MMAs have read them
+                    umma_commit(&b_empty[sb]);
+                    ra.next();
+                    rb.next();
                 }
-                __syncwarp();
-                ab.next();
+                umma_commit(&tmem_full[acc]);  // accumulator complete
+                acc ^= 1u;
+                if (acc == 0) acc_ph ^= 1u;
             }
         }
+        __syncwarp();
     } else if (warp >= G_DEC_WARP0 && warp < G_DEC_WARP0 + 8) {
         // ================= decoders: packed codes -> int8 A tile (SWIZZLE_128B, K-major) =================
         const int dw = warp - G_DEC_WARP0;
@@ -268,7 +279,7 @@ gemm_i8_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_codes, const __gri
         uint32_t a_off[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) a_off[j] = row_off + ((((uint32_t)(half * 4 + j)) ^ rx) << 4);
-        Ring ab(G_NAB), pk((uint32_t)p.n_pk);
+        Ring ab(G_NA), pk((uint32_t)p.n_pk);
         for (int it = blockIdx.x; it < p.n_items; it += gridDim.x) {
             const Item w = item_of(p, it);
             for (int kb = w.kb0; kb < w.kb1; ++kb) {
@@ -280,17 +291,18 @@ gemm_i8_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_codes, const __gri
                 const uint4 d0 = decode16(cw.x, p.lut), d1 = decode16(cw.y, p.lut);
                 const uint4 d2 = decode16(cw.z, p.lut), d3 = decode16(cw.w, p.lut);
                 const uint32_t s = ab.stage();
-                mbar_wait(&ab_empty[s], ab.parity() ^ 1u);
-                unsigned char* a_tile = base + (size_t)s * ab_stage_bytes;
+                mbar_wait(&a_empty[s], ab.parity() ^ 1u);
+                unsigned char* a_tile = base + (size_t)s * G_A_BYTES;
                 *reinterpret_cast<uint4*>(a_tile + a_off[0]) = d0;
                 *reinterpret_cast<uint4*>(a_tile + a_off[1]) = d1;
                 *reinterpret_cast<uint4*>(a_tile + a_off[2]) = d2;
                 *reinterpret_cast<uint4*>(a_tile + a_off[3]) = d3;
                 fence_proxy_async_smem();  // generic-proxy stores -> visible to the tensor core (async proxy)
-                mbar_arrive(&a_full[s]);
+                __syncwarp();              // one arrival per warp: 256 arrivals on one mbarrier serialise
+                if (lane == 0) mbar_arrive(&a_full[s]);
                 ab.next();
                 if (rel == G_PKQ - 1 || kb == w.kb1 - 1) {
-                    mbar_arrive(&pk_empty[ps]);
+                    if (lane == 0) mbar_arrive(&pk_empty[ps]);
                     pk.next();
                 }
             }
@@ -313,33 +325,46 @@ gemm_i8_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_codes, const __gri
             if (p.S == 1) {
                 for (int c0 = 0; c0 < mv; c0 += 32) {
                     uint32_t r[32];
+                    // lane l fetches the scale of token c0 + l; broadcast by shuffle below
+                    const float sl = (c0 + lane < mv) ? __ldg(p.act_scale + w.m0 + c0 + lane) : 0.f;
                     tmem_ld_32x32(t_addr + (uint32_t)c0, r);
-                    if (nv) {
+                    float* yp = p.y + (size_t)(w.m0 + c0) * p.N + n;
+                    if (c0 + 32 <= mv && !p.acc_out) {
 #pragma unroll
                         for (int j = 0; j < 32; ++j) {
-                            const int m = w.m0 + c0 + j;
-                            if (c0 + j < mv) {
-                                const size_t oi = (size_t)m * p.N + n;
-                                p.y[oi] = __fmul_rn(__ldg(p.act_scale + m), (float)(int)r[j]);
-                                if (p.acc_out) p.acc_out[oi] = (int)r[j];
+                            const float sj = __shfl_sync(0xffffffffu, sl, j);
+                            if (nv) yp[(size_t)j * p.N] = __fmul_rn(sj, (float)(int)r[j]);
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            const float sj = __shfl_sync(0xffffffffu, sl, j);
+                            if (nv && c0 + j < mv) {
+                                yp[(size_t)j * p.N] = __fmul_rn(sj, (float)(int)r[j]);
+                                if (p.acc_out) p.acc_out[(size_t)(w.m0 + c0 + j) * p.N + n] = (int)r[j];
                             }
                         }
                     }
                 }
                 tc_fence_before();
-                mbar_arrive(&tmem_empty[acc]);
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&tmem_empty[acc]);
             } else {
-                // split-K: post this CTA's int32 partial [token][128 rows], then the last arrival sums
-                int32_t* mine = p.scratch + ((size_t)w.tile * p.S + w.split) * ((size_t)p.BN * G_ROWS);
+                // split-K: every CTA of the tile adds its int32 partial into the tile's accumulation
+                // block [token][128 rows] with fire-and-forget reductions (RED.ADD at the L2; integer,
+                // hence order-independent and exact); the last arrival (ticket) turns it into y and
+                // leaves the block and the ticket zeroed for the next launch
+                int32_t* blk = p.scratch + (size_t)w.tile * ((size_t)p.BN * G_ROWS) + nl;
                 for (int c0 = 0; c0 < mv; c0 += 32) {
                     uint32_t r[32];
                     tmem_ld_32x32(t_addr + (uint32_t)c0, r);
 #pragma unroll
                     for (int j = 0; j < 32; ++j)
-                        if (c0 + j < mv) __stcg(mine + (size_t)(c0 + j) * G_ROWS + nl, (int)r[j]);
+                        if (c0 + j < mv) atomicAdd(blk + (size_t)(c0 + j) * G_ROWS, (int)r[j]);
                 }
                 tc_fence_before();
-                mbar_arrive(&tmem_empty[acc]);
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&tmem_empty[acc]);
                 __threadfence();
                 asm volatile("bar.sync 1, 128;" ::: "memory");
                 if (etid == 0) *ticket_s = atomicAdd(p.counters + w.tile, 1);
@@ -347,23 +372,20 @@ gemm_i8_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_codes, const __gri
                 const int ticket = *ticket_s;
                 if (ticket == p.S - 1) {
                     __threadfence();
-                    const int32_t* t0 = p.scratch + (size_t)w.tile * p.S * ((size_t)p.BN * G_ROWS) + nl;
-                    for (int c = 0; c < mv; c += 4) {
-                        int sum[4] = {0, 0, 0, 0};
-                        for (int sp = 0; sp < p.S; ++sp) {
-                            const int32_t* ps = t0 + (size_t)sp * ((size_t)p.BN * G_ROWS);
+                    for (int c0 = 0; c0 < mv; c0 += 32) {
+                        const float sl = (c0 + lane < mv) ? __ldg(p.act_scale + w.m0 + c0 + lane) : 0.f;
+                        int v[32];
 #pragma unroll
-                            for (int j = 0; j < 4; ++j)
-                                if (c + j < mv) sum[j] += __ldcg(ps + (size_t)(c + j) * G_ROWS);
-                        }
-                        if (nv) {
+                        for (int j = 0; j < 32; ++j) v[j] = (c0 + j < mv) ? __ldcg(blk + (size_t)(c0 + j) * G_ROWS) : 0;
 #pragma unroll
-                            for (int j = 0; j < 4; ++j) {
-                                if (c + j < mv) {
-                                    const int m = w.m0 + c + j;
-                                    const size_t oi = (size_t)m * p.N + n;
-                                    p.y[oi] = __fmul_rn(__ldg(p.act_scale + m), (float)sum[j]);
-                                    if (p.acc_out) p.acc_out[oi] = sum[j];
+                        for (int j = 0; j < 32; ++j) {
+                            const float sj = __shfl_sync(0xffffffffu, sl, j);
+                            if (c0 + j < mv) {
+                                __stcg(blk + (size_t)(c0 + j) * G_ROWS, 0);
+                                if (nv) {
+                                    const size_t oi = (size_t)(w.m0 + c0 + j) * p.N + n;
+                                    p.y[oi] = __fmul_rn(sj, (float)v[j]);
+                                    if (p.acc_out) p.acc_out[oi] = v[j];
                                 }
                             }
                         }
@@ -444,7 +466,10 @@ int launch_gemm_i8(const bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, cons
             B200_CUDA(cudaMalloc(&c->gemm_counters, G_MAX_TILE_COUNTERS * sizeof(int)));
             B200_CUDA(cudaMemsetAsync(c->gemm_counters, 0, G_MAX_TILE_COUNTERS * sizeof(int), ctx->stream));
         }
-        if (!c->gemm_scratch) B200_CUDA(cudaMalloc(&c->gemm_scratch, G_SCRATCH_BYTES));
+        if (!c->gemm_scratch) {
+            B200_CUDA(cudaMalloc(&c->gemm_scratch, G_SCRATCH_BYTES));
+            B200_CUDA(cudaMemsetAsync(c->gemm_scratch, 0, G_SCRATCH_BYTES, ctx->stream));
+        }
     }
     GemmParams p{};
     p.act_scale = act_scale;
@@ -456,23 +481,50 @@ int launch_gemm_i8(const bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, cons
     p.M = M;
     p.N = (int)w->rows;
     p.K = (int)w->cols;
-    p.n_mt = (int)div_ceil((size_t)M, 256);
-    p.BN = (int)(div_ceil(div_ceil((size_t)M, (size_t)p.n_mt), 16) * 16);
     p.n_rt = (int)div_ceil(w->rows, G_ROWS);
-    const int tiles = p.n_rt * p.n_mt, nkb = p.K / G_BK;
-    int S = 1;
-    if (tiles < ctx->num_sms * 3 / 4) {
-        S = ctx->num_sms / tiles;
-        if (S > nkb / 2) S = nkb / 2;
+    const int nkb = p.K / G_BK;
+    // Tile shape: tokens per tile BN and split-K factor S from a small cost model (us): rounds of
+    // persistent CTAs x (k-blocks x max(decode, MMA) + epilogue); RED-based split-K pays per element.
+    const int m16 = (int)(div_ceil((size_t)M, 16) * 16);
+    int bestBN = 0, bestS = 1;
+    double best = 1e30;
+    static const int bn_c[] = {16, 32, 64, 128, 256};
+    static const int s_c[] = {1, 2, 3, 4, 6, 8};
+    for (int bi = 0; bi < 5; ++bi) {
+        int BN = bn_c[bi] < m16 ? bn_c[bi] : m16;
+        if (BN > 256) BN = 256;
+        const int n_mt = (int)div_ceil((size_t)M, (size_t)BN);
+        BN = (int)(div_ceil(div_ceil((size_t)M, (size_t)n_mt), 16) * 16);  // balance ragged token tiles
+        const long tiles = (long)p.n_rt * n_mt;
+        if (tiles > G_MAX_TILE_COUNTERS) continue;
+        for (int si = 0; si < 6; ++si) {
+            const int S = s_c[si];
+            if (S > 1 && (S > nkb / 2 || (size_t)tiles * BN * G_ROWS * 4 > G_SCRATCH_BYTES)) continue;
+            const long items = tiles * S;
+            const double rounds = (double)div_ceil((size_t)items, (size_t)ctx->num_sms);
+            const double t_kb = 0.55 * BN / 256.0 > 0.12 ? 0.55 * BN / 256.0 : 0.12;
+            const double t = rounds * (div_ceil((size_t)nkb, (size_t)S) * t_kb + BN * (S > 1 ? 0.04 : 0.008) + 1.0) +
+                             (S > 1 ? 1.0 : 0.0);
+            if (t < best) {
+                best = t;
+                bestBN = BN;
+                bestS = S;
+            }
+        }
     }
-    if (gemm_split_override > 0) S = gemm_split_override;
-    if (S > nkb) S = nkb;
-    while (S > 1 && (size_t)tiles * S * p.BN * G_ROWS * 4 > G_SCRATCH_BYTES) --S;
-    if (S < 1) S = 1;
-    p.S = S;
+    if (!bestBN) return fail("linear_i8 GEMM: no tile shape for this problem");
+    if (gemm_split_override > 0 && gemm_split_override <= nkb) bestS = gemm_split_override;
+    p.BN = bestBN;
+    p.n_mt = (int)div_ceil((size_t)M, (size_t)p.BN);
+    p.S = bestS;
+    const int tiles = p.n_rt * p.n_mt;
     p.n_pk = p.BN > 128 ? 2 : 5;
-    p.n_items = tiles * S;
-    const size_t smem = (size_t)G_NAB * (G_A_BYTES + (size_t)p.BN * 128) + (size_t)p.n_pk * G_PK_BYTES + 1024 + G_BAR_BYTES;
+    const size_t fixed = (size_t)G_NA * G_A_BYTES + (size_t)p.n_pk * G_PK_BYTES + 1024 + G_BAR_BYTES;
+    p.n_b = (int)((227 * 1024 - fixed) / ((size_t)p.BN * 128));
+    if (p.n_b > G_NB_MAX) p.n_b = G_NB_MAX;
+    if (p.n_b < 2) return fail("linear_i8 GEMM: shared memory budget");
+    p.n_items = tiles * p.S;
+    const size_t smem = fixed + (size_t)p.n_b * p.BN * 128;
 
     CUtensorMap tm_codes, tm_q;
     if (make_map_2d(&tm_codes, w->codes, w->code_stride, w->rows, w->code_stride, G_ROWS)) return -1;
