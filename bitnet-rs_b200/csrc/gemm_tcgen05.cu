@@ -38,13 +38,13 @@ namespace b200 {
 
 constexpr int G_ROWS = 128;               // weight rows per tile (UMMA M)
 constexpr int G_BK = 128;                 // int8 k per block = one 128-byte swizzle row
-constexpr int G_PKQ = 4;                  // k-blocks per packed-code stage (128 B of codes per row)
-constexpr int G_NA = 4;                   // decoded-weight (A operand) stages
+constexpr int G_PKQ = 2;                  // k-blocks per packed-code stage (64 B of codes per row)
+constexpr int G_NA_MAX = 8;               // decoded-weight (A operand) stages
 constexpr int G_NB_MAX = 16;              // token (B operand) stages: as many as fit, L2 latency is hidden here
 constexpr int G_A_BYTES = G_ROWS * G_BK;  // 16 KB decoded weights per stage
-constexpr int G_PK_BYTES = G_ROWS * 128;  // 16 KB packed codes per stage
+constexpr int G_PK_BYTES = G_ROWS * 64;   // 8 KB packed codes per stage
 constexpr int G_THREADS = 15 * 32;
-constexpr int G_DEC_WARP0 = 6, G_DEC_WARPS = 8;
+constexpr int G_DEC_WARP0 = 6, G_DEC_WARPS = 8, G_DEC_GROUPS = 4;  // 4 groups of 2 warps, one k-block each
 constexpr int G_BAR_BYTES = 1024;
 constexpr size_t G_SCRATCH_BYTES = 16u << 20;  // split-K accumulation blocks (ctx-owned, zero between launches)
 constexpr int G_MAX_TILE_COUNTERS = 8192;
@@ -63,6 +63,7 @@ struct GemmParams {
     int S;         // split-K factor
     int n_pk;      // packed-code stages
     int n_b;       // token stages
+    int n_a;       // decoded-weight stages
     int n_items;   // n_rt * n_mt * S
 };
 
@@ -111,6 +112,16 @@ __device__ __forceinline__ void tma_load_2d(void* dst_smem, const CUtensorMap* t
         "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
         ::"r"(smem_u32(dst_smem)), "l"(tm), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
         : "memory");
+}
+// true in exactly one lane of the (converged) warp
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n\t.reg .pred P;\n\t"
+        "elect.sync _|P, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, P;\n\t}"
+        : "=r"(pred));
+    return pred != 0;
 }
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* tm) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(tm) : "memory");
@@ -169,27 +180,28 @@ gemm_i8_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_codes, const __gri
     // 1024-byte alignment: the swizzle pattern is a function of the absolute shared address
     unsigned char* base = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(gsm_raw) + 1023) & ~(uintptr_t)1023);
     const uint32_t b_stage_bytes = (uint32_t)p.BN * 128u;
-    unsigned char* b_base = base + (size_t)G_NA * G_A_BYTES;
+    unsigned char* b_base = base + (size_t)p.n_a * G_A_BYTES;
     unsigned char* pk_base = b_base + (size_t)p.n_b * b_stage_bytes;
     uint64_t* bars = reinterpret_cast<uint64_t*>(pk_base + (size_t)p.n_pk * G_PK_BYTES);
     uint64_t* pk_full = bars;            // [8]   count 1 (TMA tx)
-    uint64_t* pk_empty = bars + 8;       // [8]   count 8 (decoder warps)
-    uint64_t* a_full = bars + 16;        // [4]   count 8
-    uint64_t* a_empty = bars + 20;       // [4]   count 1 (tcgen05.commit)
-    uint64_t* tmem_full = bars + 24;     // [2]   count 1
-    uint64_t* tmem_empty = bars + 26;    // [2]   count 4 (epilogue warps)
+    uint64_t* pk_empty = bars + 8;       // [8]   count 4 (2 k-blocks x 2 decoder warps)
+    uint64_t* a_full = bars + 16;        // [8]   count 2 (the two warps of the owning decoder group)
+    uint64_t* a_empty = bars + 24;       // [8]   count 1 (tcgen05.commit)
     uint64_t* b_full = bars + 32;        // [16]  count 1 (TMA tx)
     uint64_t* b_empty = bars + 48;       // [16]  count 1 (tcgen05.commit)
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 64);
+    uint64_t* tmem_full = bars + 64;     // [2]   count 1
+    uint64_t* tmem_empty = bars + 66;    // [2]   count 4 (epilogue warps)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 68);
     volatile int* ticket_s = reinterpret_cast<volatile int*>(tmem_slot + 1);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
-    if (warp == 2 || warp == 3) {  // one barrier per thread
+    if (tid >= 64 && tid < 64 + 68) {  // one barrier per thread
         const int i = tid - 64;
         uint32_t cnt = 1;
-        if (i >= 8 && i < 20) cnt = (uint32_t)G_DEC_WARPS;  // one elected arrival per decoder warp
-        if (i == 26 || i == 27) cnt = 4u;                    // one per epilogue warp
+        if (i >= 8 && i < 16) cnt = 4u;
+        if (i >= 16 && i < 24) cnt = 64u;
+        if (i >= 66) cnt = 4u;
         mbar_init(&bars[i], cnt);
         mbar_fence_init();
     }
@@ -226,85 +238,107 @@ gemm_i8_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_codes, const __gri
                     const uint32_t s = pk.stage();
                     mbar_wait(&pk_empty[s], pk.parity() ^ 1u);
                     mbar_expect_tx(&pk_full[s], (uint32_t)G_PK_BYTES);
-                    tma_load_2d(pk_base + (size_t)s * G_PK_BYTES, &tm_codes, kb * (G_BK / 4), w.row0, &pk_full[s]);
+                    tma_load_2d(pk_base + (size_t)s * G_PK_BYTES, &tm_codes, kb * (G_BK / 4), w.row0, &pk_full[s]);  // 64 B x 128 rows
                     pk.next();
                 }
             }
         }
     } else if (warp == 1) {
-        // ================= MMA issuer: ONE thread runs the whole loop (waits, issue, commits) =================
-        if (lane == 0) {
-            const uint32_t idesc = umma_idesc_i8(G_ROWS, p.BN);
-            const uint64_t adesc0 = umma_desc_sw128(smem_u32(base));
-            const uint64_t bdesc0 = umma_desc_sw128(smem_u32(b_base));
-            const uint32_t b_step = b_stage_bytes >> 4;  // descriptor address field is in 16-byte units
-            Ring ra(G_NA), rb((uint32_t)p.n_b);
-            uint32_t acc = 0, acc_ph = 0;
-            for (int it = blockIdx.x; it < p.n_items; it += gridDim.x) {
-                const Item w = item_of(p, it);
-                mbar_wait(&tmem_empty[acc], acc_ph ^ 1u);
+        // ================= MMA issuer =================
+        // The whole warp runs the (warp-uniform) loop so that descriptors and barrier addresses live in
+        // uniform registers; one elected lane issues. The issuing thread's instruction count per k-block
+        // is the critical path of the CTA at small BN, so nothing else happens in here.
+        const uint32_t idesc = umma_idesc_i8(G_ROWS, p.BN);
+        const uint64_t adesc0 = umma_desc_sw128(smem_u32(base));
+        const uint64_t bdesc0 = umma_desc_sw128(smem_u32(b_base));
+        const uint32_t b_step = b_stage_bytes >> 4;  // descriptor address field is in 16-byte units
+        const uint32_t n_a = (uint32_t)p.n_a, n_b = (uint32_t)p.n_b;
+        uint32_t sa = 0, pa = 0, sb = 0, pb = 0, acc = 0, acc_ph = 0;
+        for (int it = blockIdx.x; it < p.n_items; it += gridDim.x) {
+            const Item w = item_of(p, it);
+            mbar_wait(&tmem_empty[acc], acc_ph ^ 1u);
+            tc_fence_after();
+            const uint32_t d_addr = tmem_d + acc * 256u;
+            uint32_t accumulate = 0;
+            for (int kb = w.kb0; kb < w.kb1; ++kb) {
+                mbar_wait(&b_full[sb], pb);
+                mbar_wait(&a_full[sa], pa);
                 tc_fence_after();
-                const uint32_t d_addr = tmem_d + acc * 256u;
-                uint32_t accumulate = 0;
-                for (int kb = w.kb0; kb < w.kb1; ++kb) {
-                    const uint32_t sa = ra.stage(), sb = rb.stage();
-                    mbar_wait(&b_full[sb], rb.parity());
-                    mbar_wait(&a_full[sa], ra.parity());
-                    tc_fence_after();
-                    const uint64_t adesc = adesc0 + (uint64_t)(sa * (uint32_t)(G_A_BYTES >> 4));
-                    const uint64_t bdesc = bdesc0 + (uint64_t)(sb * b_step);
+                const uint64_t adesc = adesc0 + (uint64_t)(sa * (uint32_t)(G_A_BYTES >> 4));
+                const uint64_t bdesc = bdesc0 + (uint64_t)(sb * b_step);
+                if (elect_one()) {
                     umma_i8(d_addr, adesc, bdesc, idesc, accumulate);  // +32 bytes along K = +2 in the address field
                     umma_i8(d_addr, adesc + 2, bdesc + 2, idesc, 1u);
                     umma_i8(d_addr, adesc + 4, bdesc + 4, idesc, 1u);
                     umma_i8(d_addr, adesc + 6, bdesc + 6, idesc, 1u);
-                    accumulate = 1u;
                     umma_commit(&a_empty[sa]);  // stages reusable once these MMAs have read them
                     umma_commit(&b_empty[sb]);
-                    ra.next();
-                    rb.next();
+                    if (kb == w.kb1 - 1) umma_commit(&tmem_full[acc]);  // accumulator complete
                 }
-                umma_commit(&tmem_full[acc]);  // accumulator complete
-                acc ^= 1u;
-                if (acc == 0) acc_ph ^= 1u;
+                __syncwarp();
+                accumulate = 1u;
+                if (++sa == n_a) { sa = 0; pa ^= 1u; }
+                if (++sb == n_b) { sb = 0; pb ^= 1u; }
             }
+            acc ^= 1u;
+            if (acc == 0) acc_ph ^= 1u;
         }
-        __syncwarp();
     } else if (warp >= G_DEC_WARP0 && warp < G_DEC_WARP0 + 8) {
         // ================= decoders: packed codes -> int8 A tile (SWIZZLE_128B, K-major) =================
+        // Four groups of two warps; group g expands the k-blocks with (index & 3) == g, so four k-blocks
+        // are in flight and the load -> PRMT -> store -> proxy-fence chain of one hides behind the others.
+        // A thread owns four (row, 64-k half) units: one 128-bit shared load of codes and four 128-bit
+        // stores of int8 each; a quarter-warp always covers 8 consecutive rows -> conflict-free both ways.
         const int dw = warp - G_DEC_WARP0;
-        const int r = dw * 16 + (lane & 15);   // weight row of the tile; a quarter-warp = 8 consecutive rows
-        const int half = lane >> 4;            // which 64 k of the 128-k block
-        const uint32_t rx = (uint32_t)(r & 7);
-        const uint32_t row_off = (uint32_t)r * 128u;
-        uint32_t a_off[4];
+        const int grp = dw >> 1, gw = dw & 1;
+        const uint32_t half = (uint32_t)(lane >> 4);
+        uint32_t pk_off[4], a_off[4];  // a_off: byte offset of this unit's chunk 0 position (before XOR)
+        uint32_t rx[4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) a_off[j] = row_off + ((((uint32_t)(half * 4 + j)) ^ rx) << 4);
-        Ring ab(G_NA), pk((uint32_t)p.n_pk);
+        for (int u = 0; u < 4; ++u) {
+            const uint32_t r = (uint32_t)(gw * 64 + u * 16 + (lane & 15));
+            rx[u] = r & 7u;
+            a_off[u] = r * 128u;
+            pk_off[u] = r * 64u;  // packed stage: rows of 64 bytes, SWIZZLE_64B: chunk ^= (byte offset >> 7) & 3
+        }
+        Ring ra((uint32_t)p.n_a), pk((uint32_t)p.n_pk);
         for (int it = blockIdx.x; it < p.n_items; it += gridDim.x) {
             const Item w = item_of(p, it);
-            for (int kb = w.kb0; kb < w.kb1; ++kb) {
-                const int rel = (kb - w.kb0) & (G_PKQ - 1);
+            const int nk = w.kb1 - w.kb0, nk2 = (nk + 1) & ~1;  // a packed stage always gets both its arrivals
+            for (int rel = 0; rel < nk2; ++rel) {
                 const uint32_t ps = pk.stage();
-                if (rel == 0) mbar_wait(&pk_full[ps], pk.parity());
-                const uint4 cw = *reinterpret_cast<const uint4*>(pk_base + (size_t)ps * G_PK_BYTES + row_off +
-                                                                 ((((uint32_t)(2 * rel + half)) ^ rx) << 4));
-                const uint4 d0 = decode16(cw.x, p.lut), d1 = decode16(cw.y, p.lut);
-                const uint4 d2 = decode16(cw.z, p.lut), d3 = decode16(cw.w, p.lut);
-                const uint32_t s = ab.stage();
-                mbar_wait(&a_empty[s], ab.parity() ^ 1u);
-                unsigned char* a_tile = base + (size_t)s * G_A_BYTES;
-                *reinterpret_cast<uint4*>(a_tile + a_off[0]) = d0;
-                *reinterpret_cast<uint4*>(a_tile + a_off[1]) = d1;
-                *reinterpret_cast<uint4*>(a_tile + a_off[2]) = d2;
-                *reinterpret_cast<uint4*>(a_tile + a_off[3]) = d3;
-                fence_proxy_async_smem();  // generic-proxy stores -> visible to the tensor core (async proxy)
-                __syncwarp();              // one arrival per warp: 256 arrivals on one mbarrier serialise
-                if (lane == 0) mbar_arrive(&a_full[s]);
-                ab.next();
-                if (rel == G_PKQ - 1 || kb == w.kb1 - 1) {
-                    if (lane == 0) mbar_arrive(&pk_empty[ps]);
-                    pk.next();
+                if ((rel & (G_DEC_GROUPS - 1)) == grp) {
+                    const bool real = rel < nk;
+                    uint4 cw[4];
+                    if (real) {
+                        mbar_wait(&pk_full[ps], pk.parity());
+                        const unsigned char* pks = pk_base + (size_t)ps * G_PK_BYTES;
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const uint32_t c = (uint32_t)((rel & 1) * 2) + half;  // 16-byte chunk of the 64-byte row
+                            cw[u] = *reinterpret_cast<const uint4*>(pks + pk_off[u] + ((c ^ ((pk_off[u] >> 7) & 3u)) << 4));
+                        }
+                    }
+                    if (real) {
+                        const uint32_t sa = ra.stage();
+                        mbar_wait(&a_empty[sa], ra.parity() ^ 1u);
+                        unsigned char* a_tile = base + (size_t)sa * G_A_BYTES;
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const uint32_t ws[4] = {cw[u].x, cw[u].y, cw[u].z, cw[u].w};
+#pragma unroll
+                            for (int j = 0; j < 4; ++j)
+                                *reinterpret_cast<uint4*>(a_tile + a_off[u] + (((half * 4 + (uint32_t)j) ^ rx[u]) << 4)) =
+                                    decode16(ws[j], p.lut);
+                        }
+                        fence_proxy_async_smem();  // generic-proxy stores -> visible to the tensor core (async proxy)
+                        mbar_arrive(&a_full[sa]);  // every writer arrives itself, after its own proxy fence
+                    }
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&pk_empty[ps]);  // the codes of this stage are consumed
                 }
+                if (rel < nk) ra.next();
+                if (rel & 1) pk.next();
             }
         }
     } else {
@@ -319,14 +353,22 @@ gemm_i8_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_codes, const __gri
             const int n = w.row0 + nl;
             const bool nv = n < p.N;
             const int mv = min(p.BN, p.M - w.m0);  // valid token columns of this tile
+            // act scales of the tile's tokens: lane l holds token 32c + l of chunk c. Fetched BEFORE waiting
+            // for the accumulator, so their L2 latency hides behind the main loop.
+            float slv[8];
+#pragma unroll
+            for (int c = 0; c < 8; ++c)
+                slv[c] = (32 * c + lane < mv) ? __ldg(p.act_scale + w.m0 + 32 * c + lane) : 0.f;
             mbar_wait(&tmem_full[acc], (nacc >> 1) & 1u);
             tc_fence_after();
             const uint32_t t_addr = tmem_d + ((uint32_t)(qd * 32) << 16) + acc * 256u;
             if (p.S == 1) {
+#pragma unroll 1
                 for (int c0 = 0; c0 < mv; c0 += 32) {
                     uint32_t r[32];
-                    // lane l fetches the scale of token c0 + l; broadcast by shuffle below
-                    const float sl = (c0 + lane < mv) ? __ldg(p.act_scale + w.m0 + c0 + lane) : 0.f;
+                    float sl = slv[0];  // scale of token c0 + lane; broadcast by shuffle below
+#pragma unroll
+                    for (int c = 1; c < 8; ++c) sl = (c0 == 32 * c) ? slv[c] : sl;
                     tmem_ld_32x32(t_addr + (uint32_t)c0, r);
                     float* yp = p.y + (size_t)(w.m0 + c0) * p.N + n;
                     if (c0 + 32 <= mv && !p.acc_out) {
@@ -373,7 +415,9 @@ gemm_i8_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_codes, const __gri
                 if (ticket == p.S - 1) {
                     __threadfence();
                     for (int c0 = 0; c0 < mv; c0 += 32) {
-                        const float sl = (c0 + lane < mv) ? __ldg(p.act_scale + w.m0 + c0 + lane) : 0.f;
+                        float sl = slv[0];
+#pragma unroll
+                        for (int c = 1; c < 8; ++c) sl = (c0 == 32 * c) ? slv[c] : sl;
                         int v[32];
 #pragma unroll
                         for (int j = 0; j < 32; ++j) v[j] = (c0 + j < mv) ? __ldcg(blk + (size_t)(c0 + j) * G_ROWS) : 0;
@@ -423,15 +467,17 @@ static EncodeTiledFn encode_tiled_fn() {
 
 // uint8 matrix [rows, inner] with a row pitch in bytes; box = 128 bytes x box_rows, SWIZZLE_128B;
 // out-of-range rows / bytes read as zero
-static int make_map_2d(CUtensorMap* tm, const void* ptr, size_t inner, size_t rows, size_t pitch, int box_rows) {
+static int make_map_2d(CUtensorMap* tm, const void* ptr, size_t inner, size_t rows, size_t pitch, int box_rows,
+                       int box_inner = 128) {
     EncodeTiledFn fn = encode_tiled_fn();
     if (!fn) return fail("linear_i8 GEMM: cuTensorMapEncodeTiled is not available from this driver");
     const cuuint64_t gdim[2] = {(cuuint64_t)inner, (cuuint64_t)rows};
     const cuuint64_t gstr[1] = {(cuuint64_t)pitch};
-    const cuuint32_t box[2] = {128u, (cuuint32_t)box_rows};
+    const cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_rows};
     const cuuint32_t estr[2] = {1u, 1u};
     const CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void*>(ptr), gdim, gstr, box, estr,
-                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, box_inner == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
+                          CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail("linear_i8 GEMM: cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")");
     return 0;
@@ -502,7 +548,7 @@ int launch_gemm_i8(const bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, cons
             if (S > 1 && (S > nkb / 2 || (size_t)tiles * BN * G_ROWS * 4 > G_SCRATCH_BYTES)) continue;
             const long items = tiles * S;
             const double rounds = (double)div_ceil((size_t)items, (size_t)ctx->num_sms);
-            const double t_kb = 0.55 * BN / 256.0 > 0.12 ? 0.55 * BN / 256.0 : 0.12;
+            const double t_kb = 0.43 * BN / 256.0 > 0.30 ? 0.43 * BN / 256.0 : 0.30;  // measured: MMA-bound vs issue-bound
             const double t = rounds * (div_ceil((size_t)nkb, (size_t)S) * t_kb + BN * (S > 1 ? 0.04 : 0.008) + 1.0) +
                              (S > 1 ? 1.0 : 0.0);
             if (t < best) {
@@ -518,8 +564,11 @@ int launch_gemm_i8(const bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, cons
     p.n_mt = (int)div_ceil((size_t)M, (size_t)p.BN);
     p.S = bestS;
     const int tiles = p.n_rt * p.n_mt;
-    p.n_pk = p.BN > 128 ? 2 : 5;
-    const size_t fixed = (size_t)G_NA * G_A_BYTES + (size_t)p.n_pk * G_PK_BYTES + 1024 + G_BAR_BYTES;
+    // shared memory: A (decoded) ring + token ring + packed ring; the token ring hides L2 latency,
+    // the packed ring HBM latency (small M), the A ring the decode chain
+    p.n_pk = p.BN > 128 ? 2 : 8;
+    p.n_a = p.BN > 128 ? 5 : 6;
+    const size_t fixed = (size_t)p.n_a * G_A_BYTES + (size_t)p.n_pk * G_PK_BYTES + 1024 + G_BAR_BYTES;
     p.n_b = (int)((227 * 1024 - fixed) / ((size_t)p.BN * 128));
     if (p.n_b > G_NB_MAX) p.n_b = G_NB_MAX;
     if (p.n_b < 2) return fail("linear_i8 GEMM: shared memory budget");
@@ -527,7 +576,7 @@ int launch_gemm_i8(const bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, cons
     const size_t smem = fixed + (size_t)p.n_b * p.BN * 128;
 
     CUtensorMap tm_codes, tm_q;
-    if (make_map_2d(&tm_codes, w->codes, w->code_stride, w->rows, w->code_stride, G_ROWS)) return -1;
+    if (make_map_2d(&tm_codes, w->codes, w->code_stride, w->rows, w->code_stride, G_ROWS, 64)) return -1;
     if (make_map_2d(&tm_q, q, (size_t)p.K, (size_t)M, (size_t)p.K, p.BN)) return -1;
 
     static bool attr_set[16] = {};

@@ -264,6 +264,24 @@ def test_linear_qk256_gemm_tcgen05(ctx, b200, oracle, rows, cols, M):
     assert torch.equal(y2, y)
 
 
+def test_linear_qk256_gemm_cold_weights_repeated(ctx, b200):
+    # regression: with HBM-cold weights the decoder warps are the critical path; a packed-code stage
+    # released before its shared loads had landed was overwritten by the next TMA box (wrong rows,
+    # intermittently). Fresh weights + activations every repetition, BN = 256, several rounds per CTA.
+    rows, cols, M = 13824, 2560, 1024
+    rng = np.random.default_rng(7)
+    lut = torch.tensor([-2, -1, 1, 2], dtype=torch.float32, device="cuda")
+    for rep in range(6):
+        qs = rng.integers(0, 256, rows * cols // 4, dtype=np.uint8)
+        codes = torch.from_numpy(qs).cuda().view(rows, cols // 4)
+        wd = torch.stack([lut[((codes >> (2 * j)) & 3).long()] for j in range(4)], dim=2).reshape(rows, cols)
+        q = torch.from_numpy(rng.integers(-127, 128, (M, cols)).astype(np.int8)).cuda()
+        ref = (q.float() @ wd.t()).round().to(torch.int32)   # exact in f32: |acc| < 2^24
+        w = ctx.weight(qs, b200.LAYOUT_QK256, rows, cols)
+        _, acc = ctx.linear_i8(w, q, torch.ones(M, device="cuda"), want_acc=True)
+        assert torch.equal(acc, ref), "rep %d" % rep
+
+
 @pytest.mark.parametrize("lut_name", ["MAP_B", "MAP_C"])
 def test_linear_qk256_gemm_other_code_maps(ctx, b200, oracle, lut_name):
     rows, cols, M = 192, 1024, 70
