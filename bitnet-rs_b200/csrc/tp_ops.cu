@@ -1,0 +1,220 @@
+// tp_ops.cu -- building blocks of the tensor-parallel ternary linear:
+// Megatron-style sharding, q/k/v and gate/up by output rows (no exchange), o and down by input
+// columns. For the row-parallel layers each GPU holds K/tp of the activation, so the per-token
+// absmax int8 quantiser (crates/bitnet-kernels/src/cpu/quantize.rs:32-49) is split in two:
+//   1. row_absmax      local max|x| per token        -> all-reduce(MAX) of M floats (NCCL, by the host)
+//   2. quant_absmax    scale = absmax/127, q = clamp(round(v * (1/scale)))  with the GLOBAL absmax
+// so every GPU uses exactly the scale the unsharded quantiser would, its int32 partial accumulators
+// add up to the tp = 1 accumulator bit for bit (all-reduce(SUM) on int32), and
+//   3. residual_acc    x += act_scale * float(acc)   is the same one-multiply epilogue as tp = 1.
+// The reference has only the in-process simulation of these semantics
+// (crates/bitnet-inference/src/tensor_parallel.rs:123-290: partition_tensor / all_reduce Sum, Max).
+// Also here: the decode glue the TP step needs on the local heads (RoPE + KV append + attention),
+// exported so that a host-side decoder can run it per rank.
+#include "common.cuh"
+
+namespace b200 {
+
+// q = clamp(round_half_away(v * inv), -127, 127) as i8; NaN -> 0 (Rust `as i8`) -- as quant.cu
+__device__ __forceinline__ int tp_quant1(float v, float inv) {
+    float r = roundf(v * inv);
+    if (r != r) return 0;
+    r = fminf(fmaxf(r, -127.f), 127.f);
+    return (int)r;
+}
+
+__device__ __forceinline__ float tp_block_max(float v, float* sh) {
+    v = warp_max(v);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    if (lane == 0) sh[warp] = v;
+    __syncthreads();
+    float r = lane < nw ? sh[lane] : 0.f;
+    r = warp_max(r);
+    __syncthreads();
+    return r;
+}
+
+// One CTA per token row. MODE 0: v = x[row, k]. MODE 2: SwiGLU glue on an interleaved (gate, up)
+// row of 2K floats, v = silu(gate) * up (crates/bitnet-transformer/src/lib.rs:756-789), also
+// written to h[row, k] so the quantiser reads it back instead of recomputing expf.
+template <int MODE>
+__global__ void __launch_bounds__(256) tp_row_absmax_kernel(const float* __restrict__ x, int K, float* __restrict__ h,
+                                                           float* __restrict__ absmax) {
+    __shared__ float sh[32];
+    const int row = blockIdx.x;
+    const float* xr = x + (size_t)row * (MODE == 2 ? 2 * (size_t)K : (size_t)K);
+    float m = 0.f;
+    for (int k = threadIdx.x; k < K; k += blockDim.x) {
+        float v;
+        if (MODE == 2) {
+            const float2 gu = *reinterpret_cast<const float2*>(xr + 2 * (size_t)k);
+            v = (gu.x / (1.0f + expf(-gu.x))) * gu.y;
+            h[(size_t)row * K + k] = v;
+        } else {
+            v = xr[k];
+        }
+        m = fmaxf(m, fabsf(v));
+    }
+    m = tp_block_max(m, sh);
+    if (threadIdx.x == 0) absmax[row] = m;
+}
+
+// quantize_symmetric_i8 with a given (global) absmax per row; bit-identical to the unsharded
+// quantiser on the same values: scale = absmax / 127, inv = 1 / scale, all-zero row -> scale 0
+__global__ void __launch_bounds__(256) tp_quant_absmax_kernel(const float* __restrict__ x, const float* __restrict__ absmax,
+                                                             int K, int8_t* __restrict__ q, float* __restrict__ scale) {
+    const int row = blockIdx.x;
+    const float amax = absmax[row];
+    const float sc = amax == 0.f ? 0.f : amax / 127.f;
+    const float inv = amax == 0.f ? 0.f : 1.0f / sc;
+    if (threadIdx.x == 0) scale[row] = sc;
+    const float* xr = x + (size_t)row * K;
+    int8_t* qr = q + (size_t)row * K;
+    for (int k = threadIdx.x; k < K; k += blockDim.x) qr[k] = (int8_t)(amax == 0.f ? 0 : tp_quant1(xr[k], inv));
+}
+
+// x[m, n] = x[m, n] + act_scale[m] * float(acc[m, n])   (fmul_rn then fadd_rn, as EPI_RESIDUAL)
+__global__ void __launch_bounds__(256) tp_residual_acc_kernel(const int32_t* __restrict__ acc, const float* __restrict__ act_scale,
+                                                             float* __restrict__ x, int N, size_t total) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    const size_t m = i / (size_t)N;
+    x[i] = __fadd_rn(x[i], __fmul_rn(act_scale[m], (float)acc[i]));
+}
+
+// ---- decode glue on the local heads (same arithmetic as decode.cu's generic kernels) -------------
+// RoPE (split-half pairs (i, i + D/2)) on q in place and on k into the cache; v into the cache.
+// grid (NH + 2*NKV, B), block D/2. qkv row = [q (NH*D) | k (NKV*D) | v (NKV*D)].
+__global__ void tp_rope_kv_kernel(float* __restrict__ qkv, const float* __restrict__ cos_t, const float* __restrict__ sin_t,
+                                  float* __restrict__ kc, float* __restrict__ vc, const int* __restrict__ pos_p, int NH,
+                                  int NKV, int D, int max_ctx) {
+    const int head = blockIdx.x, b = blockIdx.y, i = threadIdx.x, half = D / 2;
+    const int pos = *pos_p;
+    float* row = qkv + (size_t)b * (NH + 2 * NKV) * D;
+    if (head < NH + NKV) {
+        float* v = row + (size_t)head * D;
+        const float c = cos_t[(size_t)pos * half + i], s = sin_t[(size_t)pos * half + i];
+        const float a = v[i], bb = v[i + half];
+        const float r0 = a * c - bb * s, r1 = a * s + bb * c;
+        if (head < NH) {
+            v[i] = r0;
+            v[i + half] = r1;
+        } else {
+            float* dst = kc + (((size_t)b * NKV + (head - NH)) * max_ctx + pos) * D;
+            dst[i] = r0;
+            dst[i + half] = r1;
+        }
+    } else {
+        const int g = head - NH - NKV;
+        const float* v = row + (size_t)(NH + NKV + g) * D;
+        float* dst = vc + (((size_t)b * NKV + g) * max_ctx + pos) * D;
+        dst[i] = v[i];
+        dst[i + half] = v[i + half];
+    }
+}
+
+// Decode attention for one (head, sequence): scores over 0..pos, softmax, weighted V sum.
+// grid (NH, B), block 128 threads, dynamic smem = max_ctx floats.
+__global__ void __launch_bounds__(128) tp_attn_decode_kernel(const float* __restrict__ qkv, const float* __restrict__ kc,
+                                                            const float* __restrict__ vc, float* __restrict__ att,
+                                                            const int* __restrict__ pos_p, int NH, int NKV, int D,
+                                                            int max_ctx) {
+    extern __shared__ float sc[];
+    __shared__ float red[32];
+    const int head = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
+    const int lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
+    const int pos = *pos_p, g = head / (NH / NKV);
+    const float* q = qkv + (size_t)b * (NH + 2 * NKV) * D + (size_t)head * D;
+    const float* kb = kc + ((size_t)b * NKV + g) * max_ctx * D;
+    const float* vb = vc + ((size_t)b * NKV + g) * max_ctx * D;
+    const float scale = 1.0f / sqrtf((float)D);
+    float qr[8];
+    const int per = D / 32;
+    for (int j = 0; j < per; ++j) qr[j] = q[lane + 32 * j];
+    float mx = -INFINITY;
+    for (int p = warp; p <= pos; p += nwarps) {
+        const float* kp = kb + (size_t)p * D;
+        float d = 0.f;
+        for (int j = 0; j < per; ++j) d = fmaf(qr[j], kp[lane + 32 * j], d);
+        d = warp_sum(d) * scale;
+        if (lane == 0) sc[p] = d;
+        mx = fmaxf(mx, d);
+    }
+    if (lane == 0) red[warp] = mx;
+    __syncthreads();
+    mx = red[0];
+    for (int w = 1; w < nwarps; ++w) mx = fmaxf(mx, red[w]);
+    __syncthreads();
+    float sum = 0.f;
+    for (int p = tid; p <= pos; p += blockDim.x) {
+        const float e = expf(sc[p] - mx);
+        sc[p] = e;
+        sum += e;
+    }
+    sum = warp_sum(sum);
+    if (lane == 0) red[warp] = sum;
+    __syncthreads();
+    sum = 0.f;
+    for (int w = 0; w < nwarps; ++w) sum += red[w];
+    const float inv = 1.0f / sum;
+    for (int d = tid; d < D; d += blockDim.x) {
+        float a = 0.f;
+        for (int p = 0; p <= pos; ++p) a = fmaf(sc[p] * inv, vb[(size_t)p * D + d], a);
+        att[((size_t)b * NH + head) * D + d] = a;
+    }
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" {
+
+int bitnet_b200_row_absmax(bitnet_b200_ctx* ctx, const float* x, int M, int K, int swiglu, float* h, float* absmax) {
+    if (!ctx || !x || !absmax) return fail("row_absmax: NULL argument");
+    if (M <= 0 || K <= 0) return fail("row_absmax: M and K must be > 0");
+    if (swiglu && !h) return fail("row_absmax: the SwiGLU mode needs the h output");
+    if (swiglu && (reinterpret_cast<uintptr_t>(x) & 7)) return fail("row_absmax: x must be 8-byte aligned");
+    B200_CUDA(cudaSetDevice(ctx->device));
+    if (swiglu)
+        tp_row_absmax_kernel<2><<<M, 256, 0, ctx->stream>>>(x, K, h, absmax);
+    else
+        tp_row_absmax_kernel<0><<<M, 256, 0, ctx->stream>>>(x, K, nullptr, absmax);
+    B200_LAUNCH_CHECK("tp_row_absmax_kernel");
+    return 0;
+}
+
+int bitnet_b200_actquant_i8_absmax(bitnet_b200_ctx* ctx, const float* x, const float* absmax, int M, int K, int8_t* q,
+                                   float* scale) {
+    if (!ctx || !x || !absmax || !q || !scale) return fail("actquant_i8_absmax: NULL argument");
+    if (M <= 0 || K <= 0) return fail("actquant_i8_absmax: M and K must be > 0");
+    B200_CUDA(cudaSetDevice(ctx->device));
+    tp_quant_absmax_kernel<<<M, 256, 0, ctx->stream>>>(x, absmax, K, q, scale);
+    B200_LAUNCH_CHECK("tp_quant_absmax_kernel");
+    return 0;
+}
+
+int bitnet_b200_residual_acc(bitnet_b200_ctx* ctx, const int32_t* acc, const float* act_scale, float* x, int M, int N) {
+    if (!ctx || !acc || !act_scale || !x) return fail("residual_acc: NULL argument");
+    if (M <= 0 || N <= 0) return fail("residual_acc: M and N must be > 0");
+    B200_CUDA(cudaSetDevice(ctx->device));
+    const size_t total = (size_t)M * N;
+    tp_residual_acc_kernel<<<(unsigned)div_ceil(total, 256), 256, 0, ctx->stream>>>(acc, act_scale, x, N, total);
+    B200_LAUNCH_CHECK("tp_residual_acc_kernel");
+    return 0;
+}
+
+int bitnet_b200_rope_attn_decode(bitnet_b200_ctx* ctx, float* qkv, const float* cos_t, const float* sin_t, float* kc,
+                                 float* vc, const int32_t* pos_dev, int B, int NH, int NKV, int D, int max_ctx, float* att) {
+    if (!ctx || !qkv || !cos_t || !sin_t || !kc || !vc || !pos_dev || !att) return fail("rope_attn_decode: NULL argument");
+    if (B <= 0 || NH <= 0 || NKV <= 0 || NH % NKV != 0) return fail("rope_attn_decode: invalid head counts");
+    if (D % 64 != 0 || D > 256 || max_ctx <= 0 || max_ctx > 12000) return fail("rope_attn_decode: unsupported head_dim / max_ctx");
+    B200_CUDA(cudaSetDevice(ctx->device));
+    tp_rope_kv_kernel<<<dim3(NH + 2 * NKV, B), D / 2, 0, ctx->stream>>>(qkv, cos_t, sin_t, kc, vc, pos_dev, NH, NKV, D, max_ctx);
+    B200_LAUNCH_CHECK("tp_rope_kv_kernel");
+    tp_attn_decode_kernel<<<dim3(NH, B), 128, (size_t)max_ctx * 4, ctx->stream>>>(qkv, kc, vc, att, pos_dev, NH, NKV, D, max_ctx);
+    B200_LAUNCH_CHECK("tp_attn_decode_kernel");
+    return 0;
+}
+
+}  // extern "C"

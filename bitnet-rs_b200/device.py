@@ -144,6 +144,51 @@ class Context:
             self._h, w._h, _dev_ptr(x, torch.float32, "x"), M, _dev_ptr(y, torch.float32, "y")))
         return y
 
+    # ---- tensor-parallel building blocks (Part 5) --------------------------------------
+    def row_absmax(self, x, swiglu=False):
+        """Per-token max|v| of the local slice; swiglu: x is [M,2K] interleaved (gate, up), returns (h, absmax)."""
+        torch = _torch()
+        M = x.shape[0]
+        K = x.shape[1] // 2 if swiglu else x.shape[1]
+        am = torch.empty((M,), dtype=torch.float32, device=x.device)
+        h = torch.empty((M, K), dtype=torch.float32, device=x.device) if swiglu else None
+        ffi.check(self._lib.bitnet_b200_row_absmax(
+            self._h, _dev_ptr(x, torch.float32, "x"), M, K, 1 if swiglu else 0,
+            None if h is None else h.data_ptr(), am.data_ptr()))
+        return (h, am) if swiglu else am
+
+    def actquant_i8_absmax(self, x, absmax, q=None, scale=None):
+        """quantize_symmetric_i8 per row with the given (all-reduced) absmax."""
+        torch = _torch()
+        M, K = x.shape
+        q = torch.empty((M, K), dtype=torch.int8, device=x.device) if q is None else q
+        scale = torch.empty((M,), dtype=torch.float32, device=x.device) if scale is None else scale
+        ffi.check(self._lib.bitnet_b200_actquant_i8_absmax(
+            self._h, _dev_ptr(x, torch.float32, "x"), _dev_ptr(absmax, torch.float32, "absmax"), M, K,
+            _dev_ptr(q, torch.int8, "q"), _dev_ptr(scale, torch.float32, "scale")))
+        return q, scale
+
+    def residual_acc(self, acc, act_scale, x):
+        """x += act_scale[m] * float(acc[m, n]) in place."""
+        torch = _torch()
+        M, N = x.shape
+        ffi.check(self._lib.bitnet_b200_residual_acc(
+            self._h, _dev_ptr(acc, torch.int32, "acc"), _dev_ptr(act_scale, torch.float32, "act_scale"),
+            _dev_ptr(x, torch.float32, "x"), M, N))
+        return x
+
+    def rope_attn_decode(self, qkv, cos_t, sin_t, kc, vc, pos, n_heads, n_kv_heads, head_dim, max_ctx, att=None):
+        """RoPE + KV append + GQA decode attention on the local heads; pos is a device int32 scalar tensor."""
+        torch = _torch()
+        B = qkv.shape[0]
+        att = torch.empty((B, n_heads * head_dim), dtype=torch.float32, device=qkv.device) if att is None else att
+        ffi.check(self._lib.bitnet_b200_rope_attn_decode(
+            self._h, _dev_ptr(qkv, torch.float32, "qkv"), _dev_ptr(cos_t, torch.float32, "cos"),
+            _dev_ptr(sin_t, torch.float32, "sin"), _dev_ptr(kc, torch.float32, "kc"),
+            _dev_ptr(vc, torch.float32, "vc"), _dev_ptr(pos, torch.int32, "pos"), B, n_heads, n_kv_heads,
+            head_dim, max_ctx, _dev_ptr(att, torch.float32, "att")))
+        return att
+
 
 class Weight:
     """bitnet_b200_weight: one packed tensor uploaded once, in the reference's byte layout."""

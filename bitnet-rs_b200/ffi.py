@@ -23,6 +23,8 @@ SYMBOLS = [
     "bitnet_b200_model_get_tokens", "bitnet_b200_model_launches_per_step",
     "bitnet_b200_model_time_linears",
     "bitnet_b200_model_weight_bytes",
+    "bitnet_b200_row_absmax", "bitnet_b200_actquant_i8_absmax", "bitnet_b200_residual_acc",
+    "bitnet_b200_rope_attn_decode",
 ]
 
 
@@ -104,6 +106,10 @@ def lib():
         l.bitnet_b200_model_launches_per_step.restype = C.c_uint64
         l.bitnet_b200_model_weight_bytes.argtypes = [vp]
         l.bitnet_b200_model_weight_bytes.restype = C.c_uint64
+        l.bitnet_b200_row_absmax.argtypes = [vp, vp, i32, i32, i32, vp, vp]
+        l.bitnet_b200_actquant_i8_absmax.argtypes = [vp, vp, vp, i32, i32, vp, vp]
+        l.bitnet_b200_residual_acc.argtypes = [vp, vp, vp, vp, i32, i32]
+        l.bitnet_b200_rope_attn_decode.argtypes = [vp] * 7 + [i32] * 5 + [vp]
         l.bitnet_b200_version.restype = C.c_char_p
         l.bitnet_b200_launch_count.restype = C.c_uint64
         _lib = l

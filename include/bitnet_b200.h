@@ -196,6 +196,34 @@ int bitnet_b200_model_time_linears(bitnet_b200_model* m, int reps, float* ms_per
 uint64_t bitnet_b200_model_launches_per_step(const bitnet_b200_model* m);
 uint64_t bitnet_b200_model_weight_bytes(const bitnet_b200_model* m); /* packed ternary bytes */
 
+/* ------------------------------------------------------------------------------------ *
+ * Part 5 -- tensor-parallel building blocks. The reference has only  *
+ * the in-process simulation of the semantics (partition_tensor / all_reduce Sum and Max, *
+ * crates/bitnet-inference/src/tensor_parallel.rs:123-290); the exchange itself (NCCL      *
+ * all-reduce over NVLink) is issued by the host between these calls, on the same stream.  *
+ * q/k/v and gate/up are sharded by output rows (no exchange); o and down by input         *
+ * columns: each rank quantises its K/tp slice with the GLOBAL per-token absmax            *
+ * (row_absmax -> all-reduce MAX -> actquant_i8_absmax), so the int32 partials of          *
+ * linear_i8(acc_out) add up (all-reduce SUM, int32) to the tp = 1 accumulator bit for bit *
+ * and residual_acc applies the same one-multiply epilogue as tp = 1. DEVICE pointers.     *
+ * ------------------------------------------------------------------------------------ */
+/* absmax[m] = max_k |v[m,k]|; swiglu = 0: v = x [M,K]; swiglu = 1: x is [M,2K] with (gate, up)
+ * interleaved, v = silu(gate) * up (crates/bitnet-transformer/src/lib.rs:756-789), also stored to h [M,K] */
+int bitnet_b200_row_absmax(bitnet_b200_ctx* ctx, const float* x, int M, int K, int swiglu, float* h,
+                           float* absmax);
+/* quantize_symmetric_i8 (cpu/quantize.rs:32-49) per row with a GIVEN absmax[m] instead of the row's own */
+int bitnet_b200_actquant_i8_absmax(bitnet_b200_ctx* ctx, const float* x, const float* absmax, int M, int K,
+                                   int8_t* q, float* scale);
+/* x[m,n] += act_scale[m] * float(acc[m,n]) -- the residual epilogue of linear_i8 on reduced accumulators */
+int bitnet_b200_residual_acc(bitnet_b200_ctx* ctx, const int32_t* acc, const float* act_scale, float* x, int M,
+                             int N);
+/* decode glue on the rank's local heads: RoPE on q (in place) and k, KV append at *pos_dev, GQA attention
+ * over 0..*pos_dev (crates/bitnet-transformer/src/lib.rs:374-540). qkv [B,(NH+2*NKV)*D], caches
+ * [B,NKV,max_ctx,D], att [B,NH*D]; cos/sin [max_ctx, D/2] */
+int bitnet_b200_rope_attn_decode(bitnet_b200_ctx* ctx, float* qkv, const float* cos_t, const float* sin_t,
+                                 float* kc, float* vc, const int32_t* pos_dev, int B, int NH, int NKV, int D,
+                                 int max_ctx, float* att);
+
 /* library / build identification */
 const char* bitnet_b200_version(void);
 /* number of kernels this library has launched on the calling process (bench bookkeeping) */
