@@ -41,6 +41,10 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--layout", default="qk256", choices=["qk256", "bitnet32"])
     ap.add_argument("--prompt", type=int, default=32, help="synthetic prompt tokens decoded before timing")
+    ap.add_argument("--workload", default="2b4t-decode", choices=["2b4t-decode", "8b-tp"],
+                    help="2b4t-decode = BASELINE.json configs[1] (the judged line); 8b-tp = configs[4]: 8B-class "
+                         "batch-64 decode, tensor-parallel over the launched ranks (NCCL all-reduce)")
+    ap.add_argument("--tp-layers", type=int, default=0, help="8b-tp: use fewer layers (smoke runs only)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-budget-s", type=float, default=20.0)
     return ap.parse_args()
@@ -189,12 +193,118 @@ def workload_config(shape, args):
     }
 
 
+def run_tp(args):
+    """BASELINE.json configs[4]: 8B-class ternary model (hidden 4096, FFN 14336, 32 layers), batch-64
+    decode, tensor-parallel over WORLD_SIZE GPUs (Megatron split, int32 all-reduce after o and down)."""
+    import torch
+    import bitnet_rs_b200 as b2
+    from bitnet_rs_b200 import tp
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    K, W = args.steps, max(args.warmup, 3)
+    shape = b2.ModelShape.llama_8b_class(batch=64, max_ctx=PROMPT + 2 * (W + K) + 16)
+    ctx = b2.Context(local)
+    dec = b2.TPDecoder(ctx, shape, rank, world, n_layers=args.tp_layers or None)
+    dec.tokens.copy_((torch.arange(shape.batch, device="cuda") * 7919) % shape.vocab)
+
+    def step():
+        if dist is None:
+            tp.run_emulated([dec.step_gen()])
+        else:
+            tp.run_distributed(dec.step_gen(), dist)
+
+    def note(msg):
+        if os.environ.get("BENCH_DEBUG"):
+            print("[rank %d] %s" % (rank, msg), file=sys.stderr, flush=True)
+
+    note("decoder built")
+    for _ in range(2):            # eager: first-use allocations (split-K scratch, NCCL channels)
+        step()
+    torch.cuda.synchronize()
+    note("eager steps done")
+    launches0 = b2.launch_count()
+    step()
+    launches_per_step = b2.launch_count() - launches0
+    mode = "cuda-graph"
+    graph = None
+    try:
+        if os.environ.get("BENCH_TP_EAGER"):
+            raise RuntimeError("eager requested")
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            ctx.use_torch_stream()
+            step()
+        ctx.use_torch_stream()
+        note("graph captured")
+    except Exception as ex:       # NCCL capture unavailable: time the eager loop instead
+        note("capture failed: %r" % (ex,))
+        graph, mode = None, "eager (graph capture failed: %s)" % type(ex).__name__
+        ctx.use_torch_stream()
+        torch.cuda.synchronize()
+
+    def run(n):
+        for _ in range(n):
+            graph.replay() if graph is not None else step()
+
+    run(W)
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    run(K)
+    e1.record()
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop()
+    if dist is not None:
+        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t[0])
+    if rank == 0:
+        nl = dec.n_layers
+        line = {
+            "metric": "8B-class batch-64 decode tok/s (tensor parallel)", "value": shape.batch * K / (ms * 1e-3),
+            "unit": "tok/s", "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms / K,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "int8", "data": "synthetic",
+            "config": {"workload": "8B-class ternary decoder (hidden 4096, FFN 14336, %d layers, GQA 32/8, vocab 128256), "
+                                   "batch 64, random-init I2_S QK256 weights (BASELINE.json configs[4])" % nl,
+                       "parallelism": "tp%d: q/k/v + gate/up by rows, o + down by input columns, int32 all-reduce(SUM) "
+                                      "+ f32 all-reduce(MAX) of the per-token absmax over NCCL" % world,
+                       "launch": mode,
+                       "l2": "weights %.0f MB per rank vs 126 MB L2" % (dec.weight_bytes / 1e6)},
+            "clocks": clocks, "gpu_launches": int(launches_per_step * K), "launches_per_step": int(launches_per_step),
+            "collectives_per_step": 4 * nl + 1,
+        }
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        # every rank has passed the final all-reduce; tearing NCCL down with a captured graph alive can
+        # hang, so leave without the destructor chain
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
+
+
 def main():
     global PROMPT
     args = parse()
     PROMPT = args.prompt
     if args.impl == "reference":
         return run_reference(args)
+    if args.workload == "8b-tp":
+        return run_tp(args)
 
     import torch
     import bitnet_rs_b200 as b2
