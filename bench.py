@@ -372,6 +372,16 @@ def main():
     alg = linear_alg_bytes(shape, B)
     peak, peak_src = measured_peak()
     achieved = alg / (ms_lin * 1e-3) / 1e9
+    # dram__bytes_read + dram__bytes_write of the same launch from the committed ncu --set full capture
+    # (profiles/r01_ncu_summary.json); not measured live -- a number taken under ncu is never a bench value
+    traffic, traffic_src = None, None
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_ncu_summary.json")) as f:
+            ent = json.load(f)["decode_mega_kernel_mode1_gemv_phases"]
+        if n_lin == 1 and shape.layout == b2.LAYOUT_QK256 and B == 1:
+            traffic, traffic_src = ent["traffic_bytes_per_launch"], "profiles/r01_ncu_summary.json (ncu --set full, same launch)"
+    except Exception:
+        pass
 
     if dist is not None:
         t = torch.tensor([ms_dev, ms_e2e], device="cuda", dtype=torch.float64)
@@ -388,9 +398,12 @@ def main():
                     "d2h_bytes_per_step": 4 * B, "ms_per_step": ms_e2e / K},
             "gpu_launches": int(launches_timed),
             "launches_per_step": model.launches_per_step,
-            "roofline": {"bound": "hbm", "kernel": "gemv_i8_kernel (ternary GEMV, M=%d)" % B,
+            "roofline": {"bound": "hbm",
+                         "kernel": "decode_mega_kernel restricted to its %d ternary GEMV phases (M=%d): one launch "
+                                   "streams every packed ternary weight of the model once" % (4 * shape.n_layers, B)
+                         if n_lin == 1 else "ternary GEMV launches of one step (M=%d), graph-replayed" % B,
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": peak_src,
+                         "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": alg / n_lin, "launches_per_pass": n_lin,
                          "us_per_launch": ms_lin * 1e3 / n_lin,
                          "pct_of_8TBs_nominal": 100.0 * achieved / 8000.0,

@@ -1,4 +1,4 @@
-// gemm_tcgen05.cu -- the batched / prefill regime of the ternary linear (M > 8): a dense
+// gemm_tcgen05.cu -- the batched / prefill regime of the ternary linear (M >= 9): a dense
 // contraction on the 5th-generation tensor cores, tcgen05.mma kind::i8 with the int32 accumulator
 // in tensor memory (TMEM), operands fed by TMA. QK256 layout.
 //
@@ -11,23 +11,32 @@
 //
 // Shape of the kernel (persistent, one CTA per SM, 15 warps with fixed roles):
 //   * the WEIGHTS are the A operand (UMMA M = 128 weight rows per tile), the TOKENS the B operand
-//     (UMMA N = BN = up to 256 tokens): one expansion of a 128 x 128 block of 2-bit codes feeds
+//     (UMMA N = BN = 16..256 tokens): one expansion of a 128 x 128 block of 2-bit codes feeds
 //     128 x BN x 128 MACs, and the accumulator sits in TMEM as [weight row = lane][token = column],
 //     so the epilogue's stores of y[m, n0 .. n0+31] are 128-byte coalesced per warp;
 //   * warp 0  : TMA producer of the int8 token tiles  (2-D tensor map over q[M,K], box 128 B x BN rows,
 //               SWIZZLE_128B; rows beyond M are zero-filled by the TMA unit -> ragged M costs nothing);
-//   * warp 14 : TMA producer of the packed 2-bit codes (box 128 B x 128 rows = 512 k of 128 rows, 16 KB,
-//               SWIZZLE_128B), its own deeper ring: in the small-M regime this is the HBM stream;
-//   * warps 6-13: decoders. Thread = (weight row, 64-k half): one conflict-free 128-bit shared load of
-//               packed codes, four PRMT LUT decodes (common.cuh), four 128-bit stores into the
-//               canonical K-major SWIZZLE_128B operand tile, fence.proxy.async, mbarrier arrive;
-//   * warp 1  : MMA issuer: one elected lane issues four tcgen05.mma (K = 32 each) per 128-k block and
-//               frees the stage with tcgen05.commit -> mbarrier; two TMEM accumulator stages
-//               (2 x 256 columns) so the epilogue of tile i overlaps the main loop of tile i+1;
-//   * warps 2-5: epilogue: tcgen05.ld (32 lanes x 32 columns) -> act_scale * float(acc) -> y.
-//   * small M (few output tiles): split-K over CTAs so that all 148 SMs stream weights; the int32
-//     partials meet in an L2-resident block through RED.ADD, the last CTA of a tile (ticket counter)
-//     scales it into y -- integer addition, so the result is independent of arrival order, bit-exact.
+//               its own ring of up to 16 stages: this is where L2 latency is hidden;
+//   * warp 14 : TMA producer of the packed 2-bit codes (box 64 B x 128 rows = 256 k of 128 rows, 8 KB,
+//               SWIZZLE_64B), its own ring: in the small-M regime this is the HBM stream;
+//   * warps 6-13: decoders, four groups of two warps, group g expands k-blocks g, g+4, ... so four
+//               k-blocks are in flight. Thread = 4 x (weight row, 64-k half): one conflict-free 128-bit
+//               shared load of packed codes, four PRMT LUT decodes (common.cuh), four 128-bit stores into
+//               the canonical K-major SWIZZLE_128B operand tile each, fence.proxy.async, mbarrier arrive.
+//               A packed stage is released only AFTER its codes have been consumed (an early release let
+//               the next TMA box overwrite codes whose shared loads were still in flight);
+//   * warp 1  : MMA issuer. The loop is warp-uniform (descriptors and barrier addresses in uniform
+//               registers) and one elected lane issues four tcgen05.mma (K = 32 each) per 128-k block, then
+//               tcgen05.commit -> mbarrier frees the A and B stages. Its instruction count per k-block is
+//               the critical path of the CTA at small BN (measured: 0.3 us per k-block issue-bound vs
+//               0.43 us MMA-bound at BN = 256 under the 1 kW power cap), so nothing else lives in it.
+//               Two TMEM accumulator stages (2 x 256 columns): the epilogue of tile i overlaps tile i+1;
+//   * warps 2-5: epilogue: act scales prefetched before the accumulator is ready, tcgen05.ld (32 lanes x
+//               32 columns) -> act_scale * float(acc) -> y.
+//   * few output tiles (small M): the host picks BN and a split-K factor S from a small cost model so
+//     that all 148 SMs stream weights; the int32 partials meet in an L2-resident block through RED.ADD,
+//     the last CTA of a tile (ticket counter) scales it into y and re-zeroes the block -- integer
+//     addition, so the result is independent of arrival order and stays bit-exact.
 #include <cuda.h>
 
 #include <mutex>

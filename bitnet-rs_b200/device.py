@@ -111,7 +111,8 @@ class Context:
         acc = None
         if want_acc:
             shape = (M, w.rows) if w.layout == LAYOUT_QK256 else (M, w.rows, w.cols // 32)
-            acc = torch.zeros(shape, dtype=torch.int32, device=q.device)
+            # QK256: the kernel writes every accumulator; BitNet32-F16 blocks are zero-initialised
+            acc = (torch.empty if w.layout == LAYOUT_QK256 else torch.zeros)(shape, dtype=torch.int32, device=q.device)
         ffi.check(self._lib.bitnet_b200_linear_i8(
             self._h, w._h, _dev_ptr(q, torch.int8, "q"), _dev_ptr(act_scale, torch.float32, "act_scale"),
             M, _dev_ptr(y, torch.float32, "y"), None if acc is None else acc.data_ptr()))
