@@ -35,6 +35,8 @@ int launch_gemv_fast(const bitnet_b200_ctx*, const bitnet_b200_weight*, int M, i
 int launch_gemm_i8(const bitnet_b200_ctx*, const bitnet_b200_weight*, const int8_t*, const float*,
                    int, float*, int32_t*);
 bool gemm_i8_supported(const bitnet_b200_weight*, int M);
+int launch_gemm_f16(const bitnet_b200_ctx*, const bitnet_b200_weight*, const int8_t*, const float*, int, float*);
+bool gemm_f16_supported(const bitnet_b200_weight*, int M);
 int launch_actquant(const bitnet_b200_ctx*, const float*, const float*, float, int, int, int8_t*,
                     float*, float*, int mode);
 int launch_quantize_weights(cudaStream_t, const float*, int, uint8_t*, int, float*, int);
@@ -392,6 +394,8 @@ int bitnet_b200_linear_i8(bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, con
     const bool force_gemv = acc_out && w->layout == BITNET_B200_LAYOUT_BITNET32_F16;
     if (!force_gemv && gemm_i8_supported(w, M))
         return launch_gemm_i8(ctx, w, q, act_scale, M, y, acc_out);
+    if (!acc_out && gemm_f16_supported(w, M))  // BitNet32-F16, M >= 9: tcgen05 kind::f16 on s * LUT[code]
+        return launch_gemm_f16(ctx, w, q, act_scale, M, y);
     if (M <= 8 && !getenv("BITNET_B200_NO_STREAM")) {  // decode fast path (gemv_stream.cu); 1 = shape not covered
         const int rc = launch_gemv_fast(ctx, w, M, /*PRO_Q8*/ 0, q, act_scale, nullptr, nullptr, 0.f, /*EPI_STORE*/ 0,
                                           y, nullptr, acc_out, nullptr, nullptr, nullptr,

@@ -256,7 +256,7 @@ struct bitnet_b200_model {
     int fused = -1;             // -1 undecided, 0 generic kernels, 1 fused PDL path
     int mega = -1;              // -1 undecided, 0 no, 1 the persistent one-kernel step (decode_mega.cu)
     MegaLayer* mega_layers = nullptr;  // device table
-    unsigned* mega_bar = nullptr;      // [2] grid-barrier counters
+    unsigned* mega_bar = nullptr;      // [2][8] grid-barrier counters, one per 256-byte line
     int mega_parity = 0;
     size_t mega_smem = 0;
     MegaParams mega_p{};
@@ -494,10 +494,10 @@ static int mega_setup(bitnet_b200_model* m) {
             if (w->code_stride != w->cols / 4 || w->lut_word != m->layers[0].wqkv->lut_word) return 0;
         tab[(size_t)l] = MegaLayer{L.wqkv->codes, L.wo->codes, L.wgateup->codes, L.wdown->codes, L.attn_norm, L.ffn_norm};
     }
-    if (dmalloc((void**)&m->mega_layers, tab.size() * sizeof(MegaLayer)) || dmalloc((void**)&m->mega_bar, 8)) return -1;
+    if (dmalloc((void**)&m->mega_layers, tab.size() * sizeof(MegaLayer)) || dmalloc((void**)&m->mega_bar, 4096)) return -1;  // 2 parities x 8 counters on 256-byte lines
     cudaStream_t st = m->ctx->stream;
     B200_CUDA(cudaMemcpyAsync(m->mega_layers, tab.data(), tab.size() * sizeof(MegaLayer), cudaMemcpyHostToDevice, st));
-    B200_CUDA(cudaMemsetAsync(m->mega_bar, 0, 8, st));
+    B200_CUDA(cudaMemsetAsync(m->mega_bar, 0, 4096, st));
     B200_CUDA(cudaStreamSynchronize(st));
     p.layers = m->mega_layers;
     p.emb = m->emb; p.final_norm = m->final_norm; p.rope_cos = m->rope_cos; p.rope_sin = m->rope_sin;

@@ -89,18 +89,31 @@ __device__ __forceinline__ void mbar_wait_backoff(void* bar, uint32_t parity) {
 }
 
 // Grid-wide barrier over the consumer threads of all CTAs (the kernel is launched cooperatively,
-// so all CTAs are resident). Bounded spin: a lost arrival traps instead of hanging the GPU.
+// so all CTAs are resident). Arrivals are spread over MEGA_BAR_CTRS counters on separate 256-byte
+// lines: same-address atomics serialise at the L2 (~27 cycles each, i.e. ~2 us for 148 CTAs on one
+// counter, which is what a single-counter barrier measured); eight lanes of warp 0 poll one counter
+// each with ld.acquire and the warp sums them. Bounded spin: a lost arrival traps instead of hanging.
+constexpr int MEGA_BAR_CTRS = 8, MEGA_BAR_STRIDE = 64;  // counters per parity, stride in 32-bit words
 __device__ __forceinline__ void grid_sync(unsigned* ctr, unsigned& target, unsigned ncta) {
     target += ncta;
     cons_sync();
-    if (threadIdx.x == 0) {
-        asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(ctr) : "memory");
-        unsigned v;
+    if (threadIdx.x < 32) {
+        const unsigned lane = threadIdx.x;
+        if (lane == 0)
+            asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(ctr + (blockIdx.x % MEGA_BAR_CTRS) * MEGA_BAR_STRIDE)
+                         : "memory");
+        unsigned sum;
         uint32_t it = 0;
         do {
-            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
+            unsigned v = 0;
+            if (lane < MEGA_BAR_CTRS)
+                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr + lane * MEGA_BAR_STRIDE) : "memory");
+            sum = v;
+#pragma unroll
+            for (int o = 4; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+            sum = __shfl_sync(0xffffffffu, sum, 0);
             if (++it > (1u << 24)) __trap();
-        } while (v < target);
+        } while (sum < target);
     }
     cons_sync();
 }
@@ -738,7 +751,8 @@ __global__ void __launch_bounds__(MEGA_THREADS, 1) decode_mega_kernel(const __gr
             mbar_init(&sm.empty[s], MEGA_NW);
         }
         mbar_fence_init();
-        if (cta == 0) p.bar[p.parity ^ 1] = 0u;  // the counter of the NEXT launch (its last user has finished)
+        if (cta == 0)  // the counters of the NEXT launch (their last user has finished)
+            for (int j = 0; j < MEGA_BAR_CTRS; ++j) p.bar[((p.parity ^ 1) * MEGA_BAR_CTRS + j) * MEGA_BAR_STRIDE] = 0u;
     }
     for (int i = tid; i < p.L * (int)(sizeof(MegaLayer) / 8); i += MEGA_THREADS)
         reinterpret_cast<uint64_t*>(sm.layers)[i] = reinterpret_cast<const uint64_t*>(p.layers)[i];
@@ -750,7 +764,7 @@ __global__ void __launch_bounds__(MEGA_THREADS, 1) decode_mega_kernel(const __gr
     }
 
     // ---- consumers ------------------------------------------------------------------------------
-    unsigned* ctr = p.bar + p.parity;
+    unsigned* ctr = p.bar + p.parity * (MEGA_BAR_CTRS * MEGA_BAR_STRIDE);
     unsigned target = 0;
     RingPos rp{0u, 0u};
     int tcount = 0, pi = 0;

@@ -383,8 +383,37 @@ def test_linear_bitnet32(ctx, b200, oracle, rows, cols, M):
     y = y.cpu().numpy()
     assert _rel(y, ry) < 1e-5                                      # same math, different fp32 sum order
     assert _rel(y, oracle.linear_bitnet32_dequant(data, rows, cols, q, s)) < 1e-3   # the north_star bar
-    assert torch.equal(ctx.linear_i8(w, dev(q), dev(s)).cpu(), torch.from_numpy(y)) or \
-        _rel(ctx.linear_i8(w, dev(q), dev(s)).cpu().numpy(), y) < 1e-6
+    # the no-accumulator path: same GEMV at M <= 8, the tcgen05 kind::f16 GEMM at M >= 9 (fp32 sum order differs)
+    y2 = ctx.linear_i8(w, dev(q), dev(s)).cpu().numpy()
+    assert _rel(y2, y) < (1e-6 if M <= 8 else 2e-5)
+
+
+# ---- M >= 9: the tcgen05 kind::f16 GEMM on s * LUT[code] (gemm_f16_tcgen05.cu) -------------------
+@pytest.mark.parametrize("rows,cols,M", [
+    (128, 64, 16), (128, 256, 9), (100, 1024, 33), (640, 2560, 64), (2560, 6912, 64), (3840, 2560, 300),
+    (6912, 2560, 1000), (2560, 2560, 2048), (4096, 512, 64), (130, 320, 129),
+])
+def test_linear_bitnet32_gemm_tcgen05(ctx, b200, oracle, rows, cols, M):
+    data = oracle.make_bitnet32(rows, cols, 0xB2000040 + rows + M)
+    x = oracle.fill_normal(M * cols, 47 + rows).reshape(M, cols)
+    q, s = oracle.quantize_rows_i8(x)
+    w = ctx.weight(data, b200.LAYOUT_BITNET32_F16, rows, cols)
+    y = ctx.linear_i8(w, dev(q), dev(s)).cpu().numpy()
+    ry = oracle.linear_bitnet32_i8(data, rows, cols, q, s)         # block-ordered int32 x scale
+    assert _rel(y, ry) < 2e-5                                      # exact products, fp32 sum order differs
+    assert _rel(y, oracle.linear_bitnet32_dequant(data, rows, cols, q, s)) < 1e-3   # the north_star bar
+    assert np.array_equal(ctx.linear_i8(w, dev(q), dev(s)).cpu().numpy(), y) or rows * M < 148 * 128 * 16
+
+
+def test_linear_bitnet32_gemm_other_code_map(ctx, b200, oracle):
+    rows, cols, M = 192, 1024, 70
+    data = oracle.make_bitnet32(rows, cols, 77)
+    x = oracle.fill_normal(M * cols, 3).reshape(M, cols)
+    q, s = oracle.quantize_rows_i8(x)
+    w = ctx.weight(data, b200.LAYOUT_BITNET32_F16, rows, cols, lut=oracle.MAP_C)
+    y = ctx.linear_i8(w, dev(q), dev(s)).cpu().numpy()
+    ry = oracle.linear_bitnet32_i8(data, rows, cols, q, s, oracle.MAP_C)
+    assert _rel(y, ry) < 2e-5
 
 
 @pytest.mark.parametrize("policy", ["SCALE_ABS_CLAMP", "SCALE_RAW"])
