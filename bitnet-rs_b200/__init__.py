@@ -45,7 +45,7 @@ from .model import (  # noqa: F401
     synth_weight,
 )
 
-from . import tp  # noqa: F401,E402
+from . import gguf, tp  # noqa: F401,E402
 from .tp import TPDecoder  # noqa: F401,E402
 
 __all__ = [
