@@ -41,7 +41,7 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--layout", default="qk256", choices=["qk256", "bitnet32"])
     ap.add_argument("--prompt", type=int, default=32, help="synthetic prompt tokens decoded before timing")
-    ap.add_argument("--workload", default="2b4t-decode", choices=["2b4t-decode", "8b-tp"],
+    ap.add_argument("--workload", default="2b4t-decode", choices=["2b4t-decode", "8b-tp", "sweep"],
                     help="2b4t-decode = BASELINE.json configs[1] (the judged line); 8b-tp = configs[4]: 8B-class "
                          "batch-64 decode, tensor-parallel over the launched ranks (NCCL all-reduce)")
     ap.add_argument("--tp-layers", type=int, default=0, help="8b-tp: use fewer layers (smoke runs only)")
@@ -297,6 +297,131 @@ def run_tp(args):
         os._exit(0)
 
 
+# ------------------------------------------------------------------------------------------
+# Per-layer shape sweep (BASELINE.json configs[0] and configs[2]): the linears of 2B-4T at
+# M = 1, 16, 64, 512, 4096 in both layouts, weights rotated through more copies than L2 holds;
+# beside each M = 1 row the reference's CPU kernel for that layout (oracle port) on this host.
+# Not the headline line: JSON lines, one per row, then one summary line.
+# ------------------------------------------------------------------------------------------
+SWEEP_SHAPES = {"qkv": (3840, 2560), "o": (2560, 2560), "gate/up": (6912, 2560), "down": (2560, 6912)}
+
+
+def _sweep_weight_bytes(rng, layout_name, rows, cols):
+    if layout_name == "qk256":
+        return rng.integers(0, 256, rows * cols // 4, dtype=np.uint8)
+    nb = rows * cols // 32
+    codes = rng.integers(0, 256, (nb, 8), dtype=np.uint8)
+    sc = (rng.uniform(0.5, 1.5, nb) / np.sqrt(cols)).astype(np.float16).view(np.uint8).reshape(nb, 2)
+    return np.concatenate([codes, sc], 1).ravel()
+
+
+def _best_of(fn, budget_s, min_reps=3):
+    fn()
+    ts, t_start = [], time.perf_counter()
+    while len(ts) < min_reps or (time.perf_counter() - t_start < budget_s and len(ts) < 50):
+        t0 = time.perf_counter()
+        fn()
+        ts.append(time.perf_counter() - t0)
+    return min(ts) * 1e6
+
+
+def sweep_cpu_row(layout_name, rows, cols, budget_s):
+    """us per token of the reference's CPU kernel for one linear (oracle port, AVX2):
+    QK256  -> gemv_qk256 (1 thread, and rows split over all host threads);
+    BN32   -> KernelProvider::matmul_i2s on [k, n] unpacked code bytes, m = 1 (configs[0])."""
+    from oracle import pyoracle as orc
+    rng = np.random.default_rng(7)
+    threads = os.cpu_count() or 1
+    if layout_name == "qk256":
+        qs = rng.integers(0, 256, rows * cols // 4, dtype=np.uint8)
+        x = rng.standard_normal(cols).astype(np.float32)
+        one = _best_of(lambda: orc.gemv_qk256(qs, x, rows, cols, cols // 4, "avx2"), budget_s)
+        mt = _best_of(lambda: orc.gemv_qk256(qs, x, rows, cols, cols // 4, "mt", threads=threads), budget_s)
+        return {"kernel": "gemv_qk256_avx2", "us_1thread": one, "us_all_threads": mt, "threads": threads}
+    a = rng.integers(-127, 128, cols, dtype=np.int8)
+    b = rng.integers(0, 3, cols * rows, dtype=np.uint8)
+    one = _best_of(lambda: orc.matmul_i2s(a, b, 1, rows, cols, "avx2"), budget_s)
+    return {"kernel": "matmul_i2s_avx2 (m=1, unpacked [k,n] bytes)", "us_1thread": one, "us_all_threads": None,
+            "threads": 1}
+
+
+def run_sweep(args):
+    import torch
+    import bitnet_rs_b200 as b2
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback)")
+    torch.cuda.set_device(0)
+    ctx = b2.Context(0)
+    peak, peak_src = measured_peak()
+    i8_peak = 4500.0            # TOPS, nominal dense int8/fp8 (B200_PROFILING.md); f16 path: 2250 TFLOP/s
+    ms = [1, 16, 64, 512, 4096]
+    rows_out = []
+
+    def graph_time(fn, iters, reps=5):
+        for i in range(3):
+            fn(i)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            ctx.use_torch_stream()
+            for i in range(iters):
+                fn(i)
+        ctx.use_torch_stream()
+        g.replay()
+        torch.cuda.synchronize()
+        best = 1e30
+        for _ in range(reps):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            g.replay()
+            e1.record()
+            torch.cuda.synchronize()
+            best = min(best, e0.elapsed_time(e1) * 1e3 / iters)
+        return best
+
+    for lname in ("qk256", "bitnet32"):
+        layout = b2.LAYOUT_QK256 if lname == "qk256" else b2.LAYOUT_BITNET32_F16
+        for sname, (rows, cols) in SWEEP_SHAPES.items():
+            wbytes = rows * cols // 4 if lname == "qk256" else rows * cols // 32 * 10
+            ncopies = min(64, max(2, (300 << 20) // wbytes + 1))
+            ws = [ctx.weight(_sweep_weight_bytes(np.random.default_rng(i), lname, rows, cols), layout, rows, cols)
+                  for i in range(ncopies)]
+            cpu = None
+            if not args.no_cpu_baseline:
+                try:
+                    cpu = sweep_cpu_row(lname, rows, cols, args.cpu_budget_s / 16.0)
+                except Exception as ex:
+                    cpu = {"failed": repr(ex)}
+            for M in ms:
+                q = torch.randint(-127, 128, (M, cols), dtype=torch.int8, device="cuda")
+                s = torch.rand(M, device="cuda") + 0.5
+                y = torch.empty(M, rows, device="cuda")
+                iters = 200 if M <= 64 else (50 if M <= 512 else 20)
+                l0 = b2.launch_count()
+                us = graph_time(lambda i: ctx.linear_i8(ws[i % len(ws)], q, s, y=y), iters)
+                alg = wbytes + M * cols + 4 * M + 4 * M * rows
+                tops = 2.0 * M * rows * cols / us / 1e6
+                row = {"workload": "linear_i8", "layout": lname, "shape": sname, "N": rows, "K": cols, "M": M,
+                       "us": round(us, 3), "alg_bytes": alg, "GBs": round(alg / us / 1e3, 1),
+                       "hbm_frac": round(alg / us / 1e3 / peak, 4), "TOPS": round(tops, 1),
+                       "tensor_frac": round(tops / (i8_peak if lname == "qk256" else i8_peak / 2), 4),
+                       "path": "gemv" if M <= 8 else "tcgen05 gemm", "weight_copies": len(ws),
+                       "gpu_launches": b2.launch_count() - l0}
+                if M == 1 and cpu is not None:
+                    row["cpu_baseline"] = cpu
+                    if cpu.get("us_1thread"):
+                        row["gpu_vs_cpu_1thread"] = round(cpu["us_1thread"] / us, 1)
+                rows_out.append(row)
+                print(json.dumps(row), flush=True)
+            del ws
+            torch.cuda.empty_cache()
+    print(json.dumps({"summary": "sweep", "rows": len(rows_out), "hbm_peak_GBs": peak, "peak_source": peak_src,
+                      "int8_peak_TOPS_nominal": i8_peak,
+                      "best_hbm_frac_M1": max(r["hbm_frac"] for r in rows_out if r["M"] == 1),
+                      "best_tensor_frac": max(r["tensor_frac"] for r in rows_out)}), flush=True)
+
+
 def main():
     global PROMPT
     args = parse()
@@ -305,6 +430,8 @@ def main():
         return run_reference(args)
     if args.workload == "8b-tp":
         return run_tp(args)
+    if args.workload == "sweep":
+        return run_sweep(args)
 
     import torch
     import bitnet_rs_b200 as b2

@@ -506,6 +506,7 @@ static int mega_setup(bitnet_b200_model* m) {
     p.part_val = m->part_val; p.part_idx = m->part_idx;
     p.q_fixed = m->q8; p.s_fixed = m->s8; p.bar = m->mega_bar;
     p.lut = m->layers[0].wqkv->lut_word;
+    p.prefetch = getenv("BITNET_B200_MEGA_NOPF") ? 0 : 1;
     if (getenv("BITNET_B200_MEGA_PROF")) {  // diagnostics: per-phase globaltimer stamps of CTA 0, dumped at destroy
         if (dmalloc((void**)&p.prof, 16384 * 8)) return -1;
         B200_CUDA(cudaMemset(p.prof, 0, 16384 * 8));

@@ -59,6 +59,17 @@ __device__ __forceinline__ void mma_s8_m16n8k32(int (&c)[4], uint32_t a0, uint32
         : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3])
         : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
+// L2 prefetch of [ptr, ptr + bytes) by the consumer threads, one 128-byte line each. Issued BEFORE a grid
+// barrier for data the next phase reads first and that the weight stream has evicted since the last step
+// (norm weights, the K/V rows of earlier positions, the RoPE row): the miss overlaps the barrier wait.
+// Called from inside the grid barrier by warps 1..15 (warp 0 arrives and polls: a prefetch in flight ahead of
+// its red.release would hold the release back by the very miss it is meant to hide -- measured, +0.9 us).
+__device__ __forceinline__ void prefetch_l2_lines(const void* ptr, size_t bytes) {
+    const char* c = reinterpret_cast<const char*>(ptr);
+    if (threadIdx.x < 32) return;
+    for (size_t o = (size_t)(threadIdx.x - 32) * 128; o < bytes; o += (size_t)(MEGA_CONS - 32) * 128)
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(c + o));
+}
 // q = clamp(round_half_away(v * inv), -127, 127); NaN -> 0 (Rust `as i8`). Round-half-away as
 // trunc(y + copysign(0.5 - 2^-25, y)): identical to roundf(y) for every float |y| <= 200 (checked
 // exhaustively on the CPU, tests: test_round_half_away_trick), 4 instructions
@@ -94,9 +105,14 @@ __device__ __forceinline__ void mbar_wait_backoff(void* bar, uint32_t parity) {
 // counter, which is what a single-counter barrier measured); eight lanes of warp 0 poll one counter
 // each with ld.acquire and the warp sums them. Bounded spin: a lost arrival traps instead of hanging.
 constexpr int MEGA_BAR_CTRS = 8, MEGA_BAR_STRIDE = 64;  // counters per parity, stride in 32-bit words
-__device__ __forceinline__ void grid_sync(unsigned* ctr, unsigned& target, unsigned ncta) {
+struct NoPrefetch {
+    __device__ __forceinline__ void operator()() const {}
+};
+template <typename PF = NoPrefetch>
+__device__ __forceinline__ void grid_sync(unsigned* ctr, unsigned& target, unsigned ncta, PF pf = PF()) {
     target += ncta;
     cons_sync();
+    pf();  // warps 1..15: L2 prefetches for the next phase, overlapping the wait
     if (threadIdx.x < 32) {
         const unsigned lane = threadIdx.x;
         if (lane == 0)
@@ -149,6 +165,15 @@ __device__ __forceinline__ void mega_prologue_rows(const MegaParams& p, const Me
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     int8_t* qbuf = reinterpret_cast<int8_t*>(sm.act);
     const int ngrp = K >> 2;
+    float4 gm[NV];  // norm weights: fetched with the first row, not after the sum-of-squares barrier
+    if (pro == 2) {
+#pragma unroll
+        for (int j = 0; j < NV; ++j) {
+            const int g = tid + j * MEGA_CONS;
+            gm[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (g < ngrp) gm[j] = __ldg(reinterpret_cast<const float4*>(gamma) + g);
+        }
+    }
     for (int m = 0; m < p.B; ++m) {
         float4 v[NV];
 #pragma unroll
@@ -176,11 +201,10 @@ __device__ __forceinline__ void mega_prologue_rows(const MegaParams& p, const Me
             for (int j = 0; j < NV; ++j) {
                 const int g = tid + j * MEGA_CONS;
                 if (g < ngrp) {
-                    const float4 gm = __ldg(reinterpret_cast<const float4*>(gamma) + g);
-                    v[j].x = v[j].x * inv_rms * gm.x;
-                    v[j].y = v[j].y * inv_rms * gm.y;
-                    v[j].z = v[j].z * inv_rms * gm.z;
-                    v[j].w = v[j].w * inv_rms * gm.w;
+                    v[j].x = v[j].x * inv_rms * gm[j].x;
+                    v[j].y = v[j].y * inv_rms * gm[j].y;
+                    v[j].z = v[j].z * inv_rms * gm[j].z;
+                    v[j].w = v[j].w * inv_rms * gm[j].w;
                 }
             }
         }
@@ -779,7 +803,7 @@ __global__ void __launch_bounds__(MEGA_THREADS, 1) decode_mega_kernel(const __gr
             const int b = i / H, k = i - b * H;
             p.x[i] = __half2float(p.emb[(size_t)ld_cg_s32(p.tokens + b) * H + k]);
         }
-        grid_sync(ctr, target, G);
+        grid_sync(ctr, target, G, [&]() { prefetch_l2_lines(sm.layers[0].attn_norm, (size_t)H * 4); });
     }
     // ONE call site per phase kind (the bodies are inlined once): op 0 qkv, 1 attention, 2 o, 3 gate/up, 4 down
     for (int l = 0; l < p.L; ++l) {
@@ -803,7 +827,27 @@ __global__ void __launch_bounds__(MEGA_THREADS, 1) decode_mega_kernel(const __gr
             const int epi = op == 3 ? 2 : ((full && (op == 2 || op == 4)) ? 1 : 0);
             float* out = op == 0 ? p.qkv : (op == 3 ? p.gu : p.x);
             mega_gemv_phase(p, sm, N, K, pro, xin, gamma, epi, out, p.x, rp, tcount, pi);
-            if (full) grid_sync(ctr, target, G);
+            if (full) grid_sync(ctr, target, G, [&]() {
+                // what the next phase touches first and the weight stream has pushed out of L2 since the last step
+                if (!p.prefetch) return;
+                if (op == 0) {
+                    const int group = NH / NKV;
+                    for (int task = cta; task < NH * B; task += G) {
+                        const size_t kv = (size_t)l * B * NKV * p.max_ctx * D +
+                                          ((size_t)(task / NH) * NKV + (task % NH) / group) * p.max_ctx * D;
+                        prefetch_l2_lines(p.kc + kv, (size_t)pos * D * 4);
+                        prefetch_l2_lines(p.vc + kv, (size_t)pos * D * 4);
+                    }
+                    if (cta < NH * B && l == 0) {
+                        prefetch_l2_lines(p.rope_cos + (size_t)pos * (D / 2), (size_t)D * 2);
+                        prefetch_l2_lines(p.rope_sin + (size_t)pos * (D / 2), (size_t)D * 2);
+                    }
+                } else if (op == 2) {
+                    prefetch_l2_lines(L.ffn_norm, (size_t)H * 4);
+                } else if (op == 4) {
+                    prefetch_l2_lines(l + 1 < p.L ? sm.layers[l + 1].attn_norm : p.final_norm, (size_t)H * 4);
+                }
+            });
         }
     }
     if (!full) return;

@@ -25,6 +25,7 @@ struct MegaParams {
     int L, B, H, F, NH, NKV, D, V, max_ctx;
     float eps;
     uint32_t lut;
+    int prefetch;            // 1 = L2 prefetches inside the grid barriers (diagnostics knob BITNET_B200_MEGA_NOPF)
     int mode;                // 0 = full decode step; 1 = the 4L ternary GEMVs only, no dependencies
     int n_slots, act_bytes, attn_floats;
     unsigned long long* prof;  // optional [16384] globaltimer stamps of CTA 0 (diagnostics), or nullptr
