@@ -258,6 +258,9 @@ struct bitnet_b200_model {
     MegaLayer* mega_layers = nullptr;  // device table
     unsigned* mega_bar = nullptr;      // [2][8] grid-barrier counters, one per 256-byte line
     int mega_parity = 0;
+    uint2* mega_ll = nullptr;          // (value, epoch) pair buffers of the phase outputs: x | qkv | att | gu
+    size_t mega_ll_pairs = 0;
+    uint32_t mega_epoch = 1;           // 0 is what freshly cleared pair buffers hold: never a valid epoch
     size_t mega_smem = 0;
     MegaParams mega_p{};
     int8_t* q8 = nullptr;
@@ -502,7 +505,17 @@ static int mega_setup(bitnet_b200_model* m) {
     p.layers = m->mega_layers;
     p.emb = m->emb; p.final_norm = m->final_norm; p.rope_cos = m->rope_cos; p.rope_sin = m->rope_sin;
     p.kc = m->kc; p.vc = m->vc; p.pos = m->pos; p.tokens = m->tokens; p.next = m->next;
-    p.x = m->x; p.qkv = m->qkv; p.att = m->att; p.gu = m->gu; p.logits = m->logits;
+    {
+        const size_t B = (size_t)c.batch, nx = B * c.hidden, nqkv = B * (c.n_heads + 2 * c.n_kv_heads) * c.head_dim,
+                     natt = B * c.n_heads * c.head_dim, ngu = B * c.ffn;
+        m->mega_ll_pairs = nx + nqkv + natt + ngu;
+        if (dmalloc((void**)&m->mega_ll, m->mega_ll_pairs * sizeof(uint2))) return -1;
+        B200_CUDA(cudaMemsetAsync(m->mega_ll, 0, m->mega_ll_pairs * sizeof(uint2), st));
+        B200_CUDA(cudaStreamSynchronize(st));
+        p.x = m->mega_ll; p.qkv = p.x + nx; p.att = p.qkv + nqkv; p.gu = p.att + natt;
+    }
+    p.logits = m->logits;
+    p.barriers = getenv("BITNET_B200_MEGA_BARRIERS") ? 1 : 0;
     p.part_val = m->part_val; p.part_idx = m->part_idx;
     p.q_fixed = m->q8; p.s_fixed = m->s8; p.bar = m->mega_bar;
     p.lut = m->layers[0].wqkv->lut_word;
@@ -522,6 +535,13 @@ static int mega_launch(bitnet_b200_model* m, int mode) {
     p.mode = mode;
     p.parity = m->mega_parity;
     m->mega_parity ^= 1;
+    const uint32_t span = 5u * (uint32_t)p.L + 1u;  // epochs one launch hands out
+    if (m->mega_epoch > 0xffffffffu - 2u * span) {   // wrap (after ~28 M steps): start over on cleared flags
+        B200_CUDA(cudaMemsetAsync(m->mega_ll, 0, m->mega_ll_pairs * sizeof(uint2), m->ctx->stream));
+        m->mega_epoch = 1;
+    }
+    p.epoch = m->mega_epoch;
+    m->mega_epoch += span;
     return launch_decode_mega(p, m->mega_smem, m->ctx->num_sms, m->ctx->stream);
 }
 
@@ -632,6 +652,7 @@ void bitnet_b200_model_destroy(bitnet_b200_model* m) {
     }
     if (m->mega_layers) cudaFree(m->mega_layers);
     if (m->mega_bar) cudaFree(m->mega_bar);
+    if (m->mega_ll) cudaFree(m->mega_ll);
     for (auto& L : m->layers) {
         bitnet_b200_weight_destroy(L.wqkv);
         bitnet_b200_weight_destroy(L.wo);

@@ -34,6 +34,7 @@ constexpr int MEGA_MAX_TILES = 16;                  // 16-row tiles per CTA per 
 constexpr int MEGA_MAXB = 4;                        // tokens per step
 constexpr int MEGA_MAX_SLOTS = 12;
 constexpr int MEGA_MAX_LAYERS = 64;
+static_assert(MEGA_MAX_TILES * 16 <= MEGA_CONS, "epilogue: one output row per consumer thread");
 
 // ---- small PTX helpers ------------------------------------------------------------------------
 __device__ __forceinline__ void cons_sync() { asm volatile("bar.sync 1, %0;" ::"n"(MEGA_CONS) : "memory"); }
@@ -59,6 +60,47 @@ __device__ __forceinline__ void mma_s8_m16n8k32(int (&c)[4], uint32_t a0, uint32
         : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3])
         : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
+// ---- flagged dataflow between phases -------------------------------------------------------------
+// Every value a phase hands to the next one travels as an 8-byte (f32 bits, epoch) pair written with ONE
+// store: an aligned 8-byte store is single-copy atomic, so a reader that sees the expected epoch in the flag
+// word has the value too -- no fence, no separate barrier. A consumer simply polls the pairs it needs (it
+// reads the whole vector in its activation prologue anyway), which replaces "grid barrier (~2 us), then an
+// L2 round trip for the activations" by a single wait of about one L2 round trip after the last producer's
+// store. Epochs grow monotonically across phases and launches, so a stale pair can never match.
+// Write-after-read safety without barriers: a CTA can only produce out(n+1) after it has seen ALL of out(n),
+// i.e. after every CTA finished phase n including its reads of out(n-1); adjacent phase outputs live in
+// different buffers (qkv, att, x, gu, x, ...), so nothing still being read is overwritten.
+__device__ __forceinline__ void ll_store(uint2* buf, size_t i, float v, uint32_t ep) {
+    asm volatile("st.relaxed.gpu.global.v2.u32 [%0], {%1, %2};" ::"l"(buf + i), "r"(__float_as_uint(v)), "r"(ep) : "memory");
+}
+__device__ __forceinline__ uint4 ll_ld2(const uint2* p) {  // two pairs
+    uint4 v;
+    asm volatile("ld.relaxed.gpu.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint2 ll_ld1(const uint2* p) {
+    uint2 v;
+    asm volatile("ld.relaxed.gpu.global.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ float ll_wait1(const uint2* p, uint32_t ep) {
+    uint2 v = ll_ld1(p);
+    for (uint32_t it = 0; v.y != ep; ++it) {
+        if (it > (1u << 24)) __trap();  // a lost producer: fail loudly instead of hanging
+        v = ll_ld1(p);
+    }
+    return __uint_as_float(v.x);
+}
+// four consecutive values (pairs 4g .. 4g+3): `a`, `b` hold a first probe issued by the caller
+__device__ __forceinline__ float4 ll_wait4(const uint2* p, uint4 a, uint4 b, uint32_t ep) {
+    for (uint32_t it = 0; a.y != ep || a.w != ep || b.y != ep || b.w != ep; ++it) {
+        if (it > (1u << 24)) __trap();
+        a = ll_ld2(p);
+        b = ll_ld2(p + 2);
+    }
+    return make_float4(__uint_as_float(a.x), __uint_as_float(a.z), __uint_as_float(b.x), __uint_as_float(b.z));
+}
+
 // L2 prefetch of [ptr, ptr + bytes) by the consumer threads, one 128-byte line each. Issued BEFORE a grid
 // barrier for data the next phase reads first and that the weight stream has evicted since the last step
 // (norm weights, the K/V rows of earlier positions, the RoPE row): the miss overlaps the barrier wait.
@@ -160,8 +202,8 @@ struct MegaSmem {
 // pro: 0 = copy the fixed int8 rows (mode 1), 1 = absmax int8 quantise, 2 = RMSNorm then quantise.
 // NV = float4 groups per thread (K <= 16 * NV * MEGA_CONS... i.e. 2 -> K <= 4096, 4 -> K <= 8192).
 template <int NV>
-__device__ __forceinline__ void mega_prologue_rows(const MegaParams& p, const MegaSmem& sm, int pro, const float* xin,
-                                                   const float* gamma, int K, int q_ld) {
+__device__ __forceinline__ void mega_prologue_rows(const MegaParams& p, const MegaSmem& sm, int pro, const uint2* xin,
+                                                   uint32_t ep_in, const float* gamma, int K, int q_ld) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     int8_t* qbuf = reinterpret_cast<int8_t*>(sm.act);
     const int ngrp = K >> 2;
@@ -176,11 +218,20 @@ __device__ __forceinline__ void mega_prologue_rows(const MegaParams& p, const Me
     }
     for (int m = 0; m < p.B; ++m) {
         float4 v[NV];
+        uint4 pa[NV], pb[NV];  // first probe of every group in flight before any flag is looked at
+#pragma unroll
+        for (int j = 0; j < NV; ++j) {
+            const int g = tid + j * MEGA_CONS;
+            if (g < ngrp) {
+                pa[j] = ll_ld2(xin + (size_t)m * K + 4 * g);
+                pb[j] = ll_ld2(xin + (size_t)m * K + 4 * g + 2);
+            }
+        }
 #pragma unroll
         for (int j = 0; j < NV; ++j) {
             const int g = tid + j * MEGA_CONS;
             v[j] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (g < ngrp) v[j] = ld_cg_f32x4(xin + (size_t)m * K + 4 * g);
+            if (g < ngrp) v[j] = ll_wait4(xin + (size_t)m * K + 4 * g, pa[j], pb[j], ep_in);
         }
         if (pro == 2) {
             double ss = 0.0;
@@ -237,8 +288,8 @@ __device__ __forceinline__ void mega_prologue_rows(const MegaParams& p, const Me
     }
 }
 
-__device__ __forceinline__ void mega_prologue(const MegaParams& p, const MegaSmem& sm, int pro, const float* xin,
-                                           const float* gamma, int K, int q_ld) {
+__device__ __forceinline__ void mega_prologue(const MegaParams& p, const MegaSmem& sm, int pro, const uint2* xin,
+                                           uint32_t ep_in, const float* gamma, int K, int q_ld) {
     const int tid = threadIdx.x;
     if (pro == 0) {
         int8_t* qbuf = reinterpret_cast<int8_t*>(sm.act);
@@ -251,8 +302,8 @@ __device__ __forceinline__ void mega_prologue(const MegaParams& p, const MegaSme
         cons_sync();
         return;
     }
-    if (K <= 8 * MEGA_CONS) mega_prologue_rows<2>(p, sm, pro, xin, gamma, K, q_ld);
-    else mega_prologue_rows<4>(p, sm, pro, xin, gamma, K, q_ld);  // K <= 8192 (mega_plan)
+    if (K <= 8 * MEGA_CONS) mega_prologue_rows<2>(p, sm, pro, xin, ep_in, gamma, K, q_ld);
+    else mega_prologue_rows<4>(p, sm, pro, xin, ep_in, gamma, K, q_ld);  // K <= 8192 (mega_plan)
 }
 
 // ---- one ternary GEMV phase (consumer side) ------------------------------------------------------
@@ -295,8 +346,8 @@ __device__ __forceinline__ void mega_task(const unsigned char* wr, int rowb, con
 
 // epi: 0 store, 1 residual add (out may alias resid), 2 SwiGLU on interleaved (gate, up) rows
 __device__ __forceinline__ void mega_gemv_phase(const MegaParams& p, const MegaSmem& sm, int N, int K, int pro,
-                                             const float* xin, const float* gamma, int epi, float* out,
-                                             const float* resid, RingPos& rp, int& tcount, int& pi) {
+                                             const uint2* xin, const float* gamma, int epi, uint2* out,
+                                             const uint2* resid, uint32_t ep_out, RingPos& rp, int& tcount, int& pi) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, t = lane & 3;
     prof_stamp(p, pi);  // phase start
@@ -310,8 +361,19 @@ __device__ __forceinline__ void mega_gemv_phase(const MegaParams& p, const MegaS
     for (int tt = first; tt < NT; tt += G) ++nloc;
     const uint32_t NS = (uint32_t)p.n_slots;
     for (int i = tid; i < nloc * 128; i += MEGA_CONS) sm.acc[i] = 0;
-    mega_prologue(p, sm, pro, xin, gamma, K, q_ld);  // ends with a consumer barrier
+    mega_prologue(p, sm, pro, xin, ep_out - 1u, gamma, K, q_ld);  // waits for the previous phase's output; ends with a consumer barrier
     prof_stamp(p, pi);  // prologue done
+    // residual rows of this CTA: fetched now, consumed in the epilogue (nloc * 16 <= MEGA_CONS: one row per thread).
+    // The old x[row] was validated by this CTA in an earlier prologue and has no writer before this phase's epilogue.
+    float rv[MEGA_MAXB];
+    if (epi == 1) {
+        const int row = (first + (tid >> 4) * G) * 16 + (tid & 15);
+#pragma unroll
+        for (int m = 0; m < MEGA_MAXB; ++m) {
+            rv[m] = 0.f;
+            if (m < p.B && tid < nloc * 16 && row < N) rv[m] = ld_cg_f32(reinterpret_cast<const float*>(resid + (size_t)m * N + row));
+        }
+    }
 
     // tasks (local tile i, step s) are dealt round-robin to the 16 warps: q = i * ns + s = warp, warp + 16, ...
     const bool tok = g < p.B;
@@ -380,18 +442,21 @@ __device__ __forceinline__ void mega_gemv_phase(const MegaParams& p, const MegaS
                 const float as = sm.sc_s[m];
                 const float v0 = __fmul_rn(as, (float)sm.acc[ii * 128 + (2 * j) * 8 + m]);
                 const float v1 = __fmul_rn(as, (float)sm.acc[ii * 128 + (2 * j + 1) * 8 + m]);
-                out[(size_t)m * half + (row >> 1)] = __fmul_rn(v0 / (1.0f + expf(-v0)), v1);
+                ll_store(out, (size_t)m * half + (row >> 1), __fmul_rn(v0 / (1.0f + expf(-v0)), v1), ep_out);
             }
         }
     } else {
-        for (int m = 0; m < p.B; ++m)
-        for (int rr = tid; rr < nloc * 16; rr += MEGA_CONS) {
-            const int ii = rr >> 4, rw = rr & 15;
-            const int row = (first + ii * G) * 16 + rw;
-            if (row < N) {
-                const float v = __fmul_rn(sm.sc_s[m], (float)sm.acc[ii * 128 + rw * 8 + m]);
-                const size_t oi = (size_t)m * N + row;
-                out[oi] = epi == 1 ? __fadd_rn(ld_cg_f32(resid + oi), v) : v;
+#pragma unroll
+        for (int m = 0; m < MEGA_MAXB; ++m) {
+            if (m >= p.B) break;
+            const int rr = tid;  // nloc <= MEGA_MAX_TILES = 16 tiles -> at most 256 rows per CTA
+            if (rr < nloc * 16) {
+                const int ii = rr >> 4, rw = rr & 15;
+                const int row = (first + ii * G) * 16 + rw;
+                if (row < N) {
+                    const float v = __fmul_rn(sm.sc_s[m], (float)sm.acc[ii * 128 + rw * 8 + m]);
+                    ll_store(out, (size_t)m * N + row, epi == 1 ? __fadd_rn(rv[m], v) : v, ep_out);
+                }
             }
         }
     }
@@ -405,7 +470,7 @@ __device__ __forceinline__ void mega_gemv_phase(const MegaParams& p, const MegaS
 // (crates/bitnet-transformer/src/lib.rs:134-184, 374-540, 1171-1202; same arithmetic as
 // attn_fused_kernel in decode_fused.cuh)
 __device__ __forceinline__ void mega_attention(const MegaParams& p, const MegaSmem& sm, int head, int b, int pos,
-                                               float* kc, float* vc) {
+                                               float* kc, float* vc, uint32_t ep_out) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int D = p.D, NH = p.NH, NKV = p.NKV, half = D / 2, max_ctx = p.max_ctx;
     float* sc = sm.attn;
@@ -414,22 +479,29 @@ __device__ __forceinline__ void mega_attention(const MegaParams& p, const MegaSm
     float* ks = qs + 256;
     float* vs = ks + 256;
     const int group = NH / NKV, g = head / group;
-    const float* row = p.qkv + (size_t)b * (NH + 2 * NKV) * D;
+    const uint2* row = p.qkv + (size_t)b * (NH + 2 * NKV) * D;
+    const uint32_t ep_in = ep_out - 1u;
     float* kb = kc + ((size_t)b * NKV + g) * max_ctx * D;
     float* vb = vc + ((size_t)b * NKV + g) * max_ctx * D;
     if (tid < half) {
         const float c = __ldg(p.rope_cos + (size_t)pos * half + tid), s = __ldg(p.rope_sin + (size_t)pos * half + tid);
-        const float* qh = row + (size_t)head * D;
-        const float* kh = row + (size_t)(NH + g) * D;
-        const float* vh = row + (size_t)(NH + NKV + g) * D;
-        const float qa = ld_cg_f32(qh + tid), qb = ld_cg_f32(qh + tid + half);
-        const float ka = ld_cg_f32(kh + tid), kbv = ld_cg_f32(kh + tid + half);
+        const uint2* qh = row + (size_t)head * D;
+        const uint2* kh = row + (size_t)(NH + g) * D;
+        const uint2* vh = row + (size_t)(NH + NKV + g) * D;
+        // six probes in flight, then wait for the qkv phase's epoch on each
+        const uint2 p0 = ll_ld1(qh + tid), p1 = ll_ld1(qh + tid + half), p2 = ll_ld1(kh + tid), p3 = ll_ld1(kh + tid + half);
+        const uint2 p4 = ll_ld1(vh + tid), p5 = ll_ld1(vh + tid + half);
+        const float qa = p0.y == ep_in ? __uint_as_float(p0.x) : ll_wait1(qh + tid, ep_in);
+        const float qb = p1.y == ep_in ? __uint_as_float(p1.x) : ll_wait1(qh + tid + half, ep_in);
+        const float ka = p2.y == ep_in ? __uint_as_float(p2.x) : ll_wait1(kh + tid, ep_in);
+        const float kbv = p3.y == ep_in ? __uint_as_float(p3.x) : ll_wait1(kh + tid + half, ep_in);
         qs[tid] = qa * c - qb * s;
         qs[tid + half] = qa * s + qb * c;
         const float k0 = ka * c - kbv * s, k1 = ka * s + kbv * c;
         ks[tid] = k0;
         ks[tid + half] = k1;
-        const float v0 = ld_cg_f32(vh + tid), v1 = ld_cg_f32(vh + tid + half);
+        const float v0 = p4.y == ep_in ? __uint_as_float(p4.x) : ll_wait1(vh + tid, ep_in);
+        const float v1 = p5.y == ep_in ? __uint_as_float(p5.x) : ll_wait1(vh + tid + half, ep_in);
         vs[tid] = v0;
         vs[tid + half] = v1;
         if (head % group == 0) {
@@ -534,7 +606,11 @@ __device__ __forceinline__ void mega_attention(const MegaParams& p, const MegaSm
         tt.y = fmaf(wl, vl.y, tt.y);
         tt.z = fmaf(wl, vl.z, tt.z);
         tt.w = fmaf(wl, vl.w, tt.w);
-        reinterpret_cast<float4*>(p.att + ((size_t)b * NH + head) * D)[tid] = tt;
+        uint2* ao = p.att + ((size_t)b * NH + head) * D + 4 * tid;
+        ll_store(ao, 0, tt.x, ep_out);
+        ll_store(ao, 1, tt.y, ep_out);
+        ll_store(ao, 2, tt.z, ep_out);
+        ll_store(ao, 3, tt.w, ep_out);
     }
     cons_sync();  // the attention scratch may be reused by the next (head, sequence) of this CTA
 }
@@ -630,7 +706,7 @@ __device__ __forceinline__ void mega_logits_rows(const MegaParams& p, const Mega
 }
 
 // ---- LM head: final RMSNorm, tied-embedding logits (f16 table through the ring), argmax partials
-__device__ __forceinline__ void mega_logits_phase(const MegaParams& p, const MegaSmem& sm, RingPos& rp) {
+__device__ __forceinline__ void mega_logits_phase(const MegaParams& p, const MegaSmem& sm, RingPos& rp, uint32_t ep_in) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int H = p.H, V = p.V, G = gridDim.x, cta = blockIdx.x;
     float* xn = reinterpret_cast<float*>(sm.act);  // [B][H]
@@ -638,7 +714,7 @@ __device__ __forceinline__ void mega_logits_phase(const MegaParams& p, const Meg
     for (int m = 0; m < p.B; ++m) {
         double ss = 0.0;
         for (int k = tid; k < H; k += MEGA_CONS) {
-            const float v = ld_cg_f32(p.x + (size_t)m * H + k);
+            const float v = ll_wait1(p.x + (size_t)m * H + k, ep_in);
             xn[m * H + k] = v;
             ss += (double)v * (double)v;
         }
@@ -801,36 +877,39 @@ __global__ void __launch_bounds__(MEGA_THREADS, 1) decode_mega_kernel(const __gr
         // embed: x[b] = f32(emb[token[b]]), spread over the grid
         for (int i = cta * MEGA_CONS + tid; i < B * H; i += G * MEGA_CONS) {
             const int b = i / H, k = i - b * H;
-            p.x[i] = __half2float(p.emb[(size_t)ld_cg_s32(p.tokens + b) * H + k]);
+            ll_store(p.x, i, __half2float(p.emb[(size_t)ld_cg_s32(p.tokens + b) * H + k]), p.epoch);
         }
-        grid_sync(ctr, target, G, [&]() { prefetch_l2_lines(sm.layers[0].attn_norm, (size_t)H * 4); });
+        if (p.prefetch) prefetch_l2_lines(sm.layers[0].attn_norm, (size_t)H * 4);
+        if (p.barriers) grid_sync(ctr, target, G);
     }
     // ONE call site per phase kind (the bodies are inlined once): op 0 qkv, 1 attention, 2 o, 3 gate/up, 4 down
     for (int l = 0; l < p.L; ++l) {
         const MegaLayer& L = sm.layers[l];
         for (int op = 0; op < 5; ++op) {
+            const uint32_t ep = p.epoch + 1u + (uint32_t)(5 * l + op);  // epoch of this phase's output; its input carries ep - 1
             if (op == 1) {
                 if (!full) continue;
                 const size_t kvoff = (size_t)l * B * NKV * p.max_ctx * D;
                 prof_stamp(p, pi);  // attention start
                 for (int task = cta; task < NH * B; task += G)
-                    mega_attention(p, sm, task % NH, task / NH, pos, p.kc + kvoff, p.vc + kvoff);
+                    mega_attention(p, sm, task % NH, task / NH, pos, p.kc + kvoff, p.vc + kvoff, ep);
                 prof_stamp(p, pi);  // attention done
-                grid_sync(ctr, target, G);
+                if (p.barriers) grid_sync(ctr, target, G);
                 continue;
             }
             const int N = op == 0 ? QKV : (op == 3 ? 2 * F : H);
             const int K = op == 2 ? QD : (op == 4 ? F : H);
             const int pro = !full ? 0 : ((op == 0 || op == 3) ? 2 : 1);
-            const float* xin = op == 2 ? p.att : (op == 4 ? p.gu : p.x);
+            const uint2* xin = op == 2 ? p.att : (op == 4 ? p.gu : p.x);
             const float* gamma = op == 0 ? L.attn_norm : L.ffn_norm;
             const int epi = op == 3 ? 2 : ((full && (op == 2 || op == 4)) ? 1 : 0);
-            float* out = op == 0 ? p.qkv : (op == 3 ? p.gu : p.x);
-            mega_gemv_phase(p, sm, N, K, pro, xin, gamma, epi, out, p.x, rp, tcount, pi);
-            if (full) grid_sync(ctr, target, G, [&]() {
-                // what the next phase touches first and the weight stream has pushed out of L2 since the last step
-                if (!p.prefetch) return;
-                if (op == 0) {
+            uint2* out = op == 0 ? p.qkv : (op == 3 ? p.gu : p.x);
+            mega_gemv_phase(p, sm, N, K, pro, xin, gamma, epi, out, p.x, ep, rp, tcount, pi);
+            if (full) {
+                // what the next phase touches first and the weight stream has pushed out of L2 since the last step:
+                // the miss overlaps the wait for the other CTAs' outputs
+                if (!p.prefetch) {
+                } else if (op == 0) {
                     const int group = NH / NKV;
                     for (int task = cta; task < NH * B; task += G) {
                         const size_t kv = (size_t)l * B * NKV * p.max_ctx * D +
@@ -847,12 +926,13 @@ __global__ void __launch_bounds__(MEGA_THREADS, 1) decode_mega_kernel(const __gr
                 } else if (op == 4) {
                     prefetch_l2_lines(l + 1 < p.L ? sm.layers[l + 1].attn_norm : p.final_norm, (size_t)H * 4);
                 }
-            });
+                if (p.barriers) grid_sync(ctr, target, G);
+            }
         }
     }
     if (!full) return;
     prof_stamp(p, pi);
-    mega_logits_phase(p, sm, rp);
+    mega_logits_phase(p, sm, rp, p.epoch + (uint32_t)(5 * p.L));
     prof_stamp(p, pi);
     grid_sync(ctr, target, G);
     prof_stamp(p, pi);

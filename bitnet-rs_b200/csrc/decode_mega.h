@@ -16,7 +16,8 @@ struct MegaParams {
     const float *final_norm, *rope_cos, *rope_sin;
     float *kc, *vc;
     int *pos, *tokens, *next;
-    float *x, *qkv, *att, *gu, *logits, *part_val;
+    uint2 *x, *qkv, *att, *gu;  // phase outputs as (f32 bits, epoch) pairs: each 8-byte store carries its own ready flag
+    float *logits, *part_val;
     int* part_idx;
     const int8_t* q_fixed;   // mode 1: fixed int8 rows [B, max(H, F, NH*D)]
     const float* s_fixed;    // mode 1: their scales
@@ -25,6 +26,8 @@ struct MegaParams {
     int L, B, H, F, NH, NKV, D, V, max_ctx;
     float eps;
     uint32_t lut;
+    uint32_t epoch;          // epoch of this launch's first phase output (advances by 5L + 1 per launch)
+    int barriers;            // 1 = keep the grid barrier after every phase as well (diagnostics knob BITNET_B200_MEGA_BARRIERS)
     int prefetch;            // 1 = L2 prefetches inside the grid barriers (diagnostics knob BITNET_B200_MEGA_NOPF)
     int mode;                // 0 = full decode step; 1 = the 4L ternary GEMVs only, no dependencies
     int n_slots, act_bytes, attn_floats;
