@@ -6,7 +6,8 @@
 //     embed | per layer: [RMSNorm+act-quant | qkv GEMV] -> [RoPE + KV append + GQA attention]
 //     -> [act-quant | o GEMV + residual] -> [RMSNorm+act-quant | gate/up GEMV | SwiGLU]
 //     -> [act-quant | down GEMV + residual] | final RMSNorm + LM head + argmax
-// separated by grid-wide barriers (one global counter, red.release / ld.acquire).
+// chained by flagged (value, epoch) pairs: a phase polls exactly the outputs it consumes, there is no grid
+// barrier between phases (one per step, before the argmax).
 //
 // Why: at batch 1 a 2B-4T projection is 0.25-1.4 us of HBM time, below any launch or barrier
 // latency, so a chain of per-projection kernels is latency-bound with the memory pipe idle most
@@ -101,11 +102,12 @@ __device__ __forceinline__ float4 ll_wait4(const uint2* p, uint4 a, uint4 b, uin
     return make_float4(__uint_as_float(a.x), __uint_as_float(a.z), __uint_as_float(b.x), __uint_as_float(b.z));
 }
 
-// L2 prefetch of [ptr, ptr + bytes) by the consumer threads, one 128-byte line each. Issued BEFORE a grid
-// barrier for data the next phase reads first and that the weight stream has evicted since the last step
-// (norm weights, the K/V rows of earlier positions, the RoPE row): the miss overlaps the barrier wait.
-// Called from inside the grid barrier by warps 1..15 (warp 0 arrives and polls: a prefetch in flight ahead of
-// its red.release would hold the release back by the very miss it is meant to hide -- measured, +0.9 us).
+// L2 prefetch of [ptr, ptr + bytes) by the consumer threads, one 128-byte line each. Issued at the END of a
+// phase for data the next phase reads first and that the weight stream has evicted since the last step
+// (norm weights, the K/V rows of earlier positions, the RoPE row): the miss overlaps the wait for the other
+// CTAs' outputs.
+// Warps 1..15 only: with BITNET_B200_MEGA_BARRIERS=1 warp 0 arrives at the grid barrier next, and a prefetch in
+// flight ahead of its red.release holds the release back by the very miss it is meant to hide (measured, +0.9 us).
 __device__ __forceinline__ void prefetch_l2_lines(const void* ptr, size_t bytes) {
     const char* c = reinterpret_cast<const char*>(ptr);
     if (threadIdx.x < 32) return;
@@ -147,14 +149,9 @@ __device__ __forceinline__ void mbar_wait_backoff(void* bar, uint32_t parity) {
 // counter, which is what a single-counter barrier measured); eight lanes of warp 0 poll one counter
 // each with ld.acquire and the warp sums them. Bounded spin: a lost arrival traps instead of hanging.
 constexpr int MEGA_BAR_CTRS = 8, MEGA_BAR_STRIDE = 64;  // counters per parity, stride in 32-bit words
-struct NoPrefetch {
-    __device__ __forceinline__ void operator()() const {}
-};
-template <typename PF = NoPrefetch>
-__device__ __forceinline__ void grid_sync(unsigned* ctr, unsigned& target, unsigned ncta, PF pf = PF()) {
+__device__ __forceinline__ void grid_sync(unsigned* ctr, unsigned& target, unsigned ncta) {
     target += ncta;
     cons_sync();
-    pf();  // warps 1..15: L2 prefetches for the next phase, overlapping the wait
     if (threadIdx.x < 32) {
         const unsigned lane = threadIdx.x;
         if (lane == 0)
@@ -463,7 +460,7 @@ __device__ __forceinline__ void mega_gemv_phase(const MegaParams& p, const MegaS
     tcount += NT;
     while (tcount >= G) tcount -= G;
     prof_stamp(p, pi);  // epilogue done
-    if (p.mode == 1) cons_sync();  // no grid barrier follows: order the epilogue against the next phase's prologue
+    cons_sync();  // no grid barrier follows: the next phase zeroes sm.acc, which slower warps may still be reading here
 }
 
 // ---- RoPE + KV append + GQA decode attention for one (head, sequence); consumer threads only ---
