@@ -26,7 +26,7 @@
 
 namespace b200 {
 
-constexpr int MEGA_NW = 16;                         // consumer warps
+constexpr int MEGA_NW = 15;                         // consumer warps
 constexpr int MEGA_CONS = MEGA_NW * 32;             // consumer threads
 constexpr int MEGA_THREADS = MEGA_CONS + 32;        // + the producer warp
 constexpr int MEGA_SLOT_STEPS = 16;                 // 256-column steps per ring slot
@@ -510,9 +510,10 @@ __device__ __forceinline__ void mega_attention(const MegaParams& p, const MegaSm
     }
     cons_sync();
     const float scale = 1.0f / sqrtf((float)D);
-    float qr[8];
+    float qr[8];  // D <= 256; fixed trip counts keep q in registers and put every K load of a pass in flight at once
     const int per = D / 32;
-    for (int j = 0; j < per; ++j) qr[j] = qs[lane + 32 * j];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) qr[j] = j < per ? qs[lane + 32 * j] : 0.f;
     float mx = -INFINITY;
     for (int p0 = warp; p0 <= pos; p0 += 4 * MEGA_NW) {
         float d[4];
@@ -522,9 +523,16 @@ __device__ __forceinline__ void mega_attention(const MegaParams& p, const MegaSm
             d[u] = 0.f;
             if (pp < pos) {
                 const float* kp = kb + (size_t)pp * D;
-                for (int j = 0; j < per; ++j) d[u] = fmaf(qr[j], __ldg(kp + lane + 32 * j), d[u]);
+                float kv[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) kv[j] = j < per ? __ldg(kp + lane + 32 * j) : 0.f;
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    if (j < per) d[u] = fmaf(qr[j], kv[j], d[u]);
             } else if (pp == pos) {
-                for (int j = 0; j < per; ++j) d[u] = fmaf(qr[j], ks[lane + 32 * j], d[u]);
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    if (j < per) d[u] = fmaf(qr[j], ks[lane + 32 * j], d[u]);
             }
         }
 #pragma unroll
@@ -983,7 +991,7 @@ size_t mega_plan(MegaParams* p, int num_sms) {
     const int QD = p->NH * p->D;
     if (p->B < 1 || p->B > MEGA_MAXB || p->L > MEGA_MAX_LAYERS) return 0;
     if (p->H % 256 || p->F % 256 || QD % 256) return 0;          // whole 256-column steps, no tails
-    if (p->H > 8192 || p->F > 8192 || QD > 8192) return 0;       // one prologue pass per row
+    if (p->H > 16 * MEGA_CONS || p->F > 16 * MEGA_CONS || QD > 16 * MEGA_CONS) return 0;  // one prologue pass per row (NV = 4)
     if (p->D % 32 || p->D > 256 || MEGA_CONS % (p->D / 4)) return 0;
     if (p->H * 2 > MEGA_SLOT_BYTES) return 0;                    // one LM-head row per slot at least
     if (((p->NH + 2 * p->NKV) * p->D) % 2 || (2 * p->F) % 16) return 0;
