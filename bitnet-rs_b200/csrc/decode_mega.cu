@@ -515,10 +515,11 @@ __device__ __forceinline__ void mega_attention(const MegaParams& p, const MegaSm
 #pragma unroll
     for (int j = 0; j < 8; ++j) qr[j] = j < per ? qs[lane + 32 * j] : 0.f;
     float mx = -INFINITY;
-    for (int p0 = warp; p0 <= pos; p0 += 4 * MEGA_NW) {
-        float d[4];
+    constexpr int AU = 4;  // positions per warp (scores) / per thread group (values) in flight per pass
+    for (int p0 = warp; p0 <= pos; p0 += AU * MEGA_NW) {
+        float d[AU];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
+        for (int u = 0; u < AU; ++u) {
             const int pp = p0 + u * MEGA_NW;
             d[u] = 0.f;
             if (pp < pos) {
@@ -538,9 +539,9 @@ __device__ __forceinline__ void mega_attention(const MegaParams& p, const MegaSm
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1)
 #pragma unroll
-            for (int u = 0; u < 4; ++u) d[u] += __shfl_xor_sync(0xffffffffu, d[u], o);
+            for (int u = 0; u < AU; ++u) d[u] += __shfl_xor_sync(0xffffffffu, d[u], o);
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
+        for (int u = 0; u < AU; ++u) {
             const int pp = p0 + u * MEGA_NW;
             if (pp <= pos) {
                 const float v = d[u] * scale;
@@ -572,11 +573,11 @@ __device__ __forceinline__ void mega_attention(const MegaParams& p, const MegaSm
     const int dc = tid % ncol, pg = tid / ncol;
     float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
     if (pg < PG) {
-        for (int p0 = pg; p0 < pos; p0 += 4 * PG) {
-            float4 v[4];
-            float w[4];
+        for (int p0 = pg; p0 < pos; p0 += AU * PG) {
+            float4 v[AU];
+            float w[AU];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
+            for (int u = 0; u < AU; ++u) {
                 const int pp = p0 + u * PG;
                 v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
                 w[u] = 0.f;
@@ -586,7 +587,7 @@ __device__ __forceinline__ void mega_attention(const MegaParams& p, const MegaSm
                 }
             }
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
+            for (int u = 0; u < AU; ++u) {
                 a.x = fmaf(w[u], v[u].x, a.x);
                 a.y = fmaf(w[u], v[u].y, a.y);
                 a.z = fmaf(w[u], v[u].z, a.z);
