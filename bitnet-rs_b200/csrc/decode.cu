@@ -508,12 +508,14 @@ static int mega_setup(bitnet_b200_model* m) {
     {
         const size_t B = (size_t)c.batch, nx = B * c.hidden, nqkv = B * (c.n_heads + 2 * c.n_kv_heads) * c.head_dim,
                      natt = B * c.n_heads * c.head_dim, ngu = B * c.ffn;
-        m->mega_ll_pairs = nx + nqkv + natt + ngu;
+        const size_t nattp = B * c.n_heads * 8 * (size_t)(c.head_dim + 2);
+        m->mega_ll_pairs = nx + nqkv + natt + ngu + nattp;
         if (dmalloc((void**)&m->mega_ll, m->mega_ll_pairs * sizeof(uint2))) return -1;
         B200_CUDA(cudaMemsetAsync(m->mega_ll, 0, m->mega_ll_pairs * sizeof(uint2), st));
         B200_CUDA(cudaStreamSynchronize(st));
-        p.x = m->mega_ll; p.qkv = p.x + nx; p.att = p.qkv + nqkv; p.gu = p.att + natt;
+        p.x = m->mega_ll; p.qkv = p.x + nx; p.att = p.qkv + nqkv; p.gu = p.att + natt; p.attp = p.gu + ngu;
     }
+    p.att_split = getenv("BITNET_B200_MEGA_NOSPLIT") ? 0 : 1;
     p.logits = m->logits;
     p.barriers = getenv("BITNET_B200_MEGA_BARRIERS") ? 1 : 0;
     p.part_val = m->part_val; p.part_idx = m->part_idx;

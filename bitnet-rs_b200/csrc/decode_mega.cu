@@ -186,6 +186,7 @@ struct MegaSmem {
     double* shd;       // [32]
     float* shf;        // [32]
     float* sc_s;       // [MEGA_MAXB]
+    int* attw;         // [8] this CTA's attention work item: on, head, seq, split, lo, hi, kv offset (2 words)
     float* bestv;      // [MEGA_NW * MEGA_MAXB]
     int* besti;        // [MEGA_NW * MEGA_MAXB]
     MegaLayer* layers; // [L]
@@ -466,8 +467,32 @@ __device__ __forceinline__ void mega_gemv_phase(const MegaParams& p, const MegaS
 // ---- RoPE + KV append + GQA decode attention for one (head, sequence); consumer threads only ---
 // (crates/bitnet-transformer/src/lib.rs:134-184, 374-540, 1171-1202; same arithmetic as
 // attn_fused_kernel in decode_fused.cuh)
+// Long contexts are split over S CTAs per (head, sequence) -- 128 of the 148 CTAs would otherwise idle through
+// this phase while 20 walk the whole cache: split s owns positions [lo, hi) (the last split owns the current
+// token), produces an un-normalised partial (max, sum, sum of e * v) as flagged pairs, and split 0 merges the
+// S partials (one warp per partial polls it into shared memory, warp 0 combines) into the attention output.
+// S = 1 (short contexts) is exactly the single-CTA arithmetic.
+constexpr int ATT_SPLIT_MAX = 8;    // partial slots per (head, sequence)
+constexpr int ATT_SPLIT_FROM = 120; // contexts up to this many positions (two passes of 60) stay on one CTA: the merge hop costs about one pass
+constexpr int ATT_SPLIT_CHUNK = 60; // target positions per split beyond that (one pass of 4 x 15 warps)
+__device__ __forceinline__ int att_splits(const MegaParams& p, int pos, int G) {
+    const int ntask = p.NH * p.B;
+    int smax = G / ntask;
+    if (smax > ATT_SPLIT_MAX) smax = ATT_SPLIT_MAX;
+    if (smax > MEGA_NW) smax = MEGA_NW;
+    if (!p.att_split || p.D > 128 || smax < 2 || pos + 1 <= ATT_SPLIT_FROM) return 1;
+    const int want = (pos + 1 + ATT_SPLIT_CHUNK - 1) / ATT_SPLIT_CHUNK;
+    return want < smax ? want : smax;
+}
+__device__ __forceinline__ void att_range(int pos, int S, int split, int& lo, int& hi) {
+    const int chunk = (pos + 1 + S - 1) / S;
+    lo = split * chunk;
+    hi = lo + chunk < pos + 1 ? lo + chunk : pos + 1;
+    if (lo > hi) lo = hi;
+}
+
 __device__ __forceinline__ void mega_attention(const MegaParams& p, const MegaSmem& sm, int head, int b, int pos,
-                                               float* kc, float* vc, uint32_t ep_out) {
+                                               float* kc, float* vc, uint32_t ep_out, int split, int S, int lo, int hi) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int D = p.D, NH = p.NH, NKV = p.NKV, half = D / 2, max_ctx = p.max_ctx;
     float* sc = sm.attn;
@@ -480,6 +505,7 @@ __device__ __forceinline__ void mega_attention(const MegaParams& p, const MegaSm
     const uint32_t ep_in = ep_out - 1u;
     float* kb = kc + ((size_t)b * NKV + g) * max_ctx * D;
     float* vb = vc + ((size_t)b * NKV + g) * max_ctx * D;
+    const bool owner = hi == pos + 1;  // this split holds the current token
     if (tid < half) {
         const float c = __ldg(p.rope_cos + (size_t)pos * half + tid), s = __ldg(p.rope_sin + (size_t)pos * half + tid);
         const uint2* qh = row + (size_t)head * D;
@@ -501,7 +527,7 @@ __device__ __forceinline__ void mega_attention(const MegaParams& p, const MegaSm
         const float v1 = p5.y == ep_in ? __uint_as_float(p5.x) : ll_wait1(vh + tid + half, ep_in);
         vs[tid] = v0;
         vs[tid + half] = v1;
-        if (head % group == 0) {
+        if (head % group == 0 && owner) {
             kb[(size_t)pos * D + tid] = k0;
             kb[(size_t)pos * D + tid + half] = k1;
             vb[(size_t)pos * D + tid] = v0;
@@ -516,13 +542,13 @@ __device__ __forceinline__ void mega_attention(const MegaParams& p, const MegaSm
     for (int j = 0; j < 8; ++j) qr[j] = j < per ? qs[lane + 32 * j] : 0.f;
     float mx = -INFINITY;
     constexpr int AU = 4;  // positions per warp (scores) / per thread group (values) in flight per pass
-    for (int p0 = warp; p0 <= pos; p0 += AU * MEGA_NW) {
+    for (int p0 = lo + warp; p0 < hi; p0 += AU * MEGA_NW) {
         float d[AU];
 #pragma unroll
         for (int u = 0; u < AU; ++u) {
             const int pp = p0 + u * MEGA_NW;
             d[u] = 0.f;
-            if (pp < pos) {
+            if (pp < hi && pp < pos) {
                 const float* kp = kb + (size_t)pp * D;
                 float kv[8];
 #pragma unroll
@@ -543,7 +569,7 @@ __device__ __forceinline__ void mega_attention(const MegaParams& p, const MegaSm
 #pragma unroll
         for (int u = 0; u < AU; ++u) {
             const int pp = p0 + u * MEGA_NW;
-            if (pp <= pos) {
+            if (pp < hi) {
                 const float v = d[u] * scale;
                 if (lane == 0) sc[pp] = v;
                 mx = fmaxf(mx, v);
@@ -557,7 +583,7 @@ __device__ __forceinline__ void mega_attention(const MegaParams& p, const MegaSm
     for (int w = 1; w < MEGA_NW; ++w) mx = fmaxf(mx, sm.shf[w]);
     cons_sync();
     float sum = 0.f;
-    for (int pp = tid; pp <= pos; pp += MEGA_CONS) {
+    for (int pp = lo + tid; pp < hi; pp += MEGA_CONS) {
         const float e = expf(sc[pp] - mx);
         sc[pp] = e;
         sum += e;
@@ -568,12 +594,13 @@ __device__ __forceinline__ void mega_attention(const MegaParams& p, const MegaSm
     sum = 0.f;
 #pragma unroll
     for (int w = 0; w < MEGA_NW; ++w) sum += sm.shf[w];
-    const float inv = 1.0f / sum;
+    const float inv = S == 1 ? 1.0f / sum : 1.0f;  // partials stay un-normalised
     const int ncol = D / 4, PG = MEGA_CONS / ncol;
     const int dc = tid % ncol, pg = tid / ncol;
+    const int vhi = hi < pos ? hi : pos;  // cached rows of this split
     float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
     if (pg < PG) {
-        for (int p0 = pg; p0 < pos; p0 += AU * PG) {
+        for (int p0 = lo + pg; p0 < vhi; p0 += AU * PG) {
             float4 v[AU];
             float w[AU];
 #pragma unroll
@@ -581,7 +608,7 @@ __device__ __forceinline__ void mega_attention(const MegaParams& p, const MegaSm
                 const int pp = p0 + u * PG;
                 v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
                 w[u] = 0.f;
-                if (pp < pos) {
+                if (pp < vhi) {
                     v[u] = __ldg(reinterpret_cast<const float4*>(vb + (size_t)pp * D) + dc);
                     w[u] = sc[pp] * inv;
                 }
@@ -595,11 +622,11 @@ __device__ __forceinline__ void mega_attention(const MegaParams& p, const MegaSm
             }
         }
     }
-    const float wl = sc[pos] * inv;
+    const float wl = owner ? sc[pos] * inv : 0.f;
     if (pg < PG) part[pg * ncol + dc] = a;
     cons_sync();
+    float4 tt = make_float4(0.f, 0.f, 0.f, 0.f);
     if (tid < ncol) {
-        float4 tt = make_float4(0.f, 0.f, 0.f, 0.f);
         for (int i = 0; i < PG; ++i) {
             const float4 v = part[i * ncol + tid];
             tt.x += v.x;
@@ -607,18 +634,82 @@ __device__ __forceinline__ void mega_attention(const MegaParams& p, const MegaSm
             tt.z += v.z;
             tt.w += v.w;
         }
-        const float4 vl = reinterpret_cast<const float4*>(vs)[tid];
-        tt.x = fmaf(wl, vl.x, tt.x);
-        tt.y = fmaf(wl, vl.y, tt.y);
-        tt.z = fmaf(wl, vl.z, tt.z);
-        tt.w = fmaf(wl, vl.w, tt.w);
-        uint2* ao = p.att + ((size_t)b * NH + head) * D + 4 * tid;
-        ll_store(ao, 0, tt.x, ep_out);
-        ll_store(ao, 1, tt.y, ep_out);
-        ll_store(ao, 2, tt.z, ep_out);
-        ll_store(ao, 3, tt.w, ep_out);
+        if (owner) {
+            const float4 vl = reinterpret_cast<const float4*>(vs)[tid];
+            tt.x = fmaf(wl, vl.x, tt.x);
+            tt.y = fmaf(wl, vl.y, tt.y);
+            tt.z = fmaf(wl, vl.z, tt.z);
+            tt.w = fmaf(wl, vl.w, tt.w);
+        }
     }
-    cons_sync();  // the attention scratch may be reused by the next (head, sequence) of this CTA
+    uint2* ao = p.att + ((size_t)b * NH + head) * D + 4 * tid;
+    if (S == 1) {
+        if (tid < ncol) {
+            ll_store(ao, 0, tt.x, ep_out);
+            ll_store(ao, 1, tt.y, ep_out);
+            ll_store(ao, 2, tt.z, ep_out);
+            ll_store(ao, 3, tt.w, ep_out);
+        }
+        cons_sync();  // the attention scratch may be reused by the next (head, sequence) of this CTA
+        return;
+    }
+    // ---- split: publish the partial (split > 0) or merge all of them (split 0) --------------------
+    uint2* pbase = p.attp + (((size_t)b * NH + head) * ATT_SPLIT_MAX) * (size_t)(D + 2);
+    if (split != 0) {
+        uint2* po = pbase + (size_t)split * (D + 2);
+        if (tid < ncol) {
+            ll_store(po, 4 * tid + 0, tt.x, ep_out);
+            ll_store(po, 4 * tid + 1, tt.y, ep_out);
+            ll_store(po, 4 * tid + 2, tt.z, ep_out);
+            ll_store(po, 4 * tid + 3, tt.w, ep_out);
+        }
+        if (tid == 0) {
+            ll_store(po, D, mx, ep_out);
+            ll_store(po, D + 1, sum, ep_out);
+        }
+        cons_sync();
+        return;
+    }
+    cons_sync();  // part[] (value partials) consumed by warp 0 above: reuse it for the S split partials
+    if (warp == 0) {
+        if (lane < ncol) part[lane] = tt;
+        if (lane == 0) {
+            sm.shf[0] = mx;
+            sm.shf[16] = sum;
+        }
+    } else if (warp < S) {  // S <= MEGA_NW: one warp per foreign partial, all polls in flight together
+        const uint2* pi = pbase + (size_t)warp * (D + 2);
+        if (lane < ncol) {
+            const uint4 pa = ll_ld2(pi + 4 * lane), pb = ll_ld2(pi + 4 * lane + 2);
+            part[warp * ncol + lane] = ll_wait4(pi + 4 * lane, pa, pb, ep_out);
+        }
+        if (lane == 0) {
+            sm.shf[warp] = ll_wait1(pi + D, ep_out);
+            sm.shf[16 + warp] = ll_wait1(pi + D + 1, ep_out);
+        }
+    }
+    cons_sync();
+    if (tid < ncol) {
+        float M = sm.shf[0];
+        for (int s2 = 1; s2 < S; ++s2) M = fmaxf(M, sm.shf[s2]);
+        float Lsum = 0.f;
+        float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int s2 = 0; s2 < S; ++s2) {
+            const float cf = expf(sm.shf[s2] - M);
+            const float4 v = part[s2 * ncol + tid];
+            Lsum = fmaf(sm.shf[16 + s2], cf, Lsum);
+            o.x = fmaf(v.x, cf, o.x);
+            o.y = fmaf(v.y, cf, o.y);
+            o.z = fmaf(v.z, cf, o.z);
+            o.w = fmaf(v.w, cf, o.w);
+        }
+        const float il = 1.0f / Lsum;
+        ll_store(ao, 0, o.x * il, ep_out);
+        ll_store(ao, 1, o.y * il, ep_out);
+        ll_store(ao, 2, o.z * il, ep_out);
+        ll_store(ao, 3, o.w * il, ep_out);
+    }
+    cons_sync();
 }
 
 // rows [r0, r1) of the LM head against NB token rows in shared memory; row j of the CTA goes to warp j % 16
@@ -834,6 +925,8 @@ __global__ void __launch_bounds__(MEGA_THREADS, 1) decode_mega_kernel(const __gr
     off += 32 * 4;
     sm.sc_s = reinterpret_cast<float*>(smem_raw + off);
     off += 32;
+    sm.attw = reinterpret_cast<int*>(smem_raw + off);
+    off += 32;
     sm.bestv = reinterpret_cast<float*>(smem_raw + off);
     off += MEGA_NW * MEGA_MAXB * 4;
     sm.besti = reinterpret_cast<int*>(smem_raw + off);
@@ -888,6 +981,31 @@ __global__ void __launch_bounds__(MEGA_THREADS, 1) decode_mega_kernel(const __gr
         if (p.prefetch) prefetch_l2_lines(sm.layers[0].attn_norm, (size_t)H * 4);
         if (p.barriers) grid_sync(ctr, target, G);
     }
+    // attention work item of this CTA, fixed for the whole step: computed once (divisions) and parked in shared
+    // memory so that it does not occupy registers across the tile loops
+    const int attS = full ? att_splits(p, pos, G) : 1;
+    if (full && tid == 0) {
+        const bool on = cta < NH * B * attS;
+        int lo = 0, hi = 0, head = 0, bb = 0, sp = 0;
+        unsigned long long kv = 0;
+        if (on) {
+            const int task = cta % (NH * B);
+            sp = cta / (NH * B);
+            head = task % NH;
+            bb = task / NH;
+            att_range(pos, attS, sp, lo, hi);
+            kv = ((unsigned long long)bb * NKV + head / (NH / NKV)) * p.max_ctx * D + (unsigned long long)lo * D;
+        }
+        sm.attw[0] = on ? 1 : 0;
+        sm.attw[1] = head;
+        sm.attw[2] = bb;
+        sm.attw[3] = sp;
+        sm.attw[4] = lo;
+        sm.attw[5] = hi;
+        sm.attw[6] = (int)(unsigned)(kv & 0xffffffffull);
+        sm.attw[7] = (int)(unsigned)(kv >> 32);
+    }
+    if (full) cons_sync();
     // ONE call site per phase kind (the bodies are inlined once): op 0 qkv, 1 attention, 2 o, 3 gate/up, 4 down
     for (int l = 0; l < p.L; ++l) {
         const MegaLayer& L = sm.layers[l];
@@ -897,8 +1015,9 @@ __global__ void __launch_bounds__(MEGA_THREADS, 1) decode_mega_kernel(const __gr
                 if (!full) continue;
                 const size_t kvoff = (size_t)l * B * NKV * p.max_ctx * D;
                 prof_stamp(p, pi);  // attention start
-                for (int task = cta; task < NH * B; task += G)
-                    mega_attention(p, sm, task % NH, task / NH, pos, p.kc + kvoff, p.vc + kvoff, ep);
+                // work item = (split, head, sequence), one per CTA (mega_plan: NH * B <= SMs); split 0 merges
+                if (sm.attw[0])
+                    mega_attention(p, sm, sm.attw[1], sm.attw[2], pos, p.kc + kvoff, p.vc + kvoff, ep, sm.attw[3], attS, sm.attw[4], sm.attw[5]);
                 prof_stamp(p, pi);  // attention done
                 if (p.barriers) grid_sync(ctr, target, G);
                 continue;
@@ -916,12 +1035,13 @@ __global__ void __launch_bounds__(MEGA_THREADS, 1) decode_mega_kernel(const __gr
                 // the miss overlaps the wait for the other CTAs' outputs
                 if (!p.prefetch) {
                 } else if (op == 0) {
-                    const int group = NH / NKV;
-                    for (int task = cta; task < NH * B; task += G) {
+                    const int att_lo = sm.attw[4], att_hi = sm.attw[5];
+                    if (sm.attw[0] && att_hi > att_lo) {  // the cached rows this CTA's attention item reads
                         const size_t kv = (size_t)l * B * NKV * p.max_ctx * D +
-                                          ((size_t)(task / NH) * NKV + (task % NH) / group) * p.max_ctx * D;
-                        prefetch_l2_lines(p.kc + kv, (size_t)pos * D * 4);
-                        prefetch_l2_lines(p.vc + kv, (size_t)pos * D * 4);
+                                          (((size_t)(unsigned)sm.attw[7] << 32) | (size_t)(unsigned)sm.attw[6]);
+                        const size_t nb = (size_t)((att_hi < pos ? att_hi : pos) - att_lo) * D * 4;
+                        prefetch_l2_lines(p.kc + kv, nb);
+                        prefetch_l2_lines(p.vc + kv, nb);
                     }
                     if (cta < NH * B && l == 0) {
                         prefetch_l2_lines(p.rope_cos + (size_t)pos * (D / 2), (size_t)D * 2);
@@ -976,7 +1096,7 @@ __global__ void __launch_bounds__(MEGA_THREADS, 1) decode_mega_kernel(const __gr
 // host side
 // ---------------------------------------------------------------------------------------------
 static size_t mega_fixed_smem(int act_bytes, int attn_floats) {
-    size_t off = MEGA_MAX_SLOTS * 16 + 32 * 8 + 32 * 4 + 32 + 2 * MEGA_NW * MEGA_MAXB * 4 +
+    size_t off = MEGA_MAX_SLOTS * 16 + 32 * 8 + 32 * 4 + 32 + 32 + 2 * MEGA_NW * MEGA_MAXB * 4 +
                  (size_t)MEGA_MAX_LAYERS * sizeof(MegaLayer) + MEGA_MAX_TILES * 128 * 4;
     off = (off + 127) & ~(size_t)127;
     off += (size_t)act_bytes;
@@ -991,6 +1111,7 @@ static size_t mega_fixed_smem(int act_bytes, int attn_floats) {
 size_t mega_plan(MegaParams* p, int num_sms) {
     const int QD = p->NH * p->D;
     if (p->B < 1 || p->B > MEGA_MAXB || p->L > MEGA_MAX_LAYERS) return 0;
+    if (p->NH * p->B > num_sms) return 0;                        // one attention work item per CTA
     if (p->H % 256 || p->F % 256 || QD % 256) return 0;          // whole 256-column steps, no tails
     if (p->H > 16 * MEGA_CONS || p->F > 16 * MEGA_CONS || QD > 16 * MEGA_CONS) return 0;  // one prologue pass per row (NV = 4)
     if (p->D % 32 || p->D > 256 || MEGA_CONS % (p->D / 4)) return 0;

@@ -17,6 +17,8 @@ struct MegaParams {
     float *kc, *vc;
     int *pos, *tokens, *next;
     uint2 *x, *qkv, *att, *gu;  // phase outputs as (f32 bits, epoch) pairs: each 8-byte store carries its own ready flag
+    uint2* attp;             // attention partials of split contexts: [B, NH, 8 splits, D + 2] pairs (sum e*v | max | sum e)
+    int att_split;           // 1 = split long contexts over several CTAs per head (knob BITNET_B200_MEGA_NOSPLIT)
     float *logits, *part_val;
     int* part_idx;
     const int8_t* q_fixed;   // mode 1: fixed int8 rows [B, max(H, F, NH*D)]

@@ -61,6 +61,19 @@ def test_gqa_20_5_head128_decoder_matches_cpu(b200, oracle):
     _run_parity(b200, oracle, shape, steps=20, prompt=11)
 
 
+def test_long_context_split_attention_matches_cpu(b200, oracle):
+    # beyond 120 cached positions the persistent kernel splits a head's context over several CTAs and merges
+    # their (max, sum, sum e*v) partials; 2..8 splits are crossed on the way to position 300
+    shape = b200.ModelShape(hidden=256, ffn=512, n_layers=2, n_heads=4, n_kv_heads=2, head_dim=64,
+                            vocab=1000, max_ctx=320, batch=1)
+    _run_parity(b200, oracle, shape, steps=300, prompt=3)
+
+
+def test_long_context_split_attention_gqa_20_5(b200, oracle):
+    shape = b200.ModelShape.bitnet_2b4t(n_layers=2, vocab=2048, max_ctx=200)
+    _run_parity(b200, oracle, shape, steps=190, prompt=17)
+
+
 def test_2b4t_shape_greedy_tokens_identical(b200, oracle):
     # BASELINE.json configs[1]: the full 30-layer 2B-4T shape, vocab 128 256, batch 1
     shape = b200.ModelShape.bitnet_2b4t(max_ctx=32)
