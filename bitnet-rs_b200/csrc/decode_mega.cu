@@ -473,8 +473,8 @@ __device__ __forceinline__ void mega_gemv_phase(const MegaParams& p, const MegaS
 // S partials (one warp per partial polls it into shared memory, warp 0 combines) into the attention output.
 // S = 1 (short contexts) is exactly the single-CTA arithmetic.
 constexpr int ATT_SPLIT_MAX = 8;    // partial slots per (head, sequence)
-constexpr int ATT_SPLIT_FROM = 120; // contexts up to this many positions (two passes of 60) stay on one CTA: the merge hop costs about one pass
-constexpr int ATT_SPLIT_CHUNK = 60; // target positions per split beyond that (one pass of 4 x 15 warps)
+constexpr int ATT_SPLIT_FROM = 48;   // contexts up to this many positions stay on one CTA (the merge hop costs about one pass)
+constexpr int ATT_SPLIT_CHUNK = 24;  // target positions per split beyond that; measured 48/24 > 64/32 > 32/16 > 120/60
 __device__ __forceinline__ int att_splits(const MegaParams& p, int pos, int G) {
     const int ntask = p.NH * p.B;
     int smax = G / ntask;

@@ -62,7 +62,7 @@ def test_gqa_20_5_head128_decoder_matches_cpu(b200, oracle):
 
 
 def test_long_context_split_attention_matches_cpu(b200, oracle):
-    # beyond 120 cached positions the persistent kernel splits a head's context over several CTAs and merges
+    # beyond 48 cached positions the persistent kernel splits a head's context over several CTAs and merges
     # their (max, sum, sum e*v) partials; 2..8 splits are crossed on the way to position 300
     shape = b200.ModelShape(hidden=256, ffn=512, n_layers=2, n_heads=4, n_kv_heads=2, head_dim=64,
                             vocab=1000, max_ctx=320, batch=1)
