@@ -101,3 +101,25 @@ def test_device_loop_equals_host_loop(b200, oracle):
     ms, n = gm.time_linears(3)
     assert n in (1, 4 * shape.n_layers) and ms > 0  # 1 = the persistent one-kernel step
     gm.close()
+
+
+def test_decode_chain_is_deterministic_across_repetitions(b200):
+    # The phases of the persistent kernel hand their outputs on through flagged (value, epoch) pairs, with no
+    # grid barrier in between: a stale or torn pair would change the greedy chain, a lost one traps. Four
+    # repetitions of a 400-step chain (context splitting included) must agree checkpoint by checkpoint.
+    shape = b200.ModelShape.bitnet_2b4t(n_layers=6, vocab=8192, max_ctx=416)
+    ctx = b200.Context(0)
+    gm = b200.Model(ctx, shape)
+    gm.load_synthetic()
+    ref = None
+    for rep in range(4):
+        gm.reset()
+        gm.set_tokens(np.array([1], np.int32))
+        chain = []
+        for _ in range(8):
+            gm.decode_device(50)
+            ctx.synchronize()
+            chain.append(int(gm.get_tokens()[0]))
+        ref = ref or chain
+        assert chain == ref, "repetition %d diverged: %r vs %r" % (rep, chain, ref)
+    gm.close()
