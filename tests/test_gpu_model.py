@@ -61,12 +61,13 @@ def test_gqa_20_5_head128_decoder_matches_cpu(b200, oracle):
     _run_parity(b200, oracle, shape, steps=20, prompt=11)
 
 
-def test_long_context_split_attention_matches_cpu(b200, oracle):
+@pytest.mark.parametrize("batch,steps", [(1, 300), (2, 150)])
+def test_long_context_split_attention_matches_cpu(b200, oracle, batch, steps):
     # beyond 48 cached positions the persistent kernel splits a head's context over several CTAs and merges
     # their (max, sum, sum e*v) partials; 2..8 splits are crossed on the way to position 300
     shape = b200.ModelShape(hidden=256, ffn=512, n_layers=2, n_heads=4, n_kv_heads=2, head_dim=64,
-                            vocab=1000, max_ctx=320, batch=1)
-    _run_parity(b200, oracle, shape, steps=300, prompt=3)
+                            vocab=1000, max_ctx=320, batch=batch)
+    _run_parity(b200, oracle, shape, steps=steps, prompt=3)
 
 
 def test_long_context_split_attention_gqa_20_5(b200, oracle):
