@@ -131,22 +131,22 @@ __device__ __forceinline__ uint32_t code_of(uint32_t w_dev, int k) { return (w_d
 
 // Decode one device-layout word (sixteen 2-bit codes) through a 4-entry int8 LUT -- one PRMT
 // per four weights -- and dot it with sixteen int8 activations in natural order (a.x = k0..3).
-// The two >>16 go through IMAD.HI (FMA pipe) to keep the ALU pipe for LOP3/PRMT.
+// The shifts are plain SHF: IMAD.HI (umulhi), once used here to move them to the FMA pipe, measured SLOWER on
+// B200 (tools/ubench/tile_loop.cu: 7.8 vs 6.2 cycles per 512-weight fragment per SM).
 __device__ __forceinline__ int dot16(uint32_t w, uint32_t lut, uint4 a, int acc) {
     const uint32_t x = w & 0x33333333u;
-    const uint32_t y = __umulhi(w, 0x40000000u) & 0x33333333u;  // (w >> 2) & mask
+    const uint32_t y = (w >> 2) & 0x33333333u;
     acc = dp4a_ss(prmt(lut, 0u, x), a.x, acc);
     acc = dp4a_ss(prmt(lut, 0u, y), a.y, acc);
-    acc = dp4a_ss(prmt(lut, 0u, __umulhi(x, 0x10000u)), a.z, acc);
-    acc = dp4a_ss(prmt(lut, 0u, __umulhi(y, 0x10000u)), a.w, acc);
+    acc = dp4a_ss(prmt(lut, 0u, x >> 16), a.z, acc);
+    acc = dp4a_ss(prmt(lut, 0u, y >> 16), a.w, acc);
     return acc;
 }
 // decode a device-layout word into sixteen int8 values in natural order (4 words)
 __device__ __forceinline__ uint4 decode16(uint32_t w, uint32_t lut) {
     const uint32_t x = w & 0x33333333u;
-    const uint32_t y = __umulhi(w, 0x40000000u) & 0x33333333u;
-    return make_uint4(prmt(lut, 0u, x), prmt(lut, 0u, y), prmt(lut, 0u, __umulhi(x, 0x10000u)),
-                      prmt(lut, 0u, __umulhi(y, 0x10000u)));
+    const uint32_t y = (w >> 2) & 0x33333333u;
+    return make_uint4(prmt(lut, 0u, x), prmt(lut, 0u, y), prmt(lut, 0u, x >> 16), prmt(lut, 0u, y >> 16));
 }
 
 // ---- PTX: mbarrier, 1-D bulk copy (TMA), programmatic dependent launch ----------------------

@@ -256,6 +256,7 @@ struct bitnet_b200_model {
     int fused = -1;             // -1 undecided, 0 generic kernels, 1 fused PDL path
     int mega = -1;              // -1 undecided, 0 no, 1 the persistent one-kernel step (decode_mega.cu)
     MegaLayer* mega_layers = nullptr;  // device table
+    std::vector<uint8_t*> mega_codes;  // fragment-major copies of the code planes (4 per layer), owned
     unsigned* mega_bar = nullptr;      // [2][8] grid-barrier counters, one per 256-byte line
     int mega_parity = 0;
     uint2* mega_ll = nullptr;          // (value, epoch) pair buffers of the phase outputs: x | qkv | att | gu
@@ -495,7 +496,19 @@ static int mega_setup(bitnet_b200_model* m) {
         const LayerW& L = m->layers[(size_t)l];
         for (const bitnet_b200_weight* w : {L.wqkv, L.wo, L.wgateup, L.wdown})
             if (w->code_stride != w->cols / 4 || w->lut_word != m->layers[0].wqkv->lut_word) return 0;
-        tab[(size_t)l] = MegaLayer{L.wqkv->codes, L.wo->codes, L.wgateup->codes, L.wdown->codes, L.attn_norm, L.ffn_norm};
+    }
+    // fragment-major copies of every code plane (decode_mega.cu: mega_repack_kernel), made once
+    for (int l = 0; l < c.n_layers; ++l) {
+        const LayerW& L = m->layers[(size_t)l];
+        uint8_t* fm[4] = {nullptr, nullptr, nullptr, nullptr};
+        int j = 0;
+        for (const bitnet_b200_weight* w : {L.wqkv, L.wo, L.wgateup, L.wdown}) {
+            if (dmalloc((void**)&fm[j], w->rows * w->cols / 4)) return -1;
+            m->mega_codes.push_back(fm[j]);
+            if (mega_repack_weight(w->codes, (int)w->rows, (int)w->cols, fm[j], m->ctx->stream)) return -1;
+            ++j;
+        }
+        tab[(size_t)l] = MegaLayer{fm[0], fm[1], fm[2], fm[3], L.attn_norm, L.ffn_norm};
     }
     if (dmalloc((void**)&m->mega_layers, tab.size() * sizeof(MegaLayer)) || dmalloc((void**)&m->mega_bar, 4096)) return -1;  // 2 parities x 8 counters on 256-byte lines
     cudaStream_t st = m->ctx->stream;
@@ -522,9 +535,11 @@ static int mega_setup(bitnet_b200_model* m) {
     p.q_fixed = m->q8; p.s_fixed = m->s8; p.bar = m->mega_bar;
     p.lut = m->layers[0].wqkv->lut_word;
     p.prefetch = getenv("BITNET_B200_MEGA_NOPF") ? 0 : 1;
-    if (getenv("BITNET_B200_MEGA_PROF")) {  // diagnostics: per-phase globaltimer stamps of CTA 0, dumped at destroy
-        if (dmalloc((void**)&p.prof, 16384 * 8)) return -1;
-        B200_CUDA(cudaMemset(p.prof, 0, 16384 * 8));
+    if (getenv("BITNET_B200_MEGA_PROF")) {  // diagnostics: per-phase stamps of every CTA + per-warp trace of one CTA, dumped at destroy
+        const size_t n = (size_t)m->ctx->num_sms * 1024 + 16 * 4096;
+        if (dmalloc((void**)&p.prof, n * 8)) return -1;
+        B200_CUDA(cudaMemset(p.prof, 0, n * 8));
+        p.prof_cta = getenv("BITNET_B200_MEGA_PROF_CTA") ? atoi(getenv("BITNET_B200_MEGA_PROF_CTA")) : 0;
     }
     m->mega_parity = 0;
     m->mega = 1;
@@ -639,20 +654,18 @@ int bitnet_b200_model_create(bitnet_b200_ctx* ctx, const bitnet_b200_model_confi
 void bitnet_b200_model_destroy(bitnet_b200_model* m) {
     if (!m) return;
     if (m->graph) cudaGraphExecDestroy(m->graph);
-    if (m->mega_p.prof) {
-        std::vector<unsigned long long> h(16384);
-        if (cudaMemcpy(h.data(), m->mega_p.prof, h.size() * 8, cudaMemcpyDeviceToHost) == cudaSuccess)
-            if (FILE* f = fopen(getenv("BITNET_B200_MEGA_PROF") ? getenv("BITNET_B200_MEGA_PROF") : "/dev/null", "w")) {
-                for (size_t i = 0; i < 8192 && h[i]; ++i) fprintf(f, "%llu\n", h[i] - h[0]);
-                for (size_t i = 14000; i < 14064; ++i)
-                    if (h[i]) fprintf(f, "@ %zu %llu\n", i - 14000, h[i] - h[14000]);
-                for (size_t i = 8192; i < 14000; ++i)
-                    if (h[i]) fprintf(f, "# %zu %llu %llu\n", i - 8192, h[i] >> 32, h[i] & 0xffffffffull);
+    if (m->mega_p.prof) {  // raw u64 dump: [num_sms][1024] phase stamps, then [16][4096] warp trace (tools/megaprof.py reads it)
+        const size_t n = (size_t)m->ctx->num_sms * 1024 + 16 * 4096;
+        std::vector<unsigned long long> h(n);
+        if (cudaMemcpy(h.data(), m->mega_p.prof, n * 8, cudaMemcpyDeviceToHost) == cudaSuccess)
+            if (FILE* f = fopen(getenv("BITNET_B200_MEGA_PROF") ? getenv("BITNET_B200_MEGA_PROF") : "/dev/null", "wb")) {
+                fwrite(h.data(), 8, n, f);
                 fclose(f);
             }
         cudaFree(m->mega_p.prof);
     }
     if (m->mega_layers) cudaFree(m->mega_layers);
+    for (uint8_t* q : m->mega_codes) cudaFree(q);
     if (m->mega_bar) cudaFree(m->mega_bar);
     if (m->mega_ll) cudaFree(m->mega_ll);
     for (auto& L : m->layers) {

@@ -1,7 +1,7 @@
 // decode_mega.cu -- one decode step of a 2B-4T-shaped ternary decoder as ONE persistent,
 // cooperative kernel (QK256 layout, batch <= 4): one CTA per SM, a dedicated producer warp that
 // streams EVERY packed weight of the step (and the f16 LM head) through a shared-memory ring with
-// 1-D bulk copies (TMA, cp.async.bulk -> mbarrier) and never stops at a phase boundary, and 16
+// 1-D bulk copies (TMA, cp.async.bulk -> mbarrier) and never stops at a phase boundary, and 15
 // consumer warps that run the phases
 //     embed | per layer: [RMSNorm+act-quant | qkv GEMV] -> [RoPE + KV append + GQA attention]
 //     -> [act-quant | o GEMV + residual] -> [RMSNorm+act-quant | gate/up GEMV | SwiGLU]
@@ -12,16 +12,27 @@
 // Why: at batch 1 a 2B-4T projection is 0.25-1.4 us of HBM time, below any launch or barrier
 // latency, so a chain of per-projection kernels is latency-bound with the memory pipe idle most
 // of the time (measured: 4.3-12 us per projection launch). Here the weight stream is decoupled
-// from the dependency chain: while the consumers sit in a grid barrier or in the activation
-// prologue of phase p, the producer is already filling the ring with the tiles of phase p+1,
-// p+2, ... (up to ~1.3 layers ahead across the 148 SMs).
+// from the dependency chain: while the consumers wait for the activations of phase p, the producer is
+// already filling the ring with the tiles of phase p+1, p+2, ... (about one layer ahead across the 148 SMs).
 //
-// Hot-path arithmetic is that of gemv_mma.cu: 2-bit codes -> 4-entry int8 LUT (PRMT) -> A fragment
-// of mma.sync.m16n8k32.s8, int8 activations as the B fragment, int32 accumulation (exact;
-// bit-identical to gemv_qk256 on integer inputs, crates/bitnet-quantization/src/i2s_qk256.rs:
-// 346-372), per-token absmax int8 quantiser (cpu/quantize.rs:32-49) and cpu::rms_norm
-// (cpu/layer_norm.rs:118-137) in the prologue. Cross-warp partial sums meet through int32
-// shared-memory atomics: integer addition is associative, so the result is order-independent.
+// Work split of a GEMV phase (round 2): a CTA owns a CONTIGUOUS range of 16-row tiles, and inside the CTA
+// every warp owns a fixed slice of K (k-chunks of 32 columns) of EVERY tile. So
+//   * the weights are kept in a fragment-major copy made once at model build (mega_repack_kernel):
+//     [tile][k-chunk][lane] 32-bit words, word of lane (g, t) = the sixteen codes that lane feeds to
+//     mma.sync.m16n8k32 as (a0, a1, a2, a3); a CTA's share of a projection is ONE contiguous byte range
+//     (one bulk copy per ring slot), a warp's load of a fragment is one conflict-free 128-byte LDS.32;
+//   * a warp needs only ITS columns of the activation vector: it polls, normalises and quantises 160-480
+//     values, not the whole row (the old kernel had all 148 x 480 threads redo the whole vector behind four
+//     CTA barriers); the row statistics (sum of squares, absmax) meet through 15 shared-memory slots and one
+//     named barrier each;
+//   * accumulators stay in registers over the warp's K slice; the 15 per-warp partials of a row meet once per
+//     phase through shared memory (plain stores + one barrier, no shared atomics). Integer addition: exact,
+//     order-independent.
+//
+// Hot-path arithmetic: 2-bit codes -> 4-entry int8 LUT (PRMT) -> A fragment of mma.sync.m16n8k32.s8, int8
+// activations as the B fragment, int32 accumulation (exact; bit-identical to gemv_qk256 on integer inputs,
+// crates/bitnet-quantization/src/i2s_qk256.rs:346-372), per-token absmax int8 quantiser
+// (cpu/quantize.rs:32-49) and cpu::rms_norm (cpu/layer_norm.rs:118-137) in the prologue.
 #include "decode_mega.h"
 
 namespace b200 {
@@ -29,13 +40,18 @@ namespace b200 {
 constexpr int MEGA_NW = 15;                         // consumer warps
 constexpr int MEGA_CONS = MEGA_NW * 32;             // consumer threads
 constexpr int MEGA_THREADS = MEGA_CONS + 32;        // + the producer warp
-constexpr int MEGA_SLOT_STEPS = 16;                 // 256-column steps per ring slot
-constexpr int MEGA_SLOT_BYTES = 16 * MEGA_SLOT_STEPS * 64;  // 16 rows x 16 steps x 64 B
-constexpr int MEGA_MAX_TILES = 16;                  // 16-row tiles per CTA per phase
+constexpr int MEGA_SLOT_BYTES = 30720;              // ring slot: 240 k-chunk fragments of 128 B = three 16-row tiles at K = 2560,
+                                                    // one at K = 6912, six LM-head rows at H = 2560
+constexpr int MEGA_SLOT_KC = MEGA_SLOT_BYTES / 128; // k-chunks (32 columns of a 16-row tile) per slot
 constexpr int MEGA_MAXB = 4;                        // tokens per step
-constexpr int MEGA_MAX_SLOTS = 12;
+constexpr int MEGA_MAX_SLOTS = 8;
 constexpr int MEGA_MAX_LAYERS = 64;
-static_assert(MEGA_MAX_TILES * 16 <= MEGA_CONS, "epilogue: one output row per consumer thread");
+constexpr int MEGA_MAXC = 16;                       // k-chunks per warp at most: K <= 15 * 16 * 32 = 7680
+// shared-memory map: fixed pieces, then the ring, then (host-computed offsets) red | act | attn
+constexpr int MEGA_OFF_FULL = 0, MEGA_OFF_EMPTY = MEGA_OFF_FULL + MEGA_MAX_SLOTS * 8, MEGA_OFF_SHD = MEGA_OFF_EMPTY + MEGA_MAX_SLOTS * 8,
+              MEGA_OFF_SHF = MEGA_OFF_SHD + 32 * 8, MEGA_OFF_ATTW = MEGA_OFF_SHF + 32 * 4, MEGA_OFF_BESTV = MEGA_OFF_ATTW + 32,
+              MEGA_OFF_BESTI = MEGA_OFF_BESTV + MEGA_NW * MEGA_MAXB * 4, MEGA_OFF_LAYERS = MEGA_OFF_BESTI + MEGA_NW * MEGA_MAXB * 4,
+              MEGA_OFF_RING = (MEGA_OFF_LAYERS + MEGA_MAX_LAYERS * (int)sizeof(MegaLayer) + 127) & ~127;
 
 // ---- small PTX helpers ------------------------------------------------------------------------
 __device__ __forceinline__ void cons_sync() { asm volatile("bar.sync 1, %0;" ::"n"(MEGA_CONS) : "memory"); }
@@ -71,18 +87,27 @@ __device__ __forceinline__ void mma_s8_m16n8k32(int (&c)[4], uint32_t a0, uint32
 // Write-after-read safety without barriers: a CTA can only produce out(n+1) after it has seen ALL of out(n),
 // i.e. after every CTA finished phase n including its reads of out(n-1); adjacent phase outputs live in
 // different buffers (qkv, att, x, gu, x, ...), so nothing still being read is overwritten.
+// The pair is moved as ONE 64-bit scalar (epoch in the high word): 64-bit scalar accesses are single-copy
+// atomic in the PTX memory model; the 16-byte form below is a vector of two such scalars, each pair validated
+// by its own epoch.
 __device__ __forceinline__ void ll_store(uint2* buf, size_t i, float v, uint32_t ep) {
-    asm volatile("st.relaxed.gpu.global.v2.u32 [%0], {%1, %2};" ::"l"(buf + i), "r"(__float_as_uint(v)), "r"(ep) : "memory");
+    const unsigned long long w = ((unsigned long long)ep << 32) | (unsigned long long)__float_as_uint(v);
+    asm volatile("st.relaxed.gpu.global.b64 [%0], %1;" ::"l"(buf + i), "l"(w) : "memory");
 }
 __device__ __forceinline__ uint4 ll_ld2(const uint2* p) {  // two pairs
-    uint4 v;
-    asm volatile("ld.relaxed.gpu.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
-    return v;
+    unsigned long long a, b;
+    asm volatile("ld.relaxed.gpu.global.v2.b64 {%0,%1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
+    return make_uint4((uint32_t)a, (uint32_t)(a >> 32), (uint32_t)b, (uint32_t)(b >> 32));
+}
+__device__ __forceinline__ unsigned long long ll_ld_raw(const unsigned long long* p) {  // epoch in the high word
+    unsigned long long a;
+    asm volatile("ld.relaxed.gpu.global.b64 %0, [%1];" : "=l"(a) : "l"(p) : "memory");
+    return a;
 }
 __device__ __forceinline__ uint2 ll_ld1(const uint2* p) {
-    uint2 v;
-    asm volatile("ld.relaxed.gpu.global.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p) : "memory");
-    return v;
+    unsigned long long a;
+    asm volatile("ld.relaxed.gpu.global.b64 %0, [%1];" : "=l"(a) : "l"(p) : "memory");
+    return make_uint2((uint32_t)a, (uint32_t)(a >> 32));
 }
 __device__ __forceinline__ float ll_wait1(const uint2* p, uint32_t ep) {
     uint2 v = ll_ld1(p);
@@ -125,15 +150,46 @@ __device__ __forceinline__ int mega_quant_i8(float v, float inv) {
     return max(-127, min(127, r));
 }
 
-// diagnostics: CTA 0 / thread 0 appends a globaltimer stamp (ns) when p.prof is set
-__device__ __forceinline__ void prof_stamp(const MegaParams& p, int& pi) {
-    if (p.prof && blockIdx.x == 0 && threadIdx.x == 0 && pi < 16384) {
-        unsigned long long t;
-        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-        p.prof[pi] = t;
-    }
+// diagnostics, compiled only with -DMEGA_TRACE (`make trace` -> libbitnet_b200_trace.so; the stamps cost code
+// size, and the kernel's per-layer instruction footprint has to stay inside the 32 KB L1.5 instruction cache):
+// thread 0 of EVERY CTA appends a globaltimer stamp (ns) per phase boundary into prof[cta][MEGA_PROF_PER_CTA];
+// lane 0 of every consumer warp of CTA p.prof_cta appends finer stamps into
+// prof[G * MEGA_PROF_PER_CTA + warp * MEGA_PROF_PER_WARP ...] as (id << 48 | ns)
+constexpr int MEGA_PROF_PER_CTA = 1024, MEGA_PROF_PER_WARP = 4096;
+#ifdef MEGA_TRACE
+__device__ __forceinline__ unsigned long long gtime() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __noinline__ void prof_stamp(const MegaParams& p, int& pi) {
+    if (p.prof && threadIdx.x == 0 && pi < MEGA_PROF_PER_CTA) p.prof[(size_t)blockIdx.x * MEGA_PROF_PER_CTA + pi] = gtime();
     ++pi;
 }
+__device__ __noinline__ void wtrace(const MegaParams& p, int& wi, int id) {
+    if (p.prof && (int)blockIdx.x == p.prof_cta && (threadIdx.x & 31) == 0) {
+        if (wi < MEGA_PROF_PER_WARP)
+            p.prof[(size_t)gridDim.x * MEGA_PROF_PER_CTA + (size_t)(threadIdx.x >> 5) * MEGA_PROF_PER_WARP + wi] =
+                ((unsigned long long)id << 48) | (gtime() & 0xffffffffffffull);
+        ++wi;
+    }
+}
+// same slot format, but the low 48 bits carry a caller-supplied number (cycle counts)
+__device__ __noinline__ void wtrace_val(const MegaParams& p, int& wi, int id, unsigned long long v) {
+    if (p.prof && (int)blockIdx.x == p.prof_cta && (threadIdx.x & 31) == 0) {
+        if (wi < MEGA_PROF_PER_WARP)
+            p.prof[(size_t)gridDim.x * MEGA_PROF_PER_CTA + (size_t)(threadIdx.x >> 5) * MEGA_PROF_PER_WARP + wi] =
+                ((unsigned long long)id << 48) | (v & 0xffffffffffffull);
+        ++wi;
+    }
+}
+#define MEGA_TRACE_ONLY(x) x
+#else
+__device__ __forceinline__ void prof_stamp(const MegaParams&, int&) {}
+__device__ __forceinline__ void wtrace(const MegaParams&, int&, int) {}
+__device__ __forceinline__ void wtrace_val(const MegaParams&, int&, int, unsigned long long) {}
+#define MEGA_TRACE_ONLY(x)
+#endif
 
 // producer-side wait: sleeps between probes (the ring is deep, the producer is never latency-critical)
 __device__ __forceinline__ void mbar_wait_backoff(void* bar, uint32_t parity) {
@@ -173,140 +229,143 @@ __device__ __forceinline__ void grid_sync(unsigned* ctr, unsigned& target, unsig
     cons_sync();
 }
 
-// split `ns` 256-column steps into `nch` nearly equal chunks; chunk c = steps [s0, s0 + cs)
-__device__ __forceinline__ void chunk_range(int ns, int nch, int c, int& s0, int& cs) {
-    const int base = ns / nch, rem = ns - base * nch;
-    s0 = c * base + (c < rem ? c : rem);
-    cs = base + (c < rem ? 1 : 0);
-}
-
 struct MegaSmem {
-    uint64_t* full;    // [n_slots]
-    uint64_t* empty;   // [n_slots]
+    uint64_t* full;    // [MEGA_MAX_SLOTS]
+    uint64_t* empty;   // [MEGA_MAX_SLOTS]
     double* shd;       // [32]
-    float* shf;        // [32]
-    float* sc_s;       // [MEGA_MAXB]
+    float* shf;        // [2][16] (two parities: see mega_prologue) -- the attention and LM-head code uses the first 32
     int* attw;         // [8] this CTA's attention work item: on, head, seq, split, lo, hi, kv offset (2 words)
     float* bestv;      // [MEGA_NW * MEGA_MAXB]
     int* besti;        // [MEGA_NW * MEGA_MAXB]
     MegaLayer* layers; // [L]
-    int* acc;          // [MEGA_MAX_TILES][16][8]
-    unsigned char* act;  // int8 rows [B][K + 64]  or  f32 rows [B][H]
+    int* red;          // [MEGA_NW][red_ld] per-warp int32 partials of the CTA's output rows
+    unsigned char* act;  // int8 rows [B][K + 64] (k-chunk bytes in B-fragment order)  or  f32 rows [B][H]
+    float* stage;      // f32 staging of the prologue: values [kmax] | norm weights [H], lane-private slices
     float* attn;       // scores [max_ctx] | value partials [512 float4] | q,k,v rows [3][256]
     unsigned char* ring;
 };
 
-// ---- activation prologue: f32 rows -> (optional RMSNorm) -> int8 rows + scale in shared memory ---
+// geometry of one GEMV phase on this CTA (MegaOp: filled by mega_plan, identical arithmetic in the producer warp)
+struct PhaseGeom {
+    int t0, nloc;     // this CTA's tiles [t0, t0 + nloc): the first `tr` CTAs own tq + 1 tiles, the others tq
+};
+__device__ __forceinline__ PhaseGeom phase_geom(const MegaOp& o, int cta) {
+    PhaseGeom q;
+    q.t0 = cta * o.tq + min(cta, o.tr);
+    q.nloc = o.tq + (cta < o.tr ? 1 : 0);
+    return q;
+}
+// position of column j (0..31) of a k-chunk inside the chunk's 32 activation bytes: lane t of the B fragment
+// reads (b0, b1) = columns 4t..4t+3 and 16+4t..16+4t+3 with one 8-byte load at offset 8t
+__device__ __forceinline__ int bfrag_pos(int j) { return (j & 3) + 8 * ((j >> 2) & 3) + 4 * (j >> 4); }
+
+// ---- activation prologue, per WARP: the warp's own k-chunks [kc0, kc0 + nc) of every token row ----------
 // pro: 0 = copy the fixed int8 rows (mode 1), 1 = absmax int8 quantise, 2 = RMSNorm then quantise.
-// NV = float4 groups per thread (K <= 16 * NV * MEGA_CONS... i.e. 2 -> K <= 4096, 4 -> K <= 8192).
-template <int NV>
-__device__ __forceinline__ void mega_prologue_rows(const MegaParams& p, const MegaSmem& sm, int pro, const uint2* xin,
-                                                   uint32_t ep_in, const float* gamma, int K, int q_ld) {
+// Lane j of the warp owns column 32 * kc + j of each of its chunks. The values are parked in a lane-private
+// f32 staging slice in shared memory (with the norm weights beside them) and walked by short rolled loops:
+// the code of a phase has to be SMALL -- the kernel is one long chain of phases executed once each per layer,
+// and its per-layer instruction footprint must stay inside the 32 KB L1.5 instruction cache (measured: the
+// register-array version, 200 KB of SASS, ran every phase 2-3 x slower than its instruction count explains).
+// Row statistics meet through shd / shf and one named barrier each; shf alternates between two halves (`par`) so
+// that a fast warp's next write cannot overtake a slow warp's read of the previous value (shd needs no parity:
+// its reads precede the absmax barrier).
+constexpr int MEGA_POLL = 8;  // pair loads in flight per lane per round
+__device__ __forceinline__ void mega_prologue(const MegaParams& p, const MegaSmem& sm, int pro, const uint2* xin, uint32_t ep_in,
+                                           const float* gamma, int K, int kc0, int nc, float (&sc)[MEGA_MAXB], uint32_t& par,
+                                           int& wi) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    int8_t* qbuf = reinterpret_cast<int8_t*>(sm.act);
-    const int ngrp = K >> 2;
-    float4 gm[NV];  // norm weights: fetched with the first row, not after the sum-of-squares barrier
-    if (pro == 2) {
+    const int q_ld = K + 64;
+    unsigned char* qb = sm.act + 32 * kc0 + bfrag_pos(lane);
+    float* stg = sm.stage + 32 * kc0 + lane;  // value of chunk c at stg[32 * c], its norm weight at stg[K + 32 * c]
+    if (pro == 0) {
+        cons_sync();  // the previous phase's readers of sm.red / sm.act are done
+        for (int m = 0; m < p.B; ++m) {
+            const int8_t* src = p.q_fixed + (size_t)m * K + 32 * kc0 + lane;
+#pragma unroll 4
+            for (int c = 0; c < nc; ++c) qb[m * q_ld + 32 * c] = (unsigned char)src[32 * c];
+            const float s = p.s_fixed[m];
 #pragma unroll
-        for (int j = 0; j < NV; ++j) {
-            const int g = tid + j * MEGA_CONS;
-            gm[j] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (g < ngrp) gm[j] = __ldg(reinterpret_cast<const float4*>(gamma) + g);
+            for (int j = 0; j < MEGA_MAXB; ++j) sc[j] = j == m ? s : sc[j];
         }
+        __syncwarp();
+        return;
     }
+#pragma unroll 1
     for (int m = 0; m < p.B; ++m) {
-        float4 v[NV];
-        uint4 pa[NV], pb[NV];  // first probe of every group in flight before any flag is looked at
+        const uint2* xr = xin + (size_t)m * K + 32 * kc0 + lane;
+        double ss = 0.0;
+        float amax = 0.f;
+#pragma unroll 1
+        if (pro == 2 && m == 0) {  // norm weights (L2-prefetched by the previous phase): in flight under the polls
+#pragma unroll 4
+            for (int c = 0; c < nc; ++c) stg[K + 32 * c] = __ldg(gamma + 32 * (kc0 + c) + lane);
+        }
+        const unsigned long long valid0 = (unsigned long long)ep_in << 32;  // what a slot beyond nc pretends to hold: (0.0f, ep_in)
+#pragma unroll 1
+        for (int c0 = 0; c0 < nc; c0 += MEGA_POLL) {
+            const unsigned long long* xp = reinterpret_cast<const unsigned long long*>(xr + 32 * c0);
+            unsigned long long pr[MEGA_POLL];
+            // The whole group is (re-)probed until every pair carries the producing phase's epoch: one copy of the load
+            // code, MEGA_POLL loads in flight, one L2 round trip per round (asm volatile: re-fetched every time; the
+            // header's __ldcv is a plain asm and was hoisted out of the loop).
+            for (uint32_t it = 0;; ++it) {
 #pragma unroll
-        for (int j = 0; j < NV; ++j) {
-            const int g = tid + j * MEGA_CONS;
-            if (g < ngrp) {
-                pa[j] = ll_ld2(xin + (size_t)m * K + 4 * g);
-                pb[j] = ll_ld2(xin + (size_t)m * K + 4 * g + 2);
+                for (int j = 0; j < MEGA_POLL; ++j) pr[j] = c0 + j < nc ? ll_ld_raw(xp + 32 * j) : valid0;
+                bool ok = true;
+#pragma unroll
+                for (int j = 0; j < MEGA_POLL; ++j) ok = ok && (uint32_t)(pr[j] >> 32) == ep_in;
+                if (ok) break;
+                if (it > (1u << 24)) __trap();
+            }
+#pragma unroll
+            for (int j = 0; j < MEGA_POLL; ++j) {
+                const float v = __uint_as_float((uint32_t)pr[j]);
+                if (c0 + j < nc) stg[32 * (c0 + j)] = v;
+                if (pro == 2) ss += (double)v * (double)v;
+                else amax = fmaxf(amax, fabsf(v));
             }
         }
-#pragma unroll
-        for (int j = 0; j < NV; ++j) {
-            const int g = tid + j * MEGA_CONS;
-            v[j] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (g < ngrp) v[j] = ll_wait4(xin + (size_t)m * K + 4 * g, pa[j], pb[j], ep_in);
-        }
+        wtrace(p, wi, 2);
         if (pro == 2) {
-            double ss = 0.0;
-#pragma unroll
-            for (int j = 0; j < NV; ++j)
-                ss += (double)v[j].x * (double)v[j].x + (double)v[j].y * (double)v[j].y +
-                      (double)v[j].z * (double)v[j].z + (double)v[j].w * (double)v[j].w;
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
             if (lane == 0) sm.shd[warp] = ss;
             cons_sync();
+            wtrace(p, wi, 7);
             double tot = 0.0;
 #pragma unroll
             for (int wv = 0; wv < MEGA_NW; ++wv) tot += sm.shd[wv];
             const float ms = (float)(tot / (double)K);
             const float inv_rms = 1.0f / sqrtf(ms + p.eps);
-#pragma unroll
-            for (int j = 0; j < NV; ++j) {
-                const int g = tid + j * MEGA_CONS;
-                if (g < ngrp) {
-                    v[j].x = v[j].x * inv_rms * gm[j].x;
-                    v[j].y = v[j].y * inv_rms * gm[j].y;
-                    v[j].z = v[j].z * inv_rms * gm[j].z;
-                    v[j].w = v[j].w * inv_rms * gm[j].w;
-                }
+#pragma unroll 4
+            for (int c = 0; c < nc; ++c) {
+                const float v = stg[32 * c] * inv_rms * stg[K + 32 * c];
+                stg[32 * c] = v;
+                amax = fmaxf(amax, fabsf(v));
             }
         }
-        float amax = 0.f;
-#pragma unroll
-        for (int j = 0; j < NV; ++j)
-            amax = fmaxf(amax, fmaxf(fmaxf(fabsf(v[j].x), fabsf(v[j].y)), fmaxf(fabsf(v[j].z), fabsf(v[j].w))));
         amax = warp_max(amax);
-        if (lane == 0) sm.shf[warp] = amax;
+        float* shf = sm.shf + 16 * par;
+        par ^= 1u;
+        if (lane == 0) shf[warp] = amax;
         cons_sync();
+        wtrace(p, wi, 8);
         amax = 0.f;
 #pragma unroll
-        for (int wv = 0; wv < MEGA_NW; ++wv) amax = fmaxf(amax, sm.shf[wv]);
-        const float sc = amax == 0.f ? 0.f : amax / 127.f;
-        const float inv = amax == 0.f ? 0.f : 1.0f / sc;
-        if (tid == 0) sm.sc_s[m] = sc;
+        for (int wv = 0; wv < MEGA_NW; ++wv) amax = fmaxf(amax, shf[wv]);
+        const float s = amax == 0.f ? 0.f : amax / 127.f;
+        const float inv = amax == 0.f ? 0.f : 1.0f / s;
 #pragma unroll
-        for (int j = 0; j < NV; ++j) {
-            const int g = tid + j * MEGA_CONS;
-            if (g < ngrp) {
-                uint32_t wq = 0;
-                if (amax != 0.f)
-                    wq = (uint32_t)(uint8_t)mega_quant_i8(v[j].x, inv) | ((uint32_t)(uint8_t)mega_quant_i8(v[j].y, inv) << 8) |
-                         ((uint32_t)(uint8_t)mega_quant_i8(v[j].z, inv) << 16) |
-                         ((uint32_t)(uint8_t)mega_quant_i8(v[j].w, inv) << 24);
-                reinterpret_cast<uint32_t*>(qbuf + m * q_ld)[g] = wq;
-            }
-        }
-        cons_sync();  // shd/shf reusable; qbuf + sc_s visible
+        for (int j = 0; j < MEGA_MAXB; ++j) sc[j] = j == m ? s : sc[j];
+#pragma unroll 4
+        for (int c = 0; c < nc; ++c) qb[m * q_ld + 32 * c] = amax == 0.f ? (unsigned char)0 : (unsigned char)mega_quant_i8(stg[32 * c], inv);
     }
-}
-
-__device__ __forceinline__ void mega_prologue(const MegaParams& p, const MegaSmem& sm, int pro, const uint2* xin,
-                                           uint32_t ep_in, const float* gamma, int K, int q_ld) {
-    const int tid = threadIdx.x;
-    if (pro == 0) {
-        int8_t* qbuf = reinterpret_cast<int8_t*>(sm.act);
-        const int vpr = K >> 4;
-        for (int m = 0; m < p.B; ++m)
-            for (int v = tid; v < vpr; v += MEGA_CONS)
-                *reinterpret_cast<uint4*>(qbuf + m * q_ld + v * 16) =
-                    *reinterpret_cast<const uint4*>(p.q_fixed + (size_t)m * K + v * 16);
-        if (tid < p.B) sm.sc_s[tid] = p.s_fixed[tid];
-        cons_sync();
-        return;
-    }
-    if (K <= 8 * MEGA_CONS) mega_prologue_rows<2>(p, sm, pro, xin, ep_in, gamma, K, q_ld);
-    else mega_prologue_rows<4>(p, sm, pro, xin, ep_in, gamma, K, q_ld);  // K <= 8192 (mega_plan)
+    __syncwarp();  // the warp's bytes are read back by its own lanes only
 }
 
 // ---- one ternary GEMV phase (consumer side) ------------------------------------------------------
-// Ring position of a consumer warp / of the producer: slot index and phase parity, advanced chunk
-// by chunk (all parties walk the same chunk sequence).
+// Ring position of a consumer warp / of the producer: slot index and phase parity, advanced slot by slot
+// (all parties walk the same sequence: tile by tile, part by part).
 struct RingPos {
     uint32_t slot, par;
 };
@@ -317,151 +376,176 @@ __device__ __forceinline__ void ring_advance(RingPos& r, uint32_t n_slots) {
     }
 }
 
-// One task = 16 weight rows x 256 columns (1 KB of codes): 8 IMMAs over PRMT-decoded fragments.
-__device__ __forceinline__ void mega_task(const unsigned char* wr, int rowb, const int8_t* qk, bool tok, uint32_t lut,
-                                          int (&c)[4]) {
-    const uint4 wg = *reinterpret_cast<const uint4*>(wr);
-    const uint4 wh = *reinterpret_cast<const uint4*>(wr + 8 * rowb);
-    uint4 b[4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        b[j] = make_uint4(0, 0, 0, 0);
-        if (tok) b[j] = *reinterpret_cast<const uint4*>(qk + 16 * j);
+// lane (g, t): c[0] (row g, token 2t), c[1] (row g, 2t+1), c[2] (row g+8, 2t), c[3] (row g+8, 2t+1)
+__device__ __forceinline__ void mega_store_partial(int* rw, int i, int B, const int (&c0)[4], const int (&c1)[4]) {
+    const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+    if (2 * t < B) {
+        rw[(i * 16 + g) * B + 2 * t] = c0[0] + c1[0];
+        rw[(i * 16 + g + 8) * B + 2 * t] = c0[2] + c1[2];
+        if (2 * t + 1 < B) {
+            rw[(i * 16 + g) * B + 2 * t + 1] = c0[1] + c1[1];
+            rw[(i * 16 + g + 8) * B + 2 * t + 1] = c0[3] + c1[3];
+        }
     }
-    int c0[4] = {0, 0, 0, 0}, c1[4] = {0, 0, 0, 0};  // two independent accumulation chains
-    const uint32_t wgs[4] = {wg.x, wg.y, wg.z, wg.w};
-    const uint32_t whs[4] = {wh.x, wh.y, wh.z, wh.w};
+}
+
+// One tile (16 rows) x the warp's k-chunks out of a ring slot that is known to be full: ALL fragment loads first
+// (branch-free: a chunk beyond nc re-reads chunk 0 against a zero B fragment), the PREVIOUS tile's partial is stored
+// while they fly (its MMAs have long completed), then PRMT decode + IMMA on two accumulator chains. Fully unrolled
+// over MAXC on purpose: ~11 instructions per chunk, 1-3 KB of code; the rolled form measured 2 x slower (LDS latency
+// and loop overhead exposed in every chunk).
+template <int MAXC>
+__device__ __forceinline__ void mega_tile(const unsigned char* base, const uint2 (&b)[MAXC], int nc, uint32_t lut, int* rw, int i,
+                                          int B, bool have_prev, const int (&p0)[4], const int (&p1)[4], int (&c0)[4], int (&c1)[4]) {
+    uint32_t w[MAXC];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        const uint4 dg = decode16(wgs[j], lut);
-        const uint4 dh = decode16(whs[j], lut);
-        mma_s8_m16n8k32(c0, dg.x, dh.x, dg.y, dh.y, b[j].x, b[j].y);
-        mma_s8_m16n8k32(c1, dg.z, dh.z, dg.w, dh.w, b[j].z, b[j].w);
+    for (int c = 0; c < MAXC; ++c) w[c] = *reinterpret_cast<const uint32_t*>(base + (c < nc ? c : 0) * 128);
+    if (have_prev) mega_store_partial(rw, i - 1, B, p0, p1);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) c0[j] = c1[j] = 0;
+#pragma unroll
+    for (int c = 0; c < MAXC; ++c) {
+        const uint4 d = decode16(w[c], lut);
+        if (c & 1) mma_s8_m16n8k32(c1, d.x, d.y, d.z, d.w, b[c].x, b[c].y);
+        else mma_s8_m16n8k32(c0, d.x, d.y, d.z, d.w, b[c].x, b[c].y);
     }
+}
+
+// The warp's k-chunks of every tile of the CTA: B fragments in registers for the whole phase; the per-warp partial of
+// a tile goes to sm.red. A ring slot carries o.T consecutive tiles (one bulk copy, one full / empty barrier pair):
+// the mbarrier probe costs ~200 cycles even when the data is there, so it is paid once per slot, not per tile.
+template <int MAXC>
+__device__ __forceinline__ void mega_tiles(const MegaParams& p, const MegaSmem& sm, const MegaOp& o, int nloc, int kc0, int nc,
+                                           RingPos& rp, int& wi) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int g = lane >> 2, t = lane & 3, B = p.B;
+    const unsigned char* arow = sm.act + (g < B ? g : 0) * (o.K + 64) + 32 * kc0 + 8 * t;  // columns g >= B: ignored results
+    uint2 b[MAXC];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) c[i] = c0[i] + c1[i];
+    for (int c = 0; c < MAXC; ++c) {
+        b[c] = make_uint2(0u, 0u);
+        if (c < nc) b[c] = *reinterpret_cast<const uint2*>(arow + 32 * c);
+    }
+    const uint32_t NS = (uint32_t)p.n_slots, lut = p.lut;
+    const int tile_bytes = o.KC * 128;
+    RingPos r = rp;
+    int* rw = sm.red + warp * p.red_ld;
+    wtrace(p, wi, 3);
+    long long wcyc = 0;
+    int a0[4], a1[4], e0[4] = {0, 0, 0, 0}, e1[4] = {0, 0, 0, 0};
+    int j = 0;  // tile inside the current slot
+    const unsigned char* base = nullptr;
+    // enter the slot of tile i (hand the finished one back first)
+    auto enter = [&](int i) {
+        if (j == 0) {
+            if (i > 0) {
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&sm.empty[r.slot]);
+                ring_advance(r, NS);
+            }
+            MEGA_TRACE_ONLY(const long long tw0 = clock64();)
+            mbar_wait(&sm.full[r.slot], r.par);
+            MEGA_TRACE_ONLY(wcyc += clock64() - tw0;)
+            base = sm.ring + (size_t)r.slot * MEGA_SLOT_BYTES + (size_t)(kc0 * 32 + lane) * 4;
+        }
+    };
+    auto leave = [&]() {
+        base += tile_bytes;
+        if (++j == o.T) j = 0;
+    };
+#pragma unroll 1
+    for (int i = 0; i < nloc; i += 2) {  // two bodies per trip: the accumulator sets alternate without register moves
+        enter(i);
+        mega_tile<MAXC>(base, b, nc, lut, rw, i, B, i > 0, e0, e1, a0, a1);
+        leave();
+        wtrace(p, wi, 4);
+        if (i + 1 >= nloc) {
+            mega_store_partial(rw, i, B, a0, a1);
+            break;
+        }
+        enter(i + 1);
+        mega_tile<MAXC>(base, b, nc, lut, rw, i + 1, B, true, a0, a1, e0, e1);
+        leave();
+        wtrace(p, wi, 4);
+        if (i + 2 >= nloc) {
+            mega_store_partial(rw, i + 1, B, e0, e1);
+            break;
+        }
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&sm.empty[r.slot]);  // the last slot of the phase
+    ring_advance(r, NS);
+    wtrace_val(p, wi, 10, (unsigned long long)wcyc);
+    rp = r;
 }
 
 // epi: 0 store, 1 residual add (out may alias resid), 2 SwiGLU on interleaved (gate, up) rows
-__device__ __forceinline__ void mega_gemv_phase(const MegaParams& p, const MegaSmem& sm, int N, int K, int pro,
-                                             const uint2* xin, const float* gamma, int epi, uint2* out,
-                                             const uint2* resid, uint32_t ep_out, RingPos& rp, int& tcount, int& pi) {
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int g = lane >> 2, t = lane & 3;
+__device__ __forceinline__ void mega_gemv_phase(const MegaParams& p, const MegaSmem& sm, const MegaOp& o, int pro, const uint2* xin,
+                                             const float* gamma, int epi, uint2* out, const uint2* resid, uint32_t ep_res,
+                                             uint32_t ep_out, RingPos& rp, uint32_t& par, int& pi, int& wi) {
+    const int tid = threadIdx.x, warp = tid >> 5;
     prof_stamp(p, pi);  // phase start
-    const int G = gridDim.x, cta = blockIdx.x;
-    const int NT = (N + 15) >> 4, ns = K >> 8, nch = ns > MEGA_SLOT_STEPS ? 2 : 1;
-    const int split = nch == 2 ? (ns + 1) >> 1 : ns;  // chunk 0 = steps [0, split), chunk 1 = [split, ns)
-    const int q_ld = K + 64;
-    int first = cta - tcount;  // tcount < G
-    if (first < 0) first += G;
-    int nloc = 0;
-    for (int tt = first; tt < NT; tt += G) ++nloc;
-    const uint32_t NS = (uint32_t)p.n_slots;
-    for (int i = tid; i < nloc * 128; i += MEGA_CONS) sm.acc[i] = 0;
-    mega_prologue(p, sm, pro, xin, ep_out - 1u, gamma, K, q_ld);  // waits for the previous phase's output; ends with a consumer barrier
+    const PhaseGeom q = phase_geom(o, blockIdx.x);
+    if (q.nloc == 0) {  // no rows of this projection here: nothing to wait for, nothing in the ring
+        prof_stamp(p, pi);
+        prof_stamp(p, pi);
+        prof_stamp(p, pi);
+        return;
+    }
+    const int B = p.B, N = o.N, red_ld = p.red_ld;
+    const int kc0 = (warp * o.KC) / MEGA_NW, nc = ((warp + 1) * o.KC) / MEGA_NW - kc0;
+    // residual rows of this CTA: probed now, validated in the epilogue (one (row, token) per thread)
+    const int nout = q.nloc * 16 * B;
+    const int orow = q.t0 * 16 + tid / B, om = tid % B;   // output element of this thread (epi 0 / 1)
+    uint2 rprobe = make_uint2(0u, 0u);
+    if (epi == 1 && tid < nout) rprobe = ll_ld1(resid + (size_t)om * N + orow);
+    float sc[MEGA_MAXB];
+    wtrace(p, wi, 1);
+    mega_prologue(p, sm, pro, xin, ep_out - 1u, gamma, o.K, kc0, nc, sc, par, wi);
     prof_stamp(p, pi);  // prologue done
-    // residual rows of this CTA: fetched now, consumed in the epilogue (nloc * 16 <= MEGA_CONS: one row per thread).
-    // The old x[row] was validated by this CTA in an earlier prologue and has no writer before this phase's epilogue.
-    float rv[MEGA_MAXB];
-    if (epi == 1) {
-        const int row = (first + (tid >> 4) * G) * 16 + (tid & 15);
-#pragma unroll
-        for (int m = 0; m < MEGA_MAXB; ++m) {
-            rv[m] = 0.f;
-            if (m < p.B && tid < nloc * 16 && row < N) rv[m] = ld_cg_f32(reinterpret_cast<const float*>(resid + (size_t)m * N + row));
-        }
-    }
-
-    // tasks (local tile i, step s) are dealt round-robin to the 16 warps: q = i * ns + s = warp, warp + 16, ...
-    const bool tok = g < p.B;
-    const int8_t* qrow = reinterpret_cast<const int8_t*>(sm.act) + g * q_ld + 64 * t;
-    const uint32_t lut = p.lut;
-    const int nchunks = nloc * nch;
-    RingPos r = rp;
-    int ci = 0, i = 0, s = warp;
-    bool waited = false;
-    while (s >= ns) {
-        s -= ns;
-        ++i;
-    }
-    while (i < nloc) {
-        const int ch = s >= split ? 1 : 0;
-        const int ct = i * nch + ch;
-        while (ci < ct) {  // done with the chunks before this task's: hand their slots back
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&sm.empty[r.slot]);
-            ring_advance(r, NS);
-            ++ci;
-            waited = false;
-        }
-        if (!waited) {
-            mbar_wait(&sm.full[r.slot], r.par);
-            waited = true;
-        }
-        const int s0 = ch ? split : 0, cs = ch ? ns - split : split;
-        const int rowb = cs * 64;
-        const unsigned char* wr = sm.ring + (size_t)r.slot * MEGA_SLOT_BYTES + (size_t)g * rowb + (s - s0) * 64 + 16 * t;
-        int c[4];
-        mega_task(wr, rowb, qrow + s * 256, tok, lut, c);
-        // lane (g, t): c[0] (row g, token 2t), c[1] (row g, 2t+1), c[2] (row g+8, 2t), c[3] (row g+8, 2t+1)
-        int* a = sm.acc + i * 128;
-        if (2 * t < p.B) {
-            atomicAdd(a + g * 8 + 2 * t, c[0]);
-            atomicAdd(a + (g + 8) * 8 + 2 * t, c[2]);
-        }
-        if (2 * t + 1 < p.B) {
-            atomicAdd(a + g * 8 + 2 * t + 1, c[1]);
-            atomicAdd(a + (g + 8) * 8 + 2 * t + 1, c[3]);
-        }
-        s += MEGA_NW;
-        while (s >= ns) {
-            s -= ns;
-            ++i;
-        }
-    }
-    while (ci < nchunks) {
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&sm.empty[r.slot]);
-        ring_advance(r, NS);
-        ++ci;
-    }
-    rp = r;
+    // exact instances for the shapes that matter (2B-4T: 80 and 216 k-chunks over 15 warps = 6 and 15 each), generic otherwise
+    if (o.KC <= 6 * MEGA_NW) mega_tiles<6>(p, sm, o, q.nloc, kc0, nc, rp, wi);
+    else if (o.KC <= 10 * MEGA_NW) mega_tiles<10>(p, sm, o, q.nloc, kc0, nc, rp, wi);
+    else if (o.KC <= 15 * MEGA_NW) mega_tiles<15>(p, sm, o, q.nloc, kc0, nc, rp, wi);
+    else mega_tiles<MEGA_MAXC>(p, sm, o, q.nloc, kc0, nc, rp, wi);
+    wtrace(p, wi, 5);
     cons_sync();
+    wtrace(p, wi, 9);
     prof_stamp(p, pi);  // tiles done
-    // ---- epilogue ---------------------------------------------------------------------------
+    // ---- epilogue: sum the 15 per-warp partials, scale, residual / SwiGLU, publish ----------------
     if (epi == 2) {
         const int half = N >> 1;
-        for (int m = 0; m < p.B; ++m)
-        for (int rr = tid; rr < nloc * 8; rr += MEGA_CONS) {
-            const int ii = rr >> 3, j = rr & 7;
-            const int row = (first + ii * G) * 16 + 2 * j;
-            if (row + 1 < N) {
-                const float as = sm.sc_s[m];
-                const float v0 = __fmul_rn(as, (float)sm.acc[ii * 128 + (2 * j) * 8 + m]);
-                const float v1 = __fmul_rn(as, (float)sm.acc[ii * 128 + (2 * j + 1) * 8 + m]);
-                ll_store(out, (size_t)m * half + (row >> 1), __fmul_rn(v0 / (1.0f + expf(-v0)), v1), ep_out);
-            }
-        }
-    } else {
+        if (tid < q.nloc * 8 * B) {
+            const int m = tid % B, pr = tid / B;  // pair index inside the CTA's rows: rows 2 pr (gate), 2 pr + 1 (up)
+            int a0 = 0, a1 = 0;
 #pragma unroll
-        for (int m = 0; m < MEGA_MAXB; ++m) {
-            if (m >= p.B) break;
-            const int rr = tid;  // nloc <= MEGA_MAX_TILES = 16 tiles -> at most 256 rows per CTA
-            if (rr < nloc * 16) {
-                const int ii = rr >> 4, rw = rr & 15;
-                const int row = (first + ii * G) * 16 + rw;
-                if (row < N) {
-                    const float v = __fmul_rn(sm.sc_s[m], (float)sm.acc[ii * 128 + rw * 8 + m]);
-                    ll_store(out, (size_t)m * N + row, epi == 1 ? __fadd_rn(rv[m], v) : v, ep_out);
-                }
+            for (int w = 0; w < MEGA_NW; ++w) {
+                a0 += sm.red[w * red_ld + (2 * pr) * B + m];
+                a1 += sm.red[w * red_ld + (2 * pr + 1) * B + m];
             }
+            float as = sc[0];
+#pragma unroll
+            for (int j = 1; j < MEGA_MAXB; ++j) as = m == j ? sc[j] : as;
+            const float v0 = __fmul_rn(as, (float)a0), v1 = __fmul_rn(as, (float)a1);
+            ll_store(out, (size_t)m * half + q.t0 * 8 + pr, __fmul_rn(v0 / (1.0f + expf(-v0)), v1), ep_out);
         }
+    } else if (tid < nout) {
+        int a = 0;
+#pragma unroll
+        for (int w = 0; w < MEGA_NW; ++w) a += sm.red[w * red_ld + tid];
+        float as = sc[0];
+#pragma unroll
+        for (int j = 1; j < MEGA_MAXB; ++j) as = om == j ? sc[j] : as;
+        float v = __fmul_rn(as, (float)a);
+        if (epi == 1) {
+            const float rv = rprobe.y == ep_res ? __uint_as_float(rprobe.x) : ll_wait1(resid + (size_t)om * N + orow, ep_res);
+            v = __fadd_rn(rv, v);
+        }
+        ll_store(out, (size_t)om * N + orow, v, ep_out);
     }
-    tcount += NT;
-    while (tcount >= G) tcount -= G;
     prof_stamp(p, pi);  // epilogue done
-    cons_sync();  // no grid barrier follows: the next phase zeroes sm.acc, which slower warps may still be reading here
+    wtrace(p, wi, 6);
+    // no barrier here: sm.red / sm.act are next written after the next prologue's barrier(s)
 }
 
 // ---- RoPE + KV append + GQA decode attention for one (head, sequence); consumer threads only ---
@@ -806,7 +890,7 @@ __device__ __forceinline__ void mega_logits_rows(const MegaParams& p, const Mega
 __device__ __forceinline__ void mega_logits_phase(const MegaParams& p, const MegaSmem& sm, RingPos& rp, uint32_t ep_in) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int H = p.H, V = p.V, G = gridDim.x, cta = blockIdx.x;
-    float* xn = reinterpret_cast<float*>(sm.act);  // [B][H]
+    float* xn = sm.stage;  // [B][H] (the prologue staging buffer is idle here)
     // final RMSNorm (cpu::rms_norm) of every token row into shared memory
     for (int m = 0; m < p.B; ++m) {
         double ss = 0.0;
@@ -854,43 +938,34 @@ __device__ __forceinline__ void mega_logits_phase(const MegaParams& p, const Meg
 }
 
 // ---- the producer warp: every weight byte of the step, in consumption order ----------------------
+// One lane, one bulk copy per ring slot: a CTA's share of a projection is a contiguous byte range of the
+// fragment-major weight copy.
 __device__ __forceinline__ void mega_producer(const MegaParams& p, const MegaSmem& sm) {
-    const int lane = threadIdx.x & 31;
+    if ((threadIdx.x & 31) != 0) return;
     const int G = gridDim.x, cta = blockIdx.x;
     uint32_t n = 0;
-    int tcount = 0;
     const uint32_t NS = (uint32_t)p.n_slots;
+    MEGA_TRACE_ONLY(long long pw = 0; int pfree = 0; int pwi = 0;)
     for (int l = 0; l < p.L; ++l) {
         const MegaLayer& L = sm.layers[l];
         for (int op = 0; op < 4; ++op) {
             const uint8_t* w = op == 0 ? L.wqkv : (op == 1 ? L.wo : (op == 2 ? L.wgu : L.wdown));
-            const int N = op == 0 ? (p.NH + 2 * p.NKV) * p.D : (op == 1 ? p.H : (op == 2 ? 2 * p.F : p.H));
-            const int K = op == 1 ? p.NH * p.D : (op == 3 ? p.F : p.H);
-            const int NT = (N + 15) >> 4, ns = K >> 8, nch = (ns + MEGA_SLOT_STEPS - 1) / MEGA_SLOT_STEPS;
-            const size_t stride = (size_t)K >> 2;
-            for (int tile = (cta - tcount + G) % G; tile < NT; tile += G) {
-                const int nr = min(16, N - tile * 16);
-                for (int ch = 0; ch < nch; ++ch, ++n) {
-                    int s0, cs;
-                    chunk_range(ns, nch, ch, s0, cs);
-                    const uint32_t slot = n % NS;
-                    unsigned char* dst = sm.ring + (size_t)slot * MEGA_SLOT_BYTES;
-                    if (lane == 0) {
-                        if (n >= NS) mbar_wait_backoff(&sm.empty[slot], ((n / NS) - 1u) & 1u);
-                        mbar_expect_tx(&sm.full[slot], (uint32_t)(nr * cs * 64));
-                    }
-                    __syncwarp();
-                    if (nch == 1) {
-                        if (lane == 0) bulk_g2s(dst, w + (size_t)tile * 16 * stride, (uint32_t)(nr * cs * 64), &sm.full[slot]);
-                    } else if (lane < nr) {
-                        bulk_g2s(dst + (size_t)lane * cs * 64, w + ((size_t)tile * 16 + lane) * stride + (size_t)s0 * 64,
-                                 (uint32_t)(cs * 64), &sm.full[slot]);
-                    }
-                }
+            const MegaOp& o = p.op[op];
+            const PhaseGeom q = phase_geom(o, cta);
+            const size_t tile_bytes = (size_t)o.KC * 128;
+            for (int i = 0; i < q.nloc; i += o.T, ++n) {  // one slot = up to o.T consecutive tiles = one bulk copy
+                const uint32_t slot = n % NS, bytes = (uint32_t)(min(o.T, q.nloc - i) * tile_bytes);
+                MEGA_TRACE_ONLY(const long long tw0 = clock64(); const bool free_now = n < NS || mbar_try_wait(&sm.empty[slot], ((n / NS) - 1u) & 1u);)
+                if (n >= NS) mbar_wait_backoff(&sm.empty[slot], ((n / NS) - 1u) & 1u);
+                MEGA_TRACE_ONLY(pw += clock64() - tw0; pfree += free_now ? 1 : 0;)
+                mbar_expect_tx(&sm.full[slot], bytes);
+                bulk_g2s(sm.ring + (size_t)slot * MEGA_SLOT_BYTES, w + (size_t)(q.t0 + i) * tile_bytes, bytes, &sm.full[slot]);
             }
-            tcount = (tcount + NT) % G;
         }
     }
+    // trace: slots of the ternary phases, how many were free the moment the producer asked (= the ring had drained: the
+    // consumers were waiting on HBM), and the cycles it slept waiting for a slot (= the ring was full: good)
+    MEGA_TRACE_ONLY(wtrace_val(p, pwi, 11, n); wtrace_val(p, pwi, 12, (unsigned long long)pfree); wtrace_val(p, pwi, 13, (unsigned long long)pw);)
     if (p.mode == 0) {
         const int rpc = (p.V + G - 1) / G;
         const int r0 = min(p.V, cta * rpc), r1 = min(p.V, r0 + rpc);
@@ -898,12 +973,10 @@ __device__ __forceinline__ void mega_producer(const MegaParams& p, const MegaSme
         for (int rr = r0; rr < r1; rr += RL, ++n) {
             const int nr = min(RL, r1 - rr);
             const uint32_t slot = n % NS;
-            if (lane == 0) {
-                if (n >= NS) mbar_wait_backoff(&sm.empty[slot], ((n / NS) - 1u) & 1u);
-                const uint32_t bytes = (uint32_t)nr * (uint32_t)p.H * 2u;
-                mbar_expect_tx(&sm.full[slot], bytes);
-                bulk_g2s(sm.ring + (size_t)slot * MEGA_SLOT_BYTES, p.emb + (size_t)rr * p.H, bytes, &sm.full[slot]);
-            }
+            if (n >= NS) mbar_wait_backoff(&sm.empty[slot], ((n / NS) - 1u) & 1u);
+            const uint32_t bytes = (uint32_t)nr * (uint32_t)p.H * 2u;
+            mbar_expect_tx(&sm.full[slot], bytes);
+            bulk_g2s(sm.ring + (size_t)slot * MEGA_SLOT_BYTES, p.emb + (size_t)rr * p.H, bytes, &sm.full[slot]);
         }
     }
 }
@@ -913,36 +986,22 @@ __global__ void __launch_bounds__(MEGA_THREADS, 1) decode_mega_kernel(const __gr
     const int tid = threadIdx.x, warp = tid >> 5;
     const int G = gridDim.x, cta = blockIdx.x;
     // ---- shared memory carve-up (must match mega_smem_bytes) -----------------------------------
+    // fixed-size pieces and the ring sit at compile-time offsets; red / act / attn follow the ring at offsets the
+    // host computed (kernel parameters: rematerialised from the constant bank instead of living in registers)
     MegaSmem sm;
-    size_t off = 0;
-    sm.full = reinterpret_cast<uint64_t*>(smem_raw + off);
-    off += MEGA_MAX_SLOTS * 8;
-    sm.empty = reinterpret_cast<uint64_t*>(smem_raw + off);
-    off += MEGA_MAX_SLOTS * 8;
-    sm.shd = reinterpret_cast<double*>(smem_raw + off);
-    off += 32 * 8;
-    sm.shf = reinterpret_cast<float*>(smem_raw + off);
-    off += 32 * 4;
-    sm.sc_s = reinterpret_cast<float*>(smem_raw + off);
-    off += 32;
-    sm.attw = reinterpret_cast<int*>(smem_raw + off);
-    off += 32;
-    sm.bestv = reinterpret_cast<float*>(smem_raw + off);
-    off += MEGA_NW * MEGA_MAXB * 4;
-    sm.besti = reinterpret_cast<int*>(smem_raw + off);
-    off += MEGA_NW * MEGA_MAXB * 4;
-    sm.layers = reinterpret_cast<MegaLayer*>(smem_raw + off);
-    off += (size_t)MEGA_MAX_LAYERS * sizeof(MegaLayer);
-    sm.acc = reinterpret_cast<int*>(smem_raw + off);
-    off += MEGA_MAX_TILES * 128 * 4;
-    off = (off + 127) & ~(size_t)127;
-    sm.act = smem_raw + off;
-    off += (size_t)p.act_bytes;
-    off = (off + 127) & ~(size_t)127;
-    sm.attn = reinterpret_cast<float*>(smem_raw + off);
-    off += (size_t)p.attn_floats * 4;
-    off = (off + 127) & ~(size_t)127;
-    sm.ring = smem_raw + off;
+    sm.full = reinterpret_cast<uint64_t*>(smem_raw + MEGA_OFF_FULL);
+    sm.empty = reinterpret_cast<uint64_t*>(smem_raw + MEGA_OFF_EMPTY);
+    sm.shd = reinterpret_cast<double*>(smem_raw + MEGA_OFF_SHD);
+    sm.shf = reinterpret_cast<float*>(smem_raw + MEGA_OFF_SHF);
+    sm.attw = reinterpret_cast<int*>(smem_raw + MEGA_OFF_ATTW);
+    sm.bestv = reinterpret_cast<float*>(smem_raw + MEGA_OFF_BESTV);
+    sm.besti = reinterpret_cast<int*>(smem_raw + MEGA_OFF_BESTI);
+    sm.layers = reinterpret_cast<MegaLayer*>(smem_raw + MEGA_OFF_LAYERS);
+    sm.ring = smem_raw + MEGA_OFF_RING;
+    sm.red = reinterpret_cast<int*>(smem_raw + p.off_red);
+    sm.act = smem_raw + p.off_act;
+    sm.attn = reinterpret_cast<float*>(smem_raw + p.off_attn);
+    sm.stage = reinterpret_cast<float*>(smem_raw + p.off_stage);
 
     if (tid == 0) {
         for (int s = 0; s < p.n_slots; ++s) {
@@ -966,7 +1025,8 @@ __global__ void __launch_bounds__(MEGA_THREADS, 1) decode_mega_kernel(const __gr
     unsigned* ctr = p.bar + p.parity * (MEGA_BAR_CTRS * MEGA_BAR_STRIDE);
     unsigned target = 0;
     RingPos rp{0u, 0u};
-    int tcount = 0, pi = 0;
+    int pi = 0, wi = 0;
+    uint32_t par = 0;
     const int H = p.H, F = p.F, D = p.D, NH = p.NH, NKV = p.NKV, B = p.B;
     const int QD = NH * D, QKV = (NH + 2 * NKV) * D;
     const bool full = p.mode == 0;  // mode 1 = roofline leg: the 4L ternary GEMVs only, fixed int8 inputs, no barriers
@@ -1022,14 +1082,14 @@ __global__ void __launch_bounds__(MEGA_THREADS, 1) decode_mega_kernel(const __gr
                 if (p.barriers) grid_sync(ctr, target, G);
                 continue;
             }
-            const int N = op == 0 ? QKV : (op == 3 ? 2 * F : H);
-            const int K = op == 2 ? QD : (op == 4 ? F : H);
+            const int opi = op == 0 ? 0 : op - 1;  // index into p.op: qkv, o, gate/up, down
             const int pro = !full ? 0 : ((op == 0 || op == 3) ? 2 : 1);
             const uint2* xin = op == 2 ? p.att : (op == 4 ? p.gu : p.x);
             const float* gamma = op == 0 ? L.attn_norm : L.ffn_norm;
             const int epi = op == 3 ? 2 : ((full && (op == 2 || op == 4)) ? 1 : 0);
             uint2* out = op == 0 ? p.qkv : (op == 3 ? p.gu : p.x);
-            mega_gemv_phase(p, sm, N, K, pro, xin, gamma, epi, out, p.x, ep, rp, tcount, pi);
+            const uint32_t ep_res = op == 2 ? ep - 3u : ep - 2u;  // x was last written by the previous down phase (or the embedding) / by this layer's o phase
+            mega_gemv_phase(p, sm, p.op[opi], pro, xin, gamma, epi, out, p.x, ep_res, ep, rp, par, pi, wi);
             if (full) {
                 // what the next phase touches first and the weight stream has pushed out of L2 since the last step:
                 // the miss overlaps the wait for the other CTAs' outputs
@@ -1095,42 +1155,85 @@ __global__ void __launch_bounds__(MEGA_THREADS, 1) decode_mega_kernel(const __gr
 // ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
-static size_t mega_fixed_smem(int act_bytes, int attn_floats) {
-    size_t off = MEGA_MAX_SLOTS * 16 + 32 * 8 + 32 * 4 + 32 + 32 + 2 * MEGA_NW * MEGA_MAXB * 4 +
-                 (size_t)MEGA_MAX_LAYERS * sizeof(MegaLayer) + MEGA_MAX_TILES * 128 * 4;
-    off = (off + 127) & ~(size_t)127;
-    off += (size_t)act_bytes;
-    off = (off + 127) & ~(size_t)127;
-    off += (size_t)attn_floats * 4;
-    off = (off + 127) & ~(size_t)127;
-    return off;
-}
-
-// Fills the shape-derived fields of `p` (n_slots, act_bytes, attn_floats) and returns the dynamic
+// Fills the shape-derived fields of `p` (n_slots, act_bytes, attn_floats, red_ld) and returns the dynamic
 // shared memory the launch needs, or 0 when the shape is not covered by this kernel.
 size_t mega_plan(MegaParams* p, int num_sms) {
-    const int QD = p->NH * p->D;
+    const int QD = p->NH * p->D, QKV = (p->NH + 2 * p->NKV) * p->D;
     if (p->B < 1 || p->B > MEGA_MAXB || p->L > MEGA_MAX_LAYERS) return 0;
     if (p->NH * p->B > num_sms) return 0;                        // one attention work item per CTA
-    if (p->H % 256 || p->F % 256 || QD % 256) return 0;          // whole 256-column steps, no tails
-    if (p->H > 16 * MEGA_CONS || p->F > 16 * MEGA_CONS || QD > 16 * MEGA_CONS) return 0;  // one prologue pass per row (NV = 4)
-    if (p->D % 32 || p->D > 256 || MEGA_CONS % (p->D / 4)) return 0;
-    if (p->H * 2 > MEGA_SLOT_BYTES) return 0;                    // one LM-head row per slot at least
-    if (((p->NH + 2 * p->NKV) * p->D) % 2 || (2 * p->F) % 16) return 0;
+    if (p->H % 32 || p->F % 32 || QD % 32) return 0;             // whole k-chunks
     const int kmax = p->H > p->F ? (p->H > QD ? p->H : QD) : (p->F > QD ? p->F : QD);
-    const int tiles_max = ((2 * p->F + 15) / 16 + num_sms - 1) / num_sms + 1;
-    if (tiles_max > MEGA_MAX_TILES) return 0;
-    int act = p->B * (kmax + 64);
-    if (p->B * p->H * 4 > act) act = p->B * p->H * 4;
-    p->act_bytes = (act + 15) & ~15;
+    if (kmax > 32 * MEGA_MAXC * MEGA_NW) return 0;               // k-chunks per warp (register arrays)
+    if (kmax / 32 > MEGA_SLOT_KC) return 0;                      // a 16-row tile fits one ring slot
+    if (QKV % 16 || p->H % 16 || (2 * p->F) % 16) return 0;      // whole 16-row tiles
+    if (p->D % 32 || p->D > 256 || MEGA_CONS % (p->D / 4)) return 0;
+    if (p->H * 2 > MEGA_SLOT_BYTES || (p->H * 2) % 16) return 0; // one LM-head row per slot at least
+    const int Ns[4] = {QKV, p->H, 2 * p->F, p->H}, Ks[4] = {p->H, QD, p->H, p->F};
+    int tiles_max = 0;
+    for (int i = 0; i < 4; ++i) {
+        MegaOp& o = p->op[i];
+        o.N = Ns[i];
+        o.K = Ks[i];
+        o.KC = Ks[i] / 32;
+        o.T = MEGA_SLOT_KC / o.KC;  // >= 1: kmax <= 32 * MEGA_SLOT_KC (checked above)
+        const int NT = Ns[i] / 16;
+        o.tq = NT / num_sms;
+        o.tr = NT % num_sms;
+        if (o.tq + (o.tr ? 1 : 0) > tiles_max) tiles_max = o.tq + (o.tr ? 1 : 0);
+    }
+    if (tiles_max * 16 * p->B > MEGA_CONS) return 0;             // epilogue: one output element per consumer thread
+    p->red_ld = tiles_max * 16 * p->B;
+    p->act_bytes = (p->B * (kmax + 64) + 15) & ~15;
     p->attn_floats = ((p->max_ctx + 3) & ~3) + MEGA_CONS * 4 + 3 * 256 + 16;
-    const size_t fixed = mega_fixed_smem(p->act_bytes, p->attn_floats);
-    const size_t cap = 227 * 1024;
-    if (fixed + 3 * (size_t)MEGA_SLOT_BYTES > cap) return 0;
-    int slots = (int)((cap - fixed) / MEGA_SLOT_BYTES);
+    // the prologue staging buffer (values [kmax] | norm weights [H]; the LM head parks its normalised rows [B][H] there)
+    // and the attention scratch are never live together: one region
+    int stage_floats = kmax > 2 * p->H ? kmax : 2 * p->H;
+    if (p->B * p->H > stage_floats) stage_floats = p->B * p->H;
+    const size_t red_b = ((size_t)MEGA_NW * p->red_ld * 4 + 127) & ~(size_t)127, act_b = ((size_t)p->act_bytes + 127) & ~(size_t)127,
+                 attn_b = ((size_t)p->attn_floats * 4 + 127) & ~(size_t)127, stage_b = ((size_t)stage_floats * 4 + 127) & ~(size_t)127;
+    const size_t shared_b = attn_b > stage_b ? attn_b : stage_b;
+    const size_t cap = 227 * 1024, rest = red_b + act_b + shared_b;
+    if ((size_t)MEGA_OFF_RING + rest + 3 * (size_t)MEGA_SLOT_BYTES > cap) return 0;
+    int slots = (int)((cap - MEGA_OFF_RING - rest) / MEGA_SLOT_BYTES);
     if (slots > MEGA_MAX_SLOTS) slots = MEGA_MAX_SLOTS;
     p->n_slots = slots;
-    return fixed + (size_t)slots * MEGA_SLOT_BYTES;
+    p->off_red = MEGA_OFF_RING + slots * MEGA_SLOT_BYTES;  // MEGA_SLOT_BYTES is a multiple of 128
+    p->off_act = p->off_red + (int)red_b;
+    p->off_attn = p->off_act + (int)act_b;
+    p->off_stage = p->off_attn;
+    return (size_t)p->off_attn + shared_b;
+}
+
+// ---- fragment-major weight copy ----------------------------------------------------------------------
+// in: device-layout code plane [N, K/4] (common.cuh: sixteen codes per word, slot k of a word at code_bitpos(k));
+// out: [N/16 tiles][K/32 k-chunks][32 lanes] words; the word of lane (g, t) carries, in slot order,
+//   a0 = row g, k 4t..4t+3 | a1 = row g+8, same k | a2 = row g, k 16+4t.. | a3 = row g+8, k 16+4t..
+// of its tile and k-chunk, so that decode16() returns the A fragment of mma.sync.m16n8k32 as it stands.
+__global__ void mega_repack_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int N, int K) {
+    const size_t total = (size_t)N * K / 16;
+    const int KC = K >> 5, wpr = K >> 4;
+    for (size_t o = (size_t)blockIdx.x * blockDim.x + threadIdx.x; o < total; o += (size_t)gridDim.x * blockDim.x) {
+        const int lane = (int)(o & 31);
+        const size_t tk = o >> 5;
+        const int kc = (int)(tk % KC);
+        const size_t tile = tk / KC;
+        const int g = lane >> 2, t = lane & 3;
+        uint32_t w = 0;
+#pragma unroll
+        for (int s = 0; s < 16; ++s) {
+            const int qd = s >> 2, i = s & 3;
+            const size_t row = tile * 16 + g + ((qd & 1) ? 8 : 0);
+            const int k = 32 * kc + ((qd & 2) ? 16 : 0) + 4 * t + i;
+            const uint32_t src = in[row * wpr + (k >> 4)];
+            w |= code_of(src, k & 15) << code_bitpos(s);
+        }
+        out[o] = w;
+    }
+}
+int mega_repack_weight(const uint8_t* codes, int N, int K, uint8_t* out, cudaStream_t st) {
+    mega_repack_kernel<<<1024, 256, 0, st>>>(reinterpret_cast<const uint32_t*>(codes), reinterpret_cast<uint32_t*>(out), N, K);
+    B200_LAUNCH_CHECK("mega_repack_kernel");
+    return 0;
 }
 
 int launch_decode_mega(const MegaParams& p, size_t smem, int num_sms, cudaStream_t st) {

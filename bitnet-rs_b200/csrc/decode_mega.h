@@ -6,11 +6,19 @@
 namespace b200 {
 
 struct MegaLayer {
-    const uint8_t *wqkv, *wo, *wgu, *wdown;  // device-layout code planes [N, K/4]
+    const uint8_t *wqkv, *wo, *wgu, *wdown;  // fragment-major code planes [N/16][K/32][32 lanes] words (mega_repack_weight)
     const float *attn_norm, *ffn_norm;
 };
 
+// one ternary projection of a layer (qkv, o, gate/up, down), shape-derived constants filled by mega_plan
+struct MegaOp {
+    int N, K, KC;      // rows, columns, k-chunks (K / 32)
+    int T;             // consecutive 16-row tiles per ring slot (one bulk copy, one barrier pair)
+    int tq, tr;        // tiles per CTA: the first tr CTAs own tq + 1 contiguous tiles, the others tq
+};
+
 struct MegaParams {
+    MegaOp op[4];
     const MegaLayer* layers;
     const __half* emb;
     const float *final_norm, *rope_cos, *rope_sin;
@@ -33,11 +41,15 @@ struct MegaParams {
     int prefetch;            // 1 = L2 prefetches inside the grid barriers (diagnostics knob BITNET_B200_MEGA_NOPF)
     int mode;                // 0 = full decode step; 1 = the 4L ternary GEMVs only, no dependencies
     int n_slots, act_bytes, attn_floats;
-    unsigned long long* prof;  // optional [16384] globaltimer stamps of CTA 0 (diagnostics), or nullptr
+    int off_red, off_act, off_attn, off_stage;  // shared-memory offsets of the shape-dependent pieces (mega_plan)
+    int red_ld;              // ints per warp in the partial-sum buffer: (tiles per CTA at most) * 16 * B
+    unsigned long long* prof;  // optional diagnostics buffer (decode_mega.cu: prof_stamp / wtrace), or nullptr
+    int prof_cta;              // CTA whose warps record the finer trace
 };
 
 // decode_mega.cu
 size_t mega_plan(MegaParams* p, int num_sms);  // 0 = shape not covered
+int mega_repack_weight(const uint8_t* codes, int N, int K, uint8_t* out, cudaStream_t st);
 int launch_decode_mega(const MegaParams& p, size_t smem, int num_sms, cudaStream_t st);
 
 }  // namespace b200

@@ -4,7 +4,8 @@ import os
 import subprocess
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libbitnet_b200.so")
+# BITNET_B200_LIB: load another build of the same library (diagnostics: the `make trace` build)
+LIB_PATH = os.environ.get("BITNET_B200_LIB") or os.path.join(HERE, "libbitnet_b200.so")
 CSRC = os.path.join(HERE, "csrc")
 
 # every symbol include/bitnet_b200.h declares (tests check the library exports all of them)
