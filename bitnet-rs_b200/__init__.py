@@ -16,8 +16,13 @@ from .provider import (  # noqa: F401
     KernelManager,
     KernelProvider,
     QuantizationType,
+    QuantizedLinear,
     gemv_qk256,
     i2s_matmul_f32,
+    qk256_gemv,
+    qk256_gemv_scalar,
+    quantize_input_i2s,
+    unpack_2bit_values,
 )
 from .device import (  # noqa: F401
     EPI_RESIDUAL,

@@ -41,6 +41,7 @@ int launch_actquant(const bitnet_b200_ctx*, const float*, const float*, float, i
                     float*, float*, int mode);
 int launch_quantize_weights(cudaStream_t, const float*, int, uint8_t*, int, float*, int);
 int launch_matmul_u8(cudaStream_t, const int8_t*, const uint8_t*, float*, int, int, int);
+int launch_qk256_legacy(cudaStream_t, const uint8_t*, const float*, const float*, float*, int, int);
 int launch_i2s_matmul_f32(cudaStream_t, const float*, const uint8_t*, const float*, float*, int,
                           int, int, int);
 int launch_split_bitnet32(cudaStream_t, const uint8_t*, size_t, uint8_t*, __half*, float*, int);
@@ -335,6 +336,28 @@ int bitnet_b200_weight_create(bitnet_b200_ctx* ctx, const void* host_bytes, size
             B200_CUDA(cudaMalloc(&w->scales, nblk * sizeof(__half)));
             B200_CUDA(cudaMalloc(&w->scales_f32, nblk * sizeof(float)));
             B200_CUDA(cudaMemcpyAsync(staging.p, host_bytes, nbytes, cudaMemcpyHostToDevice, ctx->stream));
+            {   // host scan of the f16 scale bits (the bytes are here anyway): see f16_scales_exact
+                const uint8_t* hb = static_cast<const uint8_t*>(host_bytes);
+                int amax = 0;
+                for (int i = 0; i < 4; ++i) amax = std::max(amax, std::abs((int)w->lut[i]));
+                bool exact = true;
+                for (size_t b = 0; b < nblk && exact; ++b) {
+                    const uint16_t bits = (uint16_t)(hb[b * 10 + 8] | (hb[b * 10 + 9] << 8));
+                    const uint16_t mag = bits & 0x7fffu;  // f16 magnitudes order like their bit patterns
+                    if (scale_policy == BITNET_B200_SCALE_ABS_CLAMP) {
+                        // s = clamp(|h|, 1e-3, 1e3): exact in f16 iff unclamped (1e-3 is not an f16; 1e3 = 0x63D0 is)
+                        if (mag < 0x1419u /* first f16 >= 1e-3 */ || mag > 0x63D0u /* 1000 */) exact = false;
+                    } else {
+                        if (mag >= 0x7C00u) exact = false;  // inf / NaN
+                        else {                               // |s| * max|LUT| must stay finite in f16
+                            const int e = mag >> 10, f = mag & 0x3ff;
+                            const float hv = e ? ldexpf(1.0f + f / 1024.0f, e - 15) : ldexpf(f / 1024.0f, -14);
+                            if (hv * (float)amax > 65504.0f) exact = false;
+                        }
+                    }
+                }
+                w->f16_scales_exact = exact;
+            }
             if (launch_split_bitnet32(ctx->stream, staging.as<uint8_t>(), nblk, w->codes, w->scales,
                                       w->scales_f32, scale_policy == BITNET_B200_SCALE_ABS_CLAMP))
                 return -1;
@@ -516,6 +539,55 @@ int bitnet_b200_i2s_matmul_f32(const float* act, const uint8_t* packed, const fl
         return fail(e.what());
     } catch (...) {
         return fail("i2s_matmul: unknown error");
+    }
+}
+
+// ---- legacy QK256 entry points (crates/bitnet-quantization/src/qk256_dispatch.rs) ----------------
+static int legacy_check(size_t out_len, size_t rows, size_t cols, size_t packed_len, size_t scales_len, size_t act_len) {
+    // the reference asserts (panics) with these messages, qk256_dispatch.rs:28-38; here they are errors
+    if (out_len != rows) return fail("Output length mismatch");
+    if (act_len != cols) return fail("Activation length mismatch");
+    if (cols % 256) return fail("Cols must be multiple of QK256=256");
+    if (packed_len != rows * cols / 4) return fail("Packed weight size mismatch");
+    if (scales_len != rows * (cols / 256)) return fail("Scales length mismatch");
+    return 0;
+}
+
+int bitnet_b200_qk256_gemv(float* output, size_t out_len, size_t rows, size_t cols, const uint8_t* packed,
+                           size_t packed_len, const float* scales, size_t scales_len, const float* activations,
+                           size_t act_len) {
+    if (legacy_check(out_len, rows, cols, packed_len, scales_len, act_len)) return -1;
+    (void)scales;  // validated, not consumed: the GGML no-scale format (qk256_dispatch.rs:14-16)
+    return bitnet_b200_gemv_qk256(packed, packed_len, activations, act_len, output, out_len, rows, cols, cols / 256 * 64);
+}
+
+int bitnet_b200_qk256_gemv_scalar(float* output, size_t out_len, size_t rows, size_t cols, const uint8_t* packed,
+                                  size_t packed_len, const float* scales, size_t scales_len, const float* activations,
+                                  size_t act_len) {
+    try {
+        if (legacy_check(out_len, rows, cols, packed_len, scales_len, act_len)) return -1;
+        if (rows == 0) return 0;
+        if (!output || !packed || !scales || !activations) return fail("qk256_gemv_scalar: NULL pointer");
+        if (rows > 0x7fffffffu || cols / 256 > 0x7fffffffu) return fail("qk256_gemv_scalar: dimensions too large");
+        int dev;
+        if (need_device(&dev)) return -1;
+        StreamGuard sg;
+        if (sg.create()) return -1;
+        DevBuf dw, ds, dx, dy;
+        if (dw.alloc(packed_len) || ds.alloc(scales_len * 4) || dx.alloc(cols * 4) || dy.alloc(rows * 4)) return -1;
+        B200_CUDA(cudaMemcpyAsync(dw.p, packed, packed_len, cudaMemcpyHostToDevice, sg.s));
+        B200_CUDA(cudaMemcpyAsync(ds.p, scales, scales_len * 4, cudaMemcpyHostToDevice, sg.s));
+        B200_CUDA(cudaMemcpyAsync(dx.p, activations, cols * 4, cudaMemcpyHostToDevice, sg.s));
+        if (launch_qk256_legacy(sg.s, dw.as<uint8_t>(), ds.as<float>(), dx.as<float>(), dy.as<float>(), (int)rows,
+                                (int)(cols / 256)))
+            return -1;
+        B200_CUDA(cudaMemcpyAsync(output, dy.p, rows * 4, cudaMemcpyDeviceToHost, sg.s));
+        B200_CUDA(cudaStreamSynchronize(sg.s));
+        return 0;
+    } catch (const std::exception& e) {
+        return fail(e.what());
+    } catch (...) {
+        return fail("qk256_gemv_scalar: unknown error");
     }
 }
 

@@ -64,6 +64,10 @@ struct bitnet_b200_weight {
     uint32_t lut_word = 0;      // 4 int8 LUT entries, entry c in byte c
     int8_t lut[4] = {-2, -1, 1, 2};
     int scale_policy = 0;
+    // BitNet32-F16: every policy-applied block scale is exactly representable in f16 and |s| * max|LUT| stays finite
+    // in f16 -- the condition under which the tcgen05 kind::f16 GEMM (which folds s into f16 weights) computes the
+    // same products as the f32-scale GEMV (gemm_f16_tcgen05.cu); otherwise M >= 9 loops the GEMV.
+    bool f16_scales_exact = true;
 };
 
 // ---- device helpers ---------------------------------------------------------------------

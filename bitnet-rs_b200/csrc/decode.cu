@@ -272,6 +272,7 @@ struct bitnet_b200_model {
     uint64_t launches_per_step = 0;
     bool have_emb = false, have_rope = false;
     int layers_set = 0;
+    int host_pos = 0;  // host mirror of the device-side position: zeroed by reset, advanced per launched step
 };
 
 static int dmalloc(void** p, size_t n) {
@@ -565,6 +566,15 @@ static int mega_launch(bitnet_b200_model* m, int mode) {
 // one decode step on the context's stream: the persistent kernel, or a replay of the step graph
 static int ensure_graph(bitnet_b200_model* m);
 static int step_launch(bitnet_b200_model* m) {
+    // Context-length guard: the position lives on the device and every step appends one K/V row at it. Beyond
+    // max_ctx the kernels would write past the cache, read the RoPE tables out of bounds and overflow the score array.
+    if (m->host_pos >= m->cfg.max_ctx) {
+        char buf[128];
+        snprintf(buf, sizeof buf, "model_decode: context full (position %d, max_ctx %d): call model_reset", m->host_pos,
+                 m->cfg.max_ctx);
+        return fail(buf);
+    }
+    ++m->host_pos;
     if (mega_setup(m)) return -1;
     if (m->mega == 1) return mega_launch(m, 0);
     if (ensure_graph(m)) return -1;
@@ -754,6 +764,7 @@ int bitnet_b200_model_set_rope(bitnet_b200_model* m, const float* cos_t, const f
 int bitnet_b200_model_reset(bitnet_b200_model* m) {
     if (!m) return fail("model_reset: NULL argument");
     B200_CUDA(cudaMemsetAsync(m->pos, 0, 4, m->ctx->stream));
+    m->host_pos = 0;
     return 0;
 }
 
@@ -788,6 +799,12 @@ int bitnet_b200_model_decode(bitnet_b200_model* m, const int32_t* tokens, int32_
 // or model_set_tokens()).
 int bitnet_b200_model_decode_device(bitnet_b200_model* m, int n_steps) {
     if (!m || n_steps < 0) return fail("model_decode_device: bad argument");
+    if (m->host_pos + n_steps > m->cfg.max_ctx) {  // nothing is launched when the request does not fit
+        char buf[160];
+        snprintf(buf, sizeof buf, "model_decode_device: %d steps from position %d exceed max_ctx %d", n_steps, m->host_pos,
+                 m->cfg.max_ctx);
+        return fail(buf);
+    }
     B200_CUDA(cudaSetDevice(m->ctx->device));
     for (int i = 0; i < n_steps; ++i)
         if (step_launch(m)) return -1;
@@ -797,7 +814,10 @@ int bitnet_b200_model_decode_device(bitnet_b200_model* m, int n_steps) {
 int bitnet_b200_model_set_tokens(bitnet_b200_model* m, const int32_t* tokens) {
     if (!m || !tokens) return fail("model_set_tokens: NULL argument");
     const size_t B = (size_t)m->cfg.batch;
-    for (size_t b = 0; b < B; ++b) m->tok_host[b] = tokens[b];
+    for (size_t b = 0; b < B; ++b) {
+        if (tokens[b] < 0 || tokens[b] >= m->cfg.vocab) return fail("model_set_tokens: token id out of range");
+        m->tok_host[b] = tokens[b];
+    }
     B200_CUDA(cudaMemcpyAsync(m->tokens, m->tok_host, B * 4, cudaMemcpyHostToDevice, m->ctx->stream));
     B200_CUDA(cudaStreamSynchronize(m->ctx->stream));
     return 0;

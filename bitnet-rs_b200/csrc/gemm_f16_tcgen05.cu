@@ -339,7 +339,7 @@ bool gemm_f16_supported(const bitnet_b200_weight* w, int M) {
     static const bool off = getenv("BITNET_B200_NO_GEMM") != nullptr;
     if (off) return false;
     return w->layout == BITNET_B200_LAYOUT_BITNET32_F16 && M >= 9 && w->cols % H_BKE == 0 &&
-           w->code_stride == w->cols / 4 && w->scales_f32 != nullptr;
+           w->code_stride == w->cols / 4 && w->scales_f32 != nullptr && w->f16_scales_exact;
 }
 
 int launch_gemm_f16(const bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, const int8_t* q, const float* act_scale,

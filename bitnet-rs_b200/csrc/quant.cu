@@ -396,6 +396,43 @@ int launch_i2s_matmul_f32(cudaStream_t st, const float* act, const uint8_t* pack
 }
 
 // ---------------------------------------------------------------------------------------
+// Legacy bench-only kernel qk256_gemv_scalar (crates/bitnet-quantization/src/qk256_dispatch.rs:45-99):
+// map D {-1, 0, +1, -1}, one f32 scale per (row, 256-block), f32 activations;
+// out[r] = sum_blk scale[r, blk] * (sum_{e < 256} D[code(r, blk, e)] * x[blk * 256 + e]).
+// One warp per row; a lane owns 8 consecutive elements (two bytes) of every block, the block sum is
+// formed before the scale is applied, as in the reference (only the order inside a block differs).
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) qk256_legacy_kernel(const uint8_t* __restrict__ packed, const float* __restrict__ scales,
+                                                           const float* __restrict__ x, float* __restrict__ out, int rows,
+                                                           int nblk) {
+    const int row = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (row >= rows) return;
+    float row_sum = 0.f;
+    for (int b = 0; b < nblk; ++b) {
+        const size_t gb = (size_t)row * nblk + b;
+        const uint16_t two = *reinterpret_cast<const uint16_t*>(packed + gb * 64 + 2 * lane);
+        const float* xb = x + (size_t)b * 256 + 8 * lane;
+        float bs = 0.f;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            const uint32_t c = (two >> (2 * e)) & 3u;
+            const float wv = c == 2u ? 1.f : (c == 1u ? 0.f : -1.f);
+            bs = fmaf(wv, xb[e], bs);
+        }
+        bs = warp_sum(bs);
+        row_sum = fmaf(bs, scales[gb], row_sum);
+    }
+    if (lane == 0) out[row] = row_sum;
+}
+
+int launch_qk256_legacy(cudaStream_t st, const uint8_t* packed, const float* scales, const float* x, float* out, int rows,
+                        int nblk) {
+    qk256_legacy_kernel<<<(unsigned)div_ceil((size_t)rows, 4), 128, 0, st>>>(packed, scales, x, out, rows, nblk);
+    B200_LAUNCH_CHECK("qk256_legacy_kernel");
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------
 // BitNet32-F16 upload: split [rows, cols/32, 10 B] into a code plane [rows, cols/4] and an
 // f16 scale plane [rows, cols/32] (lossless; 10-byte blocks cannot be loaded 16 B aligned)
 // ---------------------------------------------------------------------------------------

@@ -12,6 +12,7 @@ CSRC = os.path.join(HERE, "csrc")
 SYMBOLS = [
     "bitnet_cpp_init", "bitnet_cpp_cleanup", "bitnet_cpp_is_available", "bitnet_cpp_matmul_i2s",
     "bitnet_cpp_quantize", "bitnet_cpp_get_last_error", "bitnet_b200_gemv_qk256",
+    "bitnet_b200_qk256_gemv", "bitnet_b200_qk256_gemv_scalar",
     "bitnet_b200_ctx_create", "bitnet_b200_ctx_set_stream", "bitnet_b200_ctx_synchronize",
     "bitnet_b200_ctx_destroy", "bitnet_b200_weight_create", "bitnet_b200_weight_destroy",
     "bitnet_b200_weight_rows", "bitnet_b200_weight_cols", "bitnet_b200_weight_nbytes",
@@ -111,6 +112,8 @@ def lib():
         l.bitnet_b200_actquant_i8_absmax.argtypes = [vp, vp, vp, i32, i32, vp, vp]
         l.bitnet_b200_residual_acc.argtypes = [vp, vp, vp, vp, i32, i32]
         l.bitnet_b200_rope_attn_decode.argtypes = [vp] * 7 + [i32] * 5 + [vp]
+        for fn in (l.bitnet_b200_qk256_gemv, l.bitnet_b200_qk256_gemv_scalar):
+            fn.argtypes = [vp, sz, sz, sz, vp, sz, vp, sz, vp, sz]
         l.bitnet_b200_version.restype = C.c_char_p
         l.bitnet_b200_launch_count.restype = C.c_uint64
         _lib = l

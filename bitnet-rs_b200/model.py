@@ -166,6 +166,26 @@ class Model:
         self.set_embedding(*synth_embedding(self.shape))
         self.set_rope(*rope_tables(self.shape))
 
+    @classmethod
+    def load_gguf(cls, ctx, path, max_ctx=256, batch=1):
+        """Whole-model load from a GGUF file: tensor-name remap (`blk.N.attn_q.weight` -> layer slot, the reference's
+        weight_mapper.rs:254-303,375-490), I2_S flavour detection per tensor, packed bytes uploaded as they lie on
+        disk (loader.rs:1405-1521; no f32 dequantisation), norms / tied f16 embedding / RoPE tables from the
+        metadata. Returns a ready Model; its `.shape` is read from the file."""
+        from . import gguf
+        r = gguf.GgufReader(path)
+        try:
+            fields, layers, emb, final_norm = gguf.load_model_tensors(r)
+        finally:
+            r.close()
+        shape = ModelShape(max_ctx=max_ctx, batch=batch, **fields)
+        m = cls(ctx, shape)
+        for l, w in enumerate(layers):
+            m.set_layer(l, w)
+        m.set_embedding(emb, final_norm)
+        m.set_rope(*rope_tables(shape))
+        return m
+
     def reset(self):
         ffi.check(self._lib.bitnet_b200_model_reset(self._h))
 

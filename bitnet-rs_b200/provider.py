@@ -223,3 +223,86 @@ def i2s_matmul_f32(activations, weights_packed, scales, out, m, n, k, block_size
                                               scales.ctypes.data, out.ctypes.data, m, n, k, block_size)
     if rc != 0:
         raise KernelError("ExecutionFailed", ffi.last_error())
+
+
+# --------------------------------------------------------------------------------------------
+# a12: the legacy QK256 entry points (crates/bitnet-quantization/src/qk256_dispatch.rs:20-99)
+# --------------------------------------------------------------------------------------------
+def _legacy(fn, output, rows, cols, packed, scales, activations):
+    output = _host(output, np.float32, "output")
+    packed = _host(packed, np.uint8, "packed")
+    scales = _host(scales, np.float32, "scales")
+    activations = _host(activations, np.float32, "activations")
+    rc = fn(output.ctypes.data, output.size, rows, cols, packed.ctypes.data, packed.size, scales.ctypes.data,
+            scales.size, activations.ctypes.data, activations.size)
+    if rc != 0:
+        # the reference asserts (panics) on a violated contract: same message, as an AssertionError
+        raise AssertionError(ffi.last_error())
+
+
+def qk256_gemv(output, rows, cols, packed, scales, activations):
+    """qk256_gemv (qk256_dispatch.rs:20-43): validates the legacy contract, then gemv_qk256 (map A);
+    `scales` is checked for its length and not consumed."""
+    _legacy(ffi.lib().bitnet_b200_qk256_gemv, output, rows, cols, packed, scales, activations)
+
+
+def qk256_gemv_scalar(output, rows, cols, packed, scales, activations):
+    """qk256_gemv_scalar (qk256_dispatch.rs:45-99): map D {-1, 0, +1, -1} with one f32 scale per 256-block."""
+    _legacy(ffi.lib().bitnet_b200_qk256_gemv_scalar, output, rows, cols, packed, scales, activations)
+
+
+# --------------------------------------------------------------------------------------------
+# a16: the in-tree consumer of the provider seam, QuantizedLinear's native I2_S path
+# (crates/bitnet-inference/src/layers/quantized_linear.rs:704-802, utils at :1762-1773 and
+# crates/bitnet-quantization/src/utils.rs:76-91). Host-side glue only; the matmul is the provider's.
+# --------------------------------------------------------------------------------------------
+def unpack_2bit_values(packed, output_len):
+    """unpack_2bit_values (bitnet-quantization/src/utils.rs:76-91): 4 codes per byte, LSB first, code - 2."""
+    packed = np.ascontiguousarray(packed, dtype=np.uint8).reshape(-1)
+    codes = ((packed[:, None] >> (2 * np.arange(4, dtype=np.uint8))) & 3).reshape(-1)[:output_len]
+    return codes.astype(np.int8) - 2
+
+
+def quantize_input_i2s(x):
+    """quantize_input_i2s (quantized_linear.rs:1762-1773): clamp to [-2, 1], round half away from zero (f32::round)."""
+    c = np.clip(np.asarray(x, dtype=np.float32), -2.0, 1.0)
+    return (np.sign(c) * np.floor(np.abs(c) + np.float32(0.5))).astype(np.int8)
+
+
+class QuantizedLinear:
+    """QuantizedLinear's I2_S branch: forward = quantize_input_i2s -> provider.matmul_i2s on the unpacked
+    (code + 2) bytes -> apply_quantization_scales. `weights_packed` holds in*out 2-bit codes of the [in, out]
+    (row-major k x n) matrix matmul_i2s expects; `scales` are per output feature or per `block_size` weights."""
+
+    def __init__(self, weights_packed, scales, in_features, out_features, block_size=32, provider=None):
+        self.data = np.ascontiguousarray(weights_packed, dtype=np.uint8).reshape(-1)
+        self.scales = np.ascontiguousarray(scales, dtype=np.float32).reshape(-1)
+        self.in_features, self.out_features, self.block_size = int(in_features), int(out_features), int(block_size)
+        self.provider = provider if provider is not None else B200Kernel()
+
+    def prepare_quantized_weights_i2s(self):
+        """quantized_linear.rs:769-776: unpack to i8 in [-2, 1], shift to u8 in [0, 3] for the kernel interface."""
+        return (unpack_2bit_values(self.data, self.in_features * self.out_features) + 2).astype(np.uint8)
+
+    def apply_quantization_scales(self, output_data):
+        """quantized_linear.rs:779-802 (in place on [batch, out_features] f32): scales[col] when there is one scale
+        per output feature, else scales[min(col * in_features / block_size, len - 1)]; a missing scale counts as 1."""
+        out = self.out_features
+        n = self.scales.size
+        if n == out:
+            idx = np.arange(out)
+        else:
+            idx = np.minimum(np.arange(out, dtype=np.int64) * self.in_features // self.block_size, n - 1)
+        sc = self.scales[idx] if n else np.ones(out, np.float32)
+        output_data.reshape(-1, out)[:] *= np.float32(1.0) * sc
+        return output_data
+
+    def forward(self, x):
+        x = np.asarray(x, dtype=np.float32)
+        batch = int(np.prod(x.shape[:-1])) if x.ndim > 1 else 1
+        q = quantize_input_i2s(x.reshape(batch, self.in_features))
+        w = self.prepare_quantized_weights_i2s()
+        y = np.zeros(batch * self.out_features, np.float32)
+        self.provider.matmul_i2s(q.reshape(-1), w, y, batch, self.out_features, self.in_features)
+        self.apply_quantization_scales(y)
+        return y.reshape(x.shape[:-1] + (self.out_features,))

@@ -137,9 +137,11 @@ class TPDecoder:
         self.v0 = rank * (shape.vocab // tp)
         self.emb_shard = self.emb[self.v0:self.v0 + shape.vocab // tp]
         self.weight_bytes = sum(e[k].nbytes for e in self.layers for k in ("wqkv", "wo", "wgu", "wdown"))
+        self._pos_host = 0   # host mirror of self.pos: the kernels index the caches and RoPE tables with it unchecked
 
     def reset(self):
         self.pos.zero_()
+        self._pos_host = 0
 
     def layers_gen(self, x):
         """The ternary part of one step on hidden state x [B, hidden] (updated in place)."""
@@ -167,6 +169,9 @@ class TPDecoder:
     def step_gen(self):
         """One greedy decode step: self.tokens [B] -> self.tokens, self.pos += 1."""
         torch, s = self.torch, self.shape
+        if self._pos_host >= s.max_ctx:
+            raise ValueError("TPDecoder: context full (position %d, max_ctx %d): call reset()" % (self._pos_host, s.max_ctx))
+        self._pos_host += 1
         x = self.emb[self.tokens].float()
         yield from self.layers_gen(x)
         _, _, xn = self.ctx.rmsnorm_actquant(x, self.final_norm, s.rms_eps, want_normed=True)

@@ -70,6 +70,20 @@ int bitnet_b200_gemv_qk256(const uint8_t* qs, size_t qs_len, const float* x, siz
                            float* y, size_t y_len, size_t rows, size_t cols,
                            size_t row_stride_bytes);
 
+/* Legacy QK256 entry points kept by the reference for old call sites and benches
+ * (crates/bitnet-quantization/src/qk256_dispatch.rs). Host slices; `packed` is rows*cols/4 bytes,
+ * `scales` rows*(cols/256) f32. The reference asserts on a violated contract; here the same messages
+ * ("Output length mismatch", "Activation length mismatch", "Cols must be multiple of QK256",
+ * "Packed weight size mismatch", "Scales length mismatch") come back as errors.
+ *   qk256_gemv        (:20-43): validates, then forwards to gemv_qk256 -- map A, `scales` NOT consumed;
+ *   qk256_gemv_scalar (:45-99): map D {-1, 0, +1, -1}, out[r] = sum_blk scales[r,blk] * blocksum. */
+int bitnet_b200_qk256_gemv(float* output, size_t out_len, size_t rows, size_t cols, const uint8_t* packed,
+                           size_t packed_len, const float* scales, size_t scales_len, const float* activations,
+                           size_t act_len);
+int bitnet_b200_qk256_gemv_scalar(float* output, size_t out_len, size_t rows, size_t cols, const uint8_t* packed,
+                                  size_t packed_len, const float* scales, size_t scales_len,
+                                  const float* activations, size_t act_len);
+
 /* ------------------------------------------------------------------------------------ *
  * Part 3 -- additive device-resident API (the fast path)                                 *
  * ------------------------------------------------------------------------------------ */
@@ -223,6 +237,33 @@ int bitnet_b200_residual_acc(bitnet_b200_ctx* ctx, const int32_t* acc, const flo
 int bitnet_b200_rope_attn_decode(bitnet_b200_ctx* ctx, float* qkv, const float* cos_t, const float* sin_t,
                                  float* kc, float* vc, const int32_t* pos_dev, int B, int NH, int NKV, int D,
                                  int max_ctx, float* att);
+
+/* ---- fused exchanges: the consumer kernel pulls its peers' buffers over NVLink itself (no NCCL call) --------
+ * One descriptor per exchange point. All pointers are DEVICE pointers valid on THIS GPU: peer_data[r] / peer_flags[r]
+ * are rank r's buffers mapped into this process (symmetric memory / CUDA IPC / the same GPU in the emulation);
+ * index `rank` is the local one. peer_flags[r]: uint32 [4 slots][8 ranks], zero-initialised; counters: local uint32
+ * [8], zero-initialised. slot in 0..3 names the exchange point (o absmax, o sum, down absmax, down sum).
+ * phase: 1 = only tell the peers "my data of this exchange is ready", 2 = wait for every rank and do the work,
+ * 3 = both (what a real rank passes; 1 then 2 lets several emulated ranks share one GPU without waiting on a
+ * kernel that is not running yet). Protocol and reuse rules: bitnet-rs_b200/csrc/tp_xchg.cuh. */
+typedef struct {
+    const void* peer_data[8];
+    uint32_t* peer_flags[8];
+    uint32_t* counters;
+    int n_ranks, rank, slot, phase;
+} bitnet_b200_tp_xchg;
+/* all-reduce(SUM, int32) + residual + RMSNorm + act-quant in ONE kernel, replacing
+ *   ncclAllReduce(acc) ; residual_acc(acc, act_scale, x) ; rmsnorm_actquant(x, gamma, eps, q, scale, normed):
+ * acc_total[m,n] = sum_r peer_data[r][m,n] (int32 [M,N] partial accumulators of a row-parallel linear_i8);
+ * x[m,n] += act_scale[m] * float(acc_total) ; then cpu::rms_norm + quantize_symmetric_i8 of the row, bit for bit
+ * what the three calls produce. Every rank computes all M rows (x stays replicated). N % 4 == 0, N <= 16384. */
+int bitnet_b200_tp_xchg_sum_rmsnorm_actquant(bitnet_b200_ctx* ctx, const bitnet_b200_tp_xchg* xc,
+                                             const float* act_scale, float* x, const float* gamma, float eps, int M,
+                                             int N, int8_t* q, float* scale, float* normed);
+/* all-reduce(MAX, f32) of the per-token absmax + quantise the local slice in ONE kernel, replacing
+ *   ncclAllReduce(absmax, MAX) ; actquant_i8_absmax(x, absmax, q, scale):  peer_data[r] = rank r's absmax [M] f32. */
+int bitnet_b200_tp_xchg_max_actquant(bitnet_b200_ctx* ctx, const bitnet_b200_tp_xchg* xc, const float* x, int M,
+                                     int K, int8_t* q, float* scale);
 
 /* library / build identification */
 const char* bitnet_b200_version(void);

@@ -392,6 +392,10 @@ class Model:
     def reset(self):
         self._lib.oracle_model_reset(self._h)
 
+    def set_threads(self, n):
+        """host threads the rows of every projection are split over (1 = the reference's serial loops)"""
+        self.threads = max(1, int(n))
+
     def step(self, token, seq=0, want_logits=False):
         logits = np.zeros(self.shape.vocab, np.float32) if want_logits else None
         t = self._lib.oracle_model_step(self._h, seq, int(token), None if logits is None else _p(logits),

@@ -105,3 +105,41 @@ def test_product_never_imports_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h", ".hpp")):
                 src = open(os.path.join(dirpath, f)).read()
                 assert "oracle" not in src.lower() or f == "__init__.py" and "oracle" not in src, (dirpath, f)
+
+
+def _build_c_caller(tmp_path):
+    import subprocess
+    exe = str(tmp_path / "abi_caller")
+    libdir = os.path.join(ROOT, "bitnet-rs_b200")
+    cmd = ["gcc", "-std=c11", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I", os.path.join(ROOT, "include"),
+           os.path.join(ROOT, "tests", "c", "abi_caller.c"), "-o", exe, "-L", libdir, "-lbitnet_b200",
+           "-Wl,-rpath," + libdir]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    return exe
+
+
+def test_header_compiles_as_c11_and_a_c_program_calls_through_it(b200, tmp_path):
+    # the boundary is a C ABI: the header must be valid C (not only C++), and a C caller must link and run
+    import subprocess
+    exe = _build_c_caller(tmp_path)
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, "abi_caller exit %d: %s %s" % (r.returncode, r.stdout, r.stderr)
+    assert ("loud failure ok" in r.stdout) if _no_gpu() else ("matmul_i2s ok" in r.stdout)
+
+
+def test_rust_bindings_name_every_header_symbol(b200):
+    # bitnet-b200-sys ships as source (no Rust toolchain in the image): keep its extern block in step with the header
+    hdr = open(os.path.join(ROOT, "include", "bitnet_b200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(bitnet_(?:cpp|b200)_[a-z0-9_]+)\s*\(", hdr))
+    rs = open(os.path.join(ROOT, "bitnet-b200-sys", "src", "lib.rs")).read()
+    bound = set(re.findall(r"pub fn (bitnet_(?:cpp|b200)_[a-z0-9_]+)\s*\(", rs))
+    assert bound == declared, "missing in lib.rs: %s; not in the header: %s" % (sorted(declared - bound), sorted(bound - declared))
+    for f in ("Cargo.toml", "build.rs", os.path.join("src", "b200.rs")):
+        assert os.path.exists(os.path.join(ROOT, "bitnet-b200-sys", f))
+    # the config struct is bound field for field
+    fields = re.search(r"typedef struct \{(.*?)\} bitnet_b200_model_config", hdr, flags=re.S).group(1)
+    names = re.findall(r"\b([a-z_]+)\s*[,;]", fields)
+    for n in names:
+        assert re.search(r"pub %s: c_" % n, rs), "model_config field %s not bound" % n

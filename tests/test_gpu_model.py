@@ -124,3 +124,31 @@ def test_decode_chain_is_deterministic_across_repetitions(b200):
         ref = ref or chain
         assert chain == ref, "repetition %d diverged: %r vs %r" % (rep, chain, ref)
     gm.close()
+
+
+def test_context_length_and_token_id_guards(b200):
+    # the position lives on the device; the host mirror must refuse the step that would write past max_ctx
+    shape = b200.ModelShape(hidden=256, ffn=512, n_layers=1, n_heads=4, n_kv_heads=2, head_dim=64, vocab=300, max_ctx=4)
+    ctx = b200.Context(0)
+    m = b200.Model(ctx, shape)
+    m.load_synthetic()
+    tok = np.array([3], np.int32)
+    for _ in range(4):
+        tok = m.decode(tok)
+    with pytest.raises(b200.B200Error, match="context full"):
+        m.decode(tok)
+    m.reset()
+    first = m.decode(np.array([3], np.int32))
+    with pytest.raises(b200.B200Error, match="exceed max_ctx"):
+        m.decode_device(4)                       # position 1 + 4 steps > 4: nothing is launched
+    m.decode_device(3)
+    ctx.synchronize()
+    with pytest.raises(b200.B200Error, match="context full"):
+        m.decode(tok)
+    with pytest.raises(b200.B200Error, match="token id out of range"):
+        m.set_tokens(np.array([300], np.int32))
+    with pytest.raises(b200.B200Error, match="token id out of range"):
+        m.set_tokens(np.array([-1], np.int32))
+    m.reset()
+    assert np.array_equal(m.decode(np.array([3], np.int32)), first)
+    m.close()

@@ -282,6 +282,37 @@ def test_linear_qk256_gemm_cold_weights_repeated(ctx, b200):
         assert torch.equal(acc, ref), "rep %d" % rep
 
 
+# ---- configs[2] / configs[3] sizes: M = 4096 and M = 16384 on the four 2B-4T projections ------------------
+# (the persistent GEMM wraps its rings the most here and split-K is off). The int32 reference is a device-side
+# dense product in f32 over K halves (every partial |sum| < 2^24, so f32 is exact), added as int64 -> int32.
+def _torch_acc_qk256(qs, rows, cols, q_dev, chunk=2048):
+    import torch
+    lut = torch.tensor([-2, -1, 1, 2], dtype=torch.float32, device="cuda")
+    codes = torch.from_numpy(qs).cuda().view(rows, cols // 4)
+    wd = torch.stack([lut[((codes >> (2 * j)) & 3).long()] for j in range(4)], dim=2).reshape(rows, cols)
+    acc = torch.zeros(q_dev.shape[0], rows, dtype=torch.int64, device="cuda")
+    for k0 in range(0, cols, chunk):   # |partial| <= 2048 * 127 * 2 < 2^24: exact in f32
+        acc += (q_dev[:, k0:k0 + chunk].float() @ wd[:, k0:k0 + chunk].t()).round().to(torch.int64)
+    return acc.to(torch.int32)
+
+
+@pytest.mark.parametrize("rows,cols", [(3840, 2560), (2560, 2560), (13824, 2560), (2560, 6912)])
+@pytest.mark.parametrize("M", [4096, 16384])
+def test_linear_qk256_gemm_prefill_sizes(ctx, b200, rows, cols, M):
+    rng = np.random.default_rng(rows + cols + M)
+    qs = rng.integers(0, 256, rows * cols // 4, dtype=np.uint8)
+    q = torch.from_numpy(rng.integers(-127, 128, (M, cols)).astype(np.int8)).cuda()
+    s = torch.from_numpy(rng.uniform(0.5, 2.0, M).astype(np.float32)).cuda()
+    w = ctx.weight(qs, b200.LAYOUT_QK256, rows, cols)
+    y, acc = ctx.linear_i8(w, q, s, want_acc=True)
+    ref = _torch_acc_qk256(qs, rows, cols, q)
+    assert torch.equal(acc, ref)
+    assert torch.equal(y, ref.float() * s[:, None])      # one exact int->f32 and one multiply
+    del y, acc, ref
+    y2 = ctx.linear_i8(w, q, s)                            # the no-accumulator path
+    assert torch.equal(y2, _torch_acc_qk256(qs, rows, cols, q).float() * s[:, None])
+
+
 @pytest.mark.parametrize("lut_name", ["MAP_B", "MAP_C"])
 def test_linear_qk256_gemm_other_code_maps(ctx, b200, oracle, lut_name):
     rows, cols, M = 192, 1024, 70
@@ -405,6 +436,28 @@ def test_linear_bitnet32_gemm_tcgen05(ctx, b200, oracle, rows, cols, M):
     assert np.array_equal(ctx.linear_i8(w, dev(q), dev(s)).cpu().numpy(), y) or rows * M < 148 * 128 * 16
 
 
+@pytest.mark.parametrize("rows,cols", [(3840, 2560), (2560, 2560), (13824, 2560), (2560, 6912)])
+@pytest.mark.parametrize("M", [4096, 16384])
+def test_linear_bitnet32_gemm_prefill_sizes(ctx, b200, oracle, rows, cols, M):
+    # configs[2] / configs[3] sizes on the BitNet32-F16 layout; reference = dequantise-then-f64 product on the device
+    data = oracle.make_bitnet32(rows, cols, 0xB2000090 + rows + M)
+    rng = np.random.default_rng(rows + cols + M + 1)
+    q = torch.from_numpy(rng.integers(-127, 128, (M, cols)).astype(np.int8)).cuda()
+    s = torch.from_numpy(rng.uniform(0.5, 2.0, M).astype(np.float32)).cuda()
+    w = ctx.weight(data, b200.LAYOUT_BITNET32_F16, rows, cols)
+    y = ctx.linear_i8(w, q, s)
+    blk = torch.from_numpy(data).cuda().view(rows, cols // 32, 10)
+    codes = blk[:, :, :8]
+    lut = torch.tensor([-2, -1, 1, 2], dtype=torch.float64, device="cuda")
+    wq = torch.stack([lut[((codes >> (2 * j)) & 3).long()] for j in range(4)], dim=3).reshape(rows, cols // 32, 32)
+    sc = blk[:, :, 8:].contiguous().view(torch.float16).reshape(rows, cols // 32).double().abs().clamp(1e-3, 1e3)  # SCALE_ABS_CLAMP (quant/i2s.rs:93)
+    wd = (wq * sc[:, :, None]).reshape(rows, cols)
+    for m0 in range(0, M, 2048):
+        ref = (q[m0:m0 + 2048].double() @ wd.t()) * s[m0:m0 + 2048, None].double()
+        err = (y[m0:m0 + 2048].double() - ref).norm() / ref.norm()
+        assert float(err) < 2e-5, "rows %d..%d rel %.3g" % (m0, m0 + 2048, float(err))
+
+
 def test_linear_bitnet32_gemm_other_code_map(ctx, b200, oracle):
     rows, cols, M = 192, 1024, 70
     data = oracle.make_bitnet32(rows, cols, 77)
@@ -435,6 +488,28 @@ def test_linear_bitnet32_scale_edge_cases(ctx, b200, oracle, policy):
     ry = oracle.linear_bitnet32_i8(data.ravel(), rows, cols, q, s, scale_policy=pol)
     assert np.all(np.isfinite(y))
     assert _rel(y, ry) < 1e-5
+
+
+@pytest.mark.parametrize("policy", ["SCALE_ABS_CLAMP", "SCALE_RAW"])
+def test_linear_bitnet32_same_result_across_the_gemv_gemm_boundary(ctx, b200, oracle, policy):
+    # The tcgen05 kind::f16 GEMM (M >= 9) folds the block scale into f16 weights. Clamped scales (1e-3 is not an f16)
+    # and raw scales whose |s| * 2 overflows f16 would make M = 9 differ from M = 8: such weights are flagged at
+    # upload and stay on the f32-scale GEMV, so a token's output does not depend on the batch it travels in.
+    rows, cols = 64, 256
+    data = oracle.make_bitnet32(rows, cols, 21).reshape(-1, 10)
+    specials = [0x0001, 0x1418, 0x7BFF, 0xFBFF, 0x6400] if policy == "SCALE_ABS_CLAMP" else [0x7BFF, 0xFBFF, 0x7800]
+    for i, bits in enumerate(specials):
+        data[3 * i, 8] = bits & 0xFF
+        data[3 * i, 9] = bits >> 8
+    x = oracle.fill_normal(9 * cols, 6).reshape(9, cols)
+    q, s = oracle.quantize_rows_i8(x)
+    pol = getattr(b200, policy)
+    w = ctx.weight(data.ravel(), b200.LAYOUT_BITNET32_F16, rows, cols, scale_policy=pol)
+    y9 = ctx.linear_i8(w, dev(q), dev(s)).cpu().numpy()
+    y8 = ctx.linear_i8(w, dev(q[:8]), dev(s[:8])).cpu().numpy()
+    assert np.array_equal(y9[:8], y8)
+    ry = oracle.linear_bitnet32_i8(data.ravel(), rows, cols, q, s, scale_policy=pol)
+    assert np.all(np.isfinite(y9)) and _rel(y9, ry) < 1e-5
 
 
 def test_linear_bitnet32_rejects_bad_sizes(ctx, b200):
@@ -568,3 +643,73 @@ def test_fused_linear_edge_rows_and_errors(ctx, b200, oracle):
     w2 = ctx.weight(oracle.fill_bytes(4 * 128, 1), b200.LAYOUT_QK256, 4, 300)
     with pytest.raises(b200.B200Error, match="not covered"):
         ctx.fused_linear(w2, torch.zeros(1, 300, device="cuda"))
+
+
+# =========================================================================================
+# a12: the legacy QK256 entry points (crates/bitnet-quantization/src/qk256_dispatch.rs:20-99)
+# =========================================================================================
+@pytest.mark.parametrize("rows,cols", [(1, 256), (7, 512), (256, 256), (33, 2560), (300, 1024)])
+def test_legacy_qk256_gemv_scalar_matches_reference(b200, oracle, rows, cols):
+    packed = oracle.fill_bytes(rows * cols // 4, 0xB2000D00 + rows)
+    scales = oracle.fill_uniform(rows * (cols // 256), 17 + rows, 0.25, 2.0)
+    act = oracle.fill_normal(cols, 23 + cols)
+    out = np.full(rows, np.nan, np.float32)
+    b200.qk256_gemv_scalar(out, rows, cols, packed, scales, act)
+    ref = oracle.qk256_gemv_scalar_legacy(rows, cols, packed, scales, act)     # map D, per-block f32 scales
+    assert np.allclose(out, ref, rtol=1e-5, atol=1e-5 * np.abs(ref).max())      # f32 sum order inside a block differs
+
+
+def test_legacy_qk256_gemv_forwards_to_gemv_qk256(b200, oracle):
+    # qk256_dispatch.rs:20-43: the legacy signature validates `scales` and does not consume it (map A, no scale)
+    rows, cols = 64, 768
+    packed = oracle.fill_bytes(rows * cols // 4, 0xB2000D77)
+    act = np.round(oracle.fill_normal(cols, 5) * 8).astype(np.float32)          # integer-valued: exact in f32
+    out = np.zeros(rows, np.float32)
+    b200.qk256_gemv(out, rows, cols, packed, np.full(rows * cols // 256, 123.0, np.float32), act)
+    assert np.array_equal(out, oracle.gemv_qk256(packed, act, rows, cols, cols // 4, "scalar"))
+    # the smoke test of the reference (qk256_dispatch.rs:106-124): all codes 1 -> -1, activations 0.5
+    out = np.zeros(256, np.float32)
+    b200.qk256_gemv(out, 256, 256, np.full(256 * 64, 0x55, np.uint8), np.ones(256, np.float32), np.full(256, 0.5, np.float32))
+    assert np.all(out == -128.0)
+
+
+@pytest.mark.parametrize("fn", ["qk256_gemv", "qk256_gemv_scalar"])
+def test_legacy_qk256_contract_messages(b200, fn):
+    f = getattr(b200, fn)
+    ok = dict(rows=2, cols=256, packed=np.zeros(128, np.uint8), scales=np.ones(2, np.float32), act=np.zeros(256, np.float32))
+    with pytest.raises(AssertionError, match="Output length mismatch"):
+        f(np.zeros(3, np.float32), ok["rows"], ok["cols"], ok["packed"], ok["scales"], ok["act"])
+    with pytest.raises(AssertionError, match="Activation length mismatch"):
+        f(np.zeros(2, np.float32), 2, 256, ok["packed"], ok["scales"], np.zeros(255, np.float32))
+    with pytest.raises(AssertionError, match="Cols must be multiple of QK256"):
+        f(np.zeros(2, np.float32), 2, 128, np.zeros(64, np.uint8), ok["scales"], np.zeros(128, np.float32))
+    with pytest.raises(AssertionError, match="Packed weight size mismatch"):
+        f(np.zeros(2, np.float32), 2, 256, np.zeros(127, np.uint8), ok["scales"], ok["act"])
+    with pytest.raises(AssertionError, match="Scales length mismatch"):
+        f(np.zeros(2, np.float32), 2, 256, ok["packed"], np.ones(3, np.float32), ok["act"])
+
+
+# =========================================================================================
+# a16: QuantizedLinear, the in-tree consumer of the provider seam (quantized_linear.rs:704-802)
+# =========================================================================================
+@pytest.mark.parametrize("scale_kind", ["per_feature", "per_block"])
+def test_quantized_linear_consumer_path(b200, kernel, oracle, scale_kind):
+    batch, fin, fout, bs = 5, 96, 40, 32
+    codes = (oracle.fill_bytes(fin * fout, 0xB2000A16) & 3).astype(np.int8) - 2        # i8 in [-2, 1], [in, out] row-major
+    packed = oracle.pack_2bit_values(codes)
+    n_scales = fout if scale_kind == "per_feature" else fin * fout // bs
+    scales = oracle.fill_uniform(n_scales, 31, 0.5, 1.5)
+    x = oracle.fill_normal(batch * fin, 9, 1.2).reshape(batch, fin)
+    ql = b200.QuantizedLinear(packed, scales, fin, fout, block_size=bs, provider=kernel)
+    assert np.array_equal(b200.unpack_2bit_values(packed, fin * fout), oracle.unpack_2bit_values(packed, fin * fout))
+    assert np.array_equal(ql.prepare_quantized_weights_i2s(), (codes + 2).astype(np.uint8))
+    y = ql.forward(x)
+    # the same pipeline stated with the oracle's kernel: quantize_input_i2s -> FallbackKernel::matmul_i2s -> scales
+    q = np.clip(x, -2.0, 1.0)
+    q = (np.sign(q) * np.floor(np.abs(q) + 0.5)).astype(np.int8)
+    ref = oracle.matmul_i2s(q.reshape(-1), (codes + 2).astype(np.uint8), batch, fout, fin, "fallback").reshape(batch, fout)
+    if scale_kind == "per_feature":
+        idx = np.arange(fout)
+    else:
+        idx = np.minimum(np.arange(fout) * fin // bs, n_scales - 1)                    # quantized_linear.rs:791-796
+    assert np.array_equal(y, ref * scales[idx])
