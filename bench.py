@@ -47,6 +47,9 @@ def parse():
     ap.add_argument("--tp-layers", type=int, default=0, help="8b-tp: use fewer layers (smoke runs only)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-budget-s", type=float, default=20.0)
+    ap.add_argument("--tp-exchange", choices=["fused", "nccl", "both"], default="both",
+                    help="8b-tp workload: how the row-parallel layers exchange (fused NVLink pulls, NCCL collectives, or both)")
+    ap.add_argument("--no-tp", action="store_true", help="N > 1: skip the tensor-parallel sub-record of the default workload")
     return ap.parse_args()
 
 
@@ -103,6 +106,16 @@ class ClockSampler:
                 pass
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
                 "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def kernel_source_sha16():
+    """Hash of the sources the persistent decode kernel is built from (ties an ncu capture to a build)."""
+    import hashlib
+    h = hashlib.sha256()
+    for f in ("decode_mega.cu", "decode_mega.h", "common.cuh"):
+        with open(os.path.join(ROOT, "bitnet-rs_b200", "csrc", f), "rb") as fh:
+            h.update(fh.read())
+    return h.hexdigest()[:16]
 
 
 def linear_alg_bytes(shape, M):
@@ -202,25 +215,24 @@ def workload_config(shape, args):
     }
 
 
-def run_tp(args):
-    """BASELINE.json configs[4]: 8B-class ternary model (hidden 4096, FFN 14336, 32 layers), batch-64
-    decode, tensor-parallel over WORLD_SIZE GPUs (Megatron split, int32 all-reduce after o and down)."""
+def tp_measure(args, dist, world, rank, local, exchange, K, W, n_layers=None):
+    """One timed run of the 8B-class batch-64 tensor-parallel decode step on the ranks of `dist` (None = 1 GPU).
+    exchange: "nccl" = the all-reduces are NCCL collectives between kernels; "fused" = the consumer kernels pull
+    their peers' buffers over NVLink themselves (csrc/tp_xchg.cuh). Returns a dict (same on every rank)."""
     import torch
     import bitnet_rs_b200 as b2
     from bitnet_rs_b200 import tp
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    torch.cuda.set_device(local)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    K, W = args.steps, max(args.warmup, 3)
     shape = b2.ModelShape.llama_8b_class(batch=64, max_ctx=PROMPT + 2 * (W + K) + 16)
     ctx = b2.Context(local)
-    dec = b2.TPDecoder(ctx, shape, rank, world, n_layers=args.tp_layers or None)
+    fabric = None
+    if exchange == "fused":
+        if dist is None:
+            fabric = b2.TpFabric.emulated(torch, torch.device("cuda", local), 1, shape.batch, shape.hidden)[0]
+        else:
+            fabric = b2.TpFabric.symmetric(torch, dist, torch.device("cuda", local), shape.batch, shape.hidden)
+    dec = b2.TPDecoder(ctx, shape, rank if dist is not None else 0, world if dist is not None else 1, n_layers=n_layers,
+                       fabric=fabric)
     dec.tokens.copy_((torch.arange(shape.batch, device="cuda") * 7919) % shape.vocab)
 
     def step():
@@ -229,15 +241,9 @@ def run_tp(args):
         else:
             tp.run_distributed(dec.step_gen(), dist)
 
-    def note(msg):
-        if os.environ.get("BENCH_DEBUG"):
-            print("[rank %d] %s" % (rank, msg), file=sys.stderr, flush=True)
-
-    note("decoder built")
     for _ in range(2):            # eager: first-use allocations (split-K scratch, NCCL channels)
         step()
     torch.cuda.synchronize()
-    note("eager steps done")
     launches0 = b2.launch_count()
     step()
     launches_per_step = b2.launch_count() - launches0
@@ -251,9 +257,7 @@ def run_tp(args):
             ctx.use_torch_stream()
             step()
         ctx.use_torch_stream()
-        note("graph captured")
-    except Exception as ex:       # NCCL capture unavailable: time the eager loop instead
-        note("capture failed: %r" % (ex,))
+    except Exception as ex:       # capture unavailable: time the eager loop instead
         graph, mode = None, "eager (graph capture failed: %s)" % type(ex).__name__
         ctx.use_torch_stream()
         torch.cuda.synchronize()
@@ -281,38 +285,56 @@ def run_tp(args):
         t = torch.tensor([ms], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t[0])
-    if rank == 0:
-        nl = dec.n_layers
-        line = {
-            "metric": "8B-class batch-64 decode tok/s (tensor parallel)", "value": shape.batch * K / (ms * 1e-3),
-            "unit": "tok/s", "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms / K,
-            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "int8", "data": "synthetic",
-            "config": {"workload": "8B-class ternary decoder (hidden 4096, FFN 14336, %d layers, GQA 32/8, vocab 128256), "
-                                   "batch 64, random-init I2_S QK256 weights (BASELINE.json configs[4])" % nl,
-                       "parallelism": "tp%d: q/k/v + gate/up by rows, o + down by input columns, int32 all-reduce(SUM) "
-                                      "+ f32 all-reduce(MAX) of the per-token absmax over NCCL" % world,
-                       "launch": mode,
-                       "l2": "weights %.0f MB per rank vs 126 MB L2" % (dec.weight_bytes / 1e6)},
-            "clocks": clocks, "gpu_launches": int(launches_per_step * K), "launches_per_step": int(launches_per_step),
-            "collectives_per_step": 4 * nl + 1,
-        }
-        print(json.dumps(line), flush=True)
+    nl = dec.n_layers
+    out = {"tok_s": shape.batch * K / (ms * 1e-3), "ms_per_step": ms / K, "launch": mode, "clocks": clocks, "n_layers": nl,
+           "launches_per_step": int(launches_per_step), "exchange": exchange,
+           "collectives_per_step": (4 * nl + 1) if exchange == "nccl" else 1,
+           "weight_mb_per_rank": dec.weight_bytes / 1e6, "batch": shape.batch}
+    del dec, graph, fabric
+    torch.cuda.empty_cache()
+    return out
+
+
+TP_WORKLOAD = ("8B-class ternary decoder (hidden 4096, FFN 14336, %d layers, GQA 32/8, vocab 128256), batch 64, "
+               "random-init I2_S QK256 weights (BASELINE.json configs[4])")
+TP_PAR = {"nccl": "tp%d: q/k/v + gate/up by rows, o + down by input columns, int32 all-reduce(SUM) + f32 all-reduce(MAX) of "
+                  "the per-token absmax as NCCL collectives between the kernels",
+          "fused": "tp%d: q/k/v + gate/up by rows, o + down by input columns; the int32 SUM and the absmax MAX are pulled "
+                   "from the peers' symmetric-memory buffers over NVLink by the consumer kernels themselves "
+                   "(sum + residual + RMSNorm + act-quant in one kernel, max + act-quant in one kernel), no collective call"}
+
+
+def run_tp(args):
+    """BASELINE.json configs[4]: 8B-class ternary model (hidden 4096, FFN 14336, 32 layers), batch-64
+    decode, tensor-parallel over WORLD_SIZE GPUs (Megatron split). Prints one line per exchange variant."""
+    import torch
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    K, W = args.steps, max(args.warmup, 3)
+    variants = ["fused", "nccl"] if args.tp_exchange == "both" else [args.tp_exchange]
+    for ex in variants:
+        r = tp_measure(args, dist, world, rank, local, ex, K, W, n_layers=args.tp_layers or None)
+        if rank == 0:
+            line = {
+                "metric": "8B-class batch-64 decode tok/s (tensor parallel)", "value": r["tok_s"],
+                "unit": "tok/s", "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": r["ms_per_step"],
+                "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "int8", "data": "synthetic",
+                "config": {"workload": TP_WORKLOAD % r["n_layers"], "parallelism": TP_PAR[ex] % world, "launch": r["launch"],
+                           "l2": "weights %.0f MB per rank vs 126 MB L2" % r["weight_mb_per_rank"]},
+                "clocks": r["clocks"], "gpu_launches": int(r["launches_per_step"] * K),
+                "launches_per_step": r["launches_per_step"], "collectives_per_step": r["collectives_per_step"],
+            }
+            print(json.dumps(line), flush=True)
     if dist is not None:
-        # every rank has passed the final all-reduce; tearing NCCL down with a captured graph alive can
-        # hang, so leave without the destructor chain
-        torch.cuda.synchronize()
-        sys.stdout.flush()
-        sys.stderr.flush()
-        os._exit(0)
-
-
-# ------------------------------------------------------------------------------------------
-# Per-layer shape sweep (BASELINE.json configs[0] and configs[2]): the linears of 2B-4T at
-# M = 1, 16, 64, 512, 4096 in both layouts, weights rotated through more copies than L2 holds;
-# beside each M = 1 row the reference's CPU kernel for that layout (oracle port) on this host.
-# Not the headline line: JSON lines, one per row, then one summary line.
-# ------------------------------------------------------------------------------------------
-SWEEP_SHAPES = {"qkv": (3840, 2560), "o": (2560, 2560), "gate/up": (6912, 2560), "down": (2560, 6912)}
+        dist.barrier()
+        dist.destroy_process_group()
 
 
 def _sweep_weight_bytes(rng, layout_name, rows, cols):
@@ -504,20 +526,50 @@ def main():
     clocks = sampler.stop()
 
     # ---- roofline: only the ternary GEMVs of a step, back to back ------------------------
+    lps = model.launches_per_step
     ms_lin, n_lin = model.time_linears(20)
     alg = linear_alg_bytes(shape, B)
     peak, peak_src = measured_peak()
     achieved = alg / (ms_lin * 1e-3) / 1e9
     # dram__bytes_read + dram__bytes_write of the same launch from the committed ncu --set full capture
-    # (profiles/r01_ncu_summary.json); not measured live -- a number taken under ncu is never a bench value
+    # (profiles/r02_ncu_summary.json); not measured live -- a number taken under ncu is never a bench value. The
+    # capture names the hash of the kernel sources it was taken at: a capture of other sources is refused (null).
     traffic, traffic_src = None, None
     try:
-        with open(os.path.join(ROOT, "profiles", "r01_ncu_summary.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "r02_ncu_summary.json")) as f:
             ent = json.load(f)["decode_mega_kernel_mode1_gemv_phases"]
         if n_lin == 1 and shape.layout == b2.LAYOUT_QK256 and B == 1:
-            traffic, traffic_src = ent["traffic_bytes_per_launch"], "profiles/r01_ncu_summary.json (ncu --set full, same launch)"
+            if ent.get("kernel_source_sha16") == kernel_source_sha16():
+                traffic = ent["traffic_bytes_per_launch"]
+                traffic_src = "profiles/r02_ncu_summary.json (ncu --set full, same launch, kernel sources %s)" % ent["kernel_source_sha16"]
+            else:
+                traffic_src = ("refused: profiles/r02_ncu_summary.json was captured at kernel sources %s, this build is %s"
+                               % (ent.get("kernel_source_sha16"), kernel_source_sha16()))
     except Exception:
         pass
+
+    # ---- N > 1: the Megatron path on the same ranks (BASELINE.json configs[4]) --------------------
+    tp_rec = None
+    if dist is not None and not args.no_tp:
+        model.close()
+        del model
+        torch.cuda.empty_cache()
+        Kt = min(K, 16)
+        try:
+            fused = tp_measure(args, dist, world, rank, local, "fused", Kt, 3)
+        except Exception as ex:      # symmetric memory unavailable: say so, keep the collective variant
+            fused = {"error": "%s: %s" % (type(ex).__name__, str(ex)[:200])}
+        nccl = tp_measure(args, dist, world, rank, local, "nccl", Kt, 3)
+        tp1 = tp_measure(args, None, 1, 0, local, "nccl", Kt, 3)          # every rank times tp = 1 on its own GPU
+        best = fused if "tok_s" in fused and fused["tok_s"] >= nccl["tok_s"] else nccl
+        tp_rec = {"workload": TP_WORKLOAD % best["n_layers"], "tok_s": best["tok_s"], "ms_per_step": best["ms_per_step"],
+                  "exchange": best["exchange"], "parallelism": TP_PAR[best["exchange"]] % world,
+                  "tp1_tok_s": tp1["tok_s"], "tp1_ms_per_step": tp1["ms_per_step"],
+                  "efficiency": best["tok_s"] / (world * tp1["tok_s"]), "scaling": "strong",
+                  "collectives_per_step": best["collectives_per_step"], "launches_per_step": best["launches_per_step"],
+                  "launch": best["launch"], "steps": Kt,
+                  "fused": {k: fused.get(k) for k in ("tok_s", "ms_per_step", "launches_per_step", "collectives_per_step", "error") if k in fused},
+                  "nccl": {k: nccl[k] for k in ("tok_s", "ms_per_step", "launches_per_step", "collectives_per_step")}}
 
     if dist is not None:
         t = torch.tensor([ms_dev, ms_e2e], device="cuda", dtype=torch.float64)
@@ -533,7 +585,7 @@ def main():
             "e2e": {"value": world * B * K / (ms_e2e * 1e-3), "unit": "tok/s", "h2d_bytes_per_step": 4 * B,
                     "d2h_bytes_per_step": 4 * B, "ms_per_step": ms_e2e / K},
             "gpu_launches": int(launches_timed),
-            "launches_per_step": model.launches_per_step,
+            "launches_per_step": lps,
             "roofline": {"bound": "hbm",
                          "kernel": "decode_mega_kernel restricted to its %d ternary GEMV phases (M=%d): one launch "
                                    "streams every packed ternary weight of the model once" % (4 * shape.n_layers, B)
@@ -546,6 +598,8 @@ def main():
                          "whole_step_weight_GBs": (shape.ternary_bytes() + 2 * shape.vocab * shape.hidden)
                          / (ms_dev / K * 1e-3) / 1e9},
         }
+        if tp_rec is not None:
+            line["tp"] = tp_rec
         if world == 1 and not args.no_cpu_baseline:
             try:
                 v, cores, sample, _, _, single = cpu_decode_tok_s(shape, 8, 1, args.cpu_budget_s)

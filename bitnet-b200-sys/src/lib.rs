@@ -46,6 +46,19 @@ pub struct bitnet_b200_model_config {
     pub layout: c_int,
 }
 
+/// One cross-GPU exchange point of the fused tensor-parallel path (include/bitnet_b200.h, Part 5).
+#[repr(C)]
+#[derive(Clone, Copy)]
+pub struct bitnet_b200_tp_xchg {
+    pub peer_data: [*const c_void; 8],
+    pub peer_flags: [*mut u32; 8],
+    pub counters: *mut u32,
+    pub n_ranks: c_int,
+    pub rank: c_int,
+    pub slot: c_int,
+    pub phase: c_int,
+}
+
 extern "C" {
     // ---- Part 1: the reference's own bridge (ffi/bridge.rs:17-39) ------------------------------------
     pub fn bitnet_cpp_init() -> c_int;
@@ -153,6 +166,15 @@ extern "C" {
         ctx: *mut bitnet_b200_ctx, qkv: *mut c_float, cos_t: *const c_float, sin_t: *const c_float,
         kc: *mut c_float, vc: *mut c_float, pos_dev: *const i32, b: c_int, nh: c_int, nkv: c_int, d: c_int,
         max_ctx: c_int, att: *mut c_float,
+    ) -> c_int;
+
+    pub fn bitnet_b200_tp_xchg_sum_rmsnorm_actquant(
+        ctx: *mut bitnet_b200_ctx, xc: *const bitnet_b200_tp_xchg, act_scale: *const c_float, x: *mut c_float,
+        gamma: *const c_float, eps: c_float, m: c_int, n: c_int, q: *mut i8, scale: *mut c_float, normed: *mut c_float,
+    ) -> c_int;
+    pub fn bitnet_b200_tp_xchg_max_actquant(
+        ctx: *mut bitnet_b200_ctx, xc: *const bitnet_b200_tp_xchg, x: *const c_float, m: c_int, k: c_int, q: *mut i8,
+        scale: *mut c_float,
     ) -> c_int;
 
     pub fn bitnet_b200_version() -> *const c_char;

@@ -51,10 +51,10 @@ from .model import (  # noqa: F401
 )
 
 from . import gguf, tp  # noqa: F401,E402
-from .tp import TPDecoder  # noqa: F401,E402
+from .tp import TPDecoder, TpFabric  # noqa: F401,E402
 
 __all__ = [
-    "TPDecoder", "tp",
+    "TPDecoder", "TpFabric", "tp",
     "Model", "ModelShape",
     "B200Error", "B200Kernel", "Context", "I2SQk256NoScale", "KernelError", "KernelManager",
     "KernelProvider", "QuantizationType", "Weight", "build", "gemv_qk256", "i2s_matmul_f32",

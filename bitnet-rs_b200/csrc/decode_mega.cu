@@ -482,7 +482,7 @@ __device__ __forceinline__ void mega_tiles(const MegaParams& p, const MegaSmem& 
 // epi: 0 store, 1 residual add (out may alias resid), 2 SwiGLU on interleaved (gate, up) rows
 __device__ __forceinline__ void mega_gemv_phase(const MegaParams& p, const MegaSmem& sm, const MegaOp& o, int pro, const uint2* xin,
                                              const float* gamma, int epi, uint2* out, const uint2* resid, uint32_t ep_res,
-                                             uint32_t ep_out, RingPos& rp, uint32_t& par, int& pi, int& wi) {
+                                             uint32_t ep_out, RingPos& rp, uint32_t& par, int& pi, int& wi, int tdiv, int tmod) {
     const int tid = threadIdx.x, warp = tid >> 5;
     prof_stamp(p, pi);  // phase start
     const PhaseGeom q = phase_geom(o, blockIdx.x);
@@ -496,7 +496,7 @@ __device__ __forceinline__ void mega_gemv_phase(const MegaParams& p, const MegaS
     const int kc0 = (warp * o.KC) / MEGA_NW, nc = ((warp + 1) * o.KC) / MEGA_NW - kc0;
     // residual rows of this CTA: probed now, validated in the epilogue (one (row, token) per thread)
     const int nout = q.nloc * 16 * B;
-    const int orow = q.t0 * 16 + tid / B, om = tid % B;   // output element of this thread (epi 0 / 1)
+    const int orow = q.t0 * 16 + tdiv, om = tmod;
     uint2 rprobe = make_uint2(0u, 0u);
     if (epi == 1 && tid < nout) rprobe = ll_ld1(resid + (size_t)om * N + orow);
     float sc[MEGA_MAXB];
@@ -516,7 +516,7 @@ __device__ __forceinline__ void mega_gemv_phase(const MegaParams& p, const MegaS
     if (epi == 2) {
         const int half = N >> 1;
         if (tid < q.nloc * 8 * B) {
-            const int m = tid % B, pr = tid / B;  // pair index inside the CTA's rows: rows 2 pr (gate), 2 pr + 1 (up)
+            const int m = tmod, pr = tdiv;
             int a0 = 0, a1 = 0;
 #pragma unroll
             for (int w = 0; w < MEGA_NW; ++w) {
@@ -1027,6 +1027,7 @@ __global__ void __launch_bounds__(MEGA_THREADS, 1) decode_mega_kernel(const __gr
     RingPos rp{0u, 0u};
     int pi = 0, wi = 0;
     uint32_t par = 0;
+    const int tdiv = tid / p.B, tmod = tid - tdiv * p.B;
     const int H = p.H, F = p.F, D = p.D, NH = p.NH, NKV = p.NKV, B = p.B;
     const int QD = NH * D, QKV = (NH + 2 * NKV) * D;
     const bool full = p.mode == 0;  // mode 1 = roofline leg: the 4L ternary GEMVs only, fixed int8 inputs, no barriers
@@ -1089,7 +1090,7 @@ __global__ void __launch_bounds__(MEGA_THREADS, 1) decode_mega_kernel(const __gr
             const int epi = op == 3 ? 2 : ((full && (op == 2 || op == 4)) ? 1 : 0);
             uint2* out = op == 0 ? p.qkv : (op == 3 ? p.gu : p.x);
             const uint32_t ep_res = op == 2 ? ep - 3u : ep - 2u;  // x was last written by the previous down phase (or the embedding) / by this layer's o phase
-            mega_gemv_phase(p, sm, p.op[opi], pro, xin, gamma, epi, out, p.x, ep_res, ep, rp, par, pi, wi);
+            mega_gemv_phase(p, sm, p.op[opi], pro, xin, gamma, epi, out, p.x, ep_res, ep, rp, par, pi, wi, tdiv, tmod);
             if (full) {
                 // what the next phase touches first and the weight stream has pushed out of L2 since the last step:
                 // the miss overlaps the wait for the other CTAs' outputs

@@ -2,6 +2,7 @@
 // reference's weight quantisers, the unpacked-byte matmul of the KernelProvider seam, and the
 // one-time BitNet32-F16 plane split done at upload.
 #include "common.cuh"
+#include "tp_xchg.cuh"
 
 namespace b200 {
 
@@ -152,6 +153,129 @@ __global__ void __launch_bounds__(1024) actquant_fast_kernel(const float* __rest
                 }
         }
     }
+}
+
+// ---------------------------------------------------------------------------------------
+// Tensor-parallel fused exchange (tp_xchg.cuh): all-reduce(SUM, int32) of the row-parallel linear's partial
+// accumulators + residual + RMSNorm + act-quant, one CTA per token row. The row statistics and the quantiser are
+// those of actquant_fast_kernel<1> with the same thread -> element map and the same reduction trees, so the int8
+// row and its scale equal what  all-reduce ; residual_acc ; rmsnorm_actquant  produce, bit for bit.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(1024) tp_xchg_sum_norm_quant_kernel(const __grid_constant__ bitnet_b200_tp_xchg xc,
+                                                                      const float* __restrict__ act_scale, float* __restrict__ x,
+                                                                      const float* __restrict__ gamma, float eps, int K,
+                                                                      int8_t* __restrict__ q, float* __restrict__ scale,
+                                                                      float* __restrict__ normed) {
+    __shared__ float shf[32];
+    __shared__ double shd[32];
+    const uint32_t epoch = xchg_begin(xc);
+    if (!(xc.phase & 2)) return;
+    const int row = blockIdx.x, tid = threadIdx.x, nt = blockDim.x;
+    float* xr = x + (size_t)row * K;
+    const float as = act_scale[row];
+    float v[16];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int k0 = (tid + j * nt) * 4;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) v[j * 4 + e] = 0.f;
+        if (k0 + 4 <= K) {  // K % 4 == 0 (launcher)
+            int4 a = make_int4(0, 0, 0, 0);
+            for (int r = 0; r < xc.n_ranks; ++r) {
+                const int4 pv = ld_sys_s32x4(static_cast<const int32_t*>(xc.peer_data[r]) + (size_t)row * K + k0);
+                a.x += pv.x; a.y += pv.y; a.z += pv.z; a.w += pv.w;
+            }
+            float4 xv = *reinterpret_cast<const float4*>(xr + k0);
+            xv.x = __fadd_rn(xv.x, __fmul_rn(as, (float)a.x));  // as tp_residual_acc_kernel / EPI_RESIDUAL
+            xv.y = __fadd_rn(xv.y, __fmul_rn(as, (float)a.y));
+            xv.z = __fadd_rn(xv.z, __fmul_rn(as, (float)a.z));
+            xv.w = __fadd_rn(xv.w, __fmul_rn(as, (float)a.w));
+            *reinterpret_cast<float4*>(xr + k0) = xv;
+            v[j * 4 + 0] = xv.x; v[j * 4 + 1] = xv.y; v[j * 4 + 2] = xv.z; v[j * 4 + 3] = xv.w;
+        }
+    }
+    double ss = 0.0;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) ss += (double)v[i] * (double)v[i];
+    ss = block_sum_f64(ss, shd);
+    const float ms = (float)(ss / (double)K);
+    const float inv_rms = 1.0f / sqrtf(ms + eps);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int k0 = (tid + j * nt) * 4;
+        if (k0 + 4 <= K) {
+            const float4 g = *reinterpret_cast<const float4*>(gamma + k0);
+            v[j * 4 + 0] = v[j * 4 + 0] * inv_rms * g.x;
+            v[j * 4 + 1] = v[j * 4 + 1] * inv_rms * g.y;
+            v[j * 4 + 2] = v[j * 4 + 2] * inv_rms * g.z;
+            v[j * 4 + 3] = v[j * 4 + 3] * inv_rms * g.w;
+        }
+    }
+    float amax = 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) amax = fmaxf(amax, fabsf(v[i]));
+    amax = block_max(amax, shf);
+    const float sc = amax == 0.f ? 0.f : amax / 127.f;
+    const float inv = amax == 0.f ? 0.f : 1.0f / sc;
+    if (tid == 0) scale[row] = sc;
+    int8_t* qr = q + (size_t)row * K;
+    float* nr = normed ? normed + (size_t)row * K : nullptr;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int k0 = (tid + j * nt) * 4;
+        if (k0 + 4 > K) continue;
+        int b[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) b[e] = amax == 0.f ? 0 : quant1(v[j * 4 + e], inv);
+        *reinterpret_cast<uint32_t*>(qr + k0) = (uint32_t)(uint8_t)b[0] | ((uint32_t)(uint8_t)b[1] << 8) |
+                                                ((uint32_t)(uint8_t)b[2] << 16) | ((uint32_t)(uint8_t)b[3] << 24);
+        if (nr) *reinterpret_cast<float4*>(nr + k0) = make_float4(v[j * 4], v[j * 4 + 1], v[j * 4 + 2], v[j * 4 + 3]);
+    }
+    xchg_end(xc, epoch);
+}
+
+int launch_tp_xchg_sum_norm_quant(const bitnet_b200_ctx* ctx, const bitnet_b200_tp_xchg* xc, const float* act_scale, float* x,
+                                  const float* gamma, float eps, int M, int K, int8_t* q, float* scale, float* normed) {
+    if (M <= 0 || K <= 0 || K % 4 || K > 16384) return fail("tp_xchg_sum: M > 0, K % 4 == 0 and K <= 16384 required");
+    if (xc->n_ranks < 1 || xc->n_ranks > TP_MAX_RANKS || xc->rank < 0 || xc->rank >= xc->n_ranks || xc->slot < 0 ||
+        xc->slot >= TP_SLOTS || !(xc->phase & 3))
+        return fail("tp_xchg: bad descriptor (ranks 1..8, slot 0..3, phase 1..3)");
+    int threads = (int)div_ceil((size_t)K, 16);   // the thread count of actquant_fast_kernel: same element map
+    threads = (int)div_ceil((size_t)threads, 32) * 32;
+    if (threads < 64) threads = 64;
+    const int grid = (xc->phase & 2) ? M : 1;
+    tp_xchg_sum_norm_quant_kernel<<<grid, threads, 0, ctx->stream>>>(*xc, act_scale, x, gamma, eps, K, q, scale, normed);
+    B200_LAUNCH_CHECK("tp_xchg_sum_norm_quant_kernel");
+    return 0;
+}
+
+// all-reduce(MAX) of the per-token absmax + quantize_symmetric_i8 of the local slice with it (tp_quant_absmax_kernel)
+__global__ void __launch_bounds__(256) tp_xchg_max_quant_kernel(const __grid_constant__ bitnet_b200_tp_xchg xc,
+                                                                const float* __restrict__ x, int K, int8_t* __restrict__ q,
+                                                                float* __restrict__ scale) {
+    const uint32_t epoch = xchg_begin(xc);
+    if (!(xc.phase & 2)) return;
+    const int row = blockIdx.x;
+    float amax = 0.f;
+    for (int r = 0; r < xc.n_ranks; ++r) amax = fmaxf(amax, ld_sys_f32(static_cast<const float*>(xc.peer_data[r]) + row));
+    const float sc = amax == 0.f ? 0.f : amax / 127.f;
+    const float inv = amax == 0.f ? 0.f : 1.0f / sc;
+    if (threadIdx.x == 0) scale[row] = sc;
+    const float* xr = x + (size_t)row * K;
+    int8_t* qr = q + (size_t)row * K;
+    for (int k = threadIdx.x; k < K; k += blockDim.x) qr[k] = (int8_t)(amax == 0.f ? 0 : quant1(xr[k], inv));
+    xchg_end(xc, epoch);
+}
+
+int launch_tp_xchg_max_quant(const bitnet_b200_ctx* ctx, const bitnet_b200_tp_xchg* xc, const float* x, int M, int K, int8_t* q,
+                             float* scale) {
+    if (M <= 0 || K <= 0) return fail("tp_xchg_max: M and K must be > 0");
+    if (xc->n_ranks < 1 || xc->n_ranks > TP_MAX_RANKS || xc->rank < 0 || xc->rank >= xc->n_ranks || xc->slot < 0 ||
+        xc->slot >= TP_SLOTS || !(xc->phase & 3))
+        return fail("tp_xchg: bad descriptor (ranks 1..8, slot 0..3, phase 1..3)");
+    tp_xchg_max_quant_kernel<<<(xc->phase & 2) ? M : 1, 256, 0, ctx->stream>>>(*xc, x, K, q, scale);
+    B200_LAUNCH_CHECK("tp_xchg_max_quant_kernel");
+    return 0;
 }
 
 template <int MODE>

@@ -168,6 +168,12 @@ __global__ void __launch_bounds__(128) tp_attn_decode_kernel(const float* __rest
 
 using namespace b200;
 
+namespace b200 {
+int launch_tp_xchg_sum_norm_quant(const bitnet_b200_ctx*, const bitnet_b200_tp_xchg*, const float*, float*, const float*, float, int,
+                                  int, int8_t*, float*, float*);
+int launch_tp_xchg_max_quant(const bitnet_b200_ctx*, const bitnet_b200_tp_xchg*, const float*, int, int, int8_t*, float*);
+}  // namespace b200
+
 extern "C" {
 
 int bitnet_b200_row_absmax(bitnet_b200_ctx* ctx, const float* x, int M, int K, int swiglu, float* h, float* absmax) {
@@ -202,6 +208,22 @@ int bitnet_b200_residual_acc(bitnet_b200_ctx* ctx, const int32_t* acc, const flo
     tp_residual_acc_kernel<<<(unsigned)div_ceil(total, 256), 256, 0, ctx->stream>>>(acc, act_scale, x, N, total);
     B200_LAUNCH_CHECK("tp_residual_acc_kernel");
     return 0;
+}
+
+int bitnet_b200_tp_xchg_sum_rmsnorm_actquant(bitnet_b200_ctx* ctx, const bitnet_b200_tp_xchg* xc, const float* act_scale,
+                                             float* x, const float* gamma, float eps, int M, int N, int8_t* q, float* scale,
+                                             float* normed) {
+    if (!ctx || !xc || !act_scale || !x || !gamma || !q || !scale) return fail("tp_xchg_sum: NULL argument");
+    if (!(eps > 0.f)) return fail("tp_xchg_sum: eps must be > 0");
+    B200_CUDA(cudaSetDevice(ctx->device));
+    return launch_tp_xchg_sum_norm_quant(ctx, xc, act_scale, x, gamma, eps, M, N, q, scale, normed);
+}
+
+int bitnet_b200_tp_xchg_max_actquant(bitnet_b200_ctx* ctx, const bitnet_b200_tp_xchg* xc, const float* x, int M, int K,
+                                     int8_t* q, float* scale) {
+    if (!ctx || !xc || !x || !q || !scale) return fail("tp_xchg_max: NULL argument");
+    B200_CUDA(cudaSetDevice(ctx->device));
+    return launch_tp_xchg_max_quant(ctx, xc, x, M, K, q, scale);
 }
 
 int bitnet_b200_rope_attn_decode(bitnet_b200_ctx* ctx, float* qkv, const float* cos_t, const float* sin_t, float* kc,

@@ -102,21 +102,25 @@ class Context:
         return (q, scale, normed) if (want_normed or normed is not None) else (q, scale)
 
     # ---- the ternary linear ------------------------------------------------------------
-    def linear_i8(self, w, q, act_scale, y=None, want_acc=False):
+    def linear_i8(self, w, q, act_scale, y=None, want_acc=False, acc_out=None):
+        """acc_out: write the int32 accumulators into this tensor (e.g. a peer-visible exchange buffer)."""
         torch = _torch()
         M = q.shape[0]
         if q.shape[1] != w.cols:
             raise ValueError("q has %d columns, weight has %d" % (q.shape[1], w.cols))
         y = torch.empty((M, w.rows), dtype=torch.float32, device=q.device) if y is None else y
-        acc = None
-        if want_acc:
+        acc = acc_out
+        if acc_out is not None:
+            if w.layout != LAYOUT_QK256 or acc_out.dtype != torch.int32 or acc_out.numel() != M * w.rows or not acc_out.is_contiguous():
+                raise ValueError("acc_out must be a contiguous int32 [M, rows] tensor of a QK256 weight")
+        elif want_acc:
             shape = (M, w.rows) if w.layout == LAYOUT_QK256 else (M, w.rows, w.cols // 32)
             # QK256: the kernel writes every accumulator; BitNet32-F16 blocks are zero-initialised
             acc = (torch.empty if w.layout == LAYOUT_QK256 else torch.zeros)(shape, dtype=torch.int32, device=q.device)
         ffi.check(self._lib.bitnet_b200_linear_i8(
             self._h, w._h, _dev_ptr(q, torch.int8, "q"), _dev_ptr(act_scale, torch.float32, "act_scale"),
             M, _dev_ptr(y, torch.float32, "y"), None if acc is None else acc.data_ptr()))
-        return (y, acc) if want_acc else y
+        return (y, acc) if (want_acc or acc_out is not None) else y
 
     def fused_linear(self, w, x, gamma=None, eps=1e-5, epilogue=EPI_STORE, y=None, residual=None, want_q=False):
         """[RMSNorm ->] act-quant -> ternary linear -> epilogue in ONE launch (decode, M <= 4)."""
@@ -146,12 +150,12 @@ class Context:
         return y
 
     # ---- tensor-parallel building blocks (Part 5) --------------------------------------
-    def row_absmax(self, x, swiglu=False):
+    def row_absmax(self, x, swiglu=False, absmax=None):
         """Per-token max|v| of the local slice; swiglu: x is [M,2K] interleaved (gate, up), returns (h, absmax)."""
         torch = _torch()
         M = x.shape[0]
         K = x.shape[1] // 2 if swiglu else x.shape[1]
-        am = torch.empty((M,), dtype=torch.float32, device=x.device)
+        am = torch.empty((M,), dtype=torch.float32, device=x.device) if absmax is None else absmax
         h = torch.empty((M, K), dtype=torch.float32, device=x.device) if swiglu else None
         ffi.check(self._lib.bitnet_b200_row_absmax(
             self._h, _dev_ptr(x, torch.float32, "x"), M, K, 1 if swiglu else 0,
@@ -168,6 +172,30 @@ class Context:
             self._h, _dev_ptr(x, torch.float32, "x"), _dev_ptr(absmax, torch.float32, "absmax"), M, K,
             _dev_ptr(q, torch.int8, "q"), _dev_ptr(scale, torch.float32, "scale")))
         return q, scale
+
+    def tp_xchg_max_actquant(self, xc, x, q=None, scale=None):
+        """all-reduce(MAX) of the per-token absmax pulled from the peers + quantise the local slice, one kernel."""
+        torch = _torch()
+        M, K = x.shape
+        q = torch.empty((M, K), dtype=torch.int8, device=x.device) if q is None else q
+        scale = torch.empty((M,), dtype=torch.float32, device=x.device) if scale is None else scale
+        ffi.check(self._lib.bitnet_b200_tp_xchg_max_actquant(
+            self._h, C.byref(xc), _dev_ptr(x, torch.float32, "x"), M, K, _dev_ptr(q, torch.int8, "q"),
+            _dev_ptr(scale, torch.float32, "scale")))
+        return q, scale
+
+    def tp_xchg_sum_rmsnorm_actquant(self, xc, act_scale, x, gamma, eps, q=None, scale=None, want_normed=False):
+        """all-reduce(SUM, int32) pulled from the peers + residual into x + RMSNorm + act-quant, one kernel."""
+        torch = _torch()
+        M, N = x.shape
+        q = torch.empty((M, N), dtype=torch.int8, device=x.device) if q is None else q
+        scale = torch.empty((M,), dtype=torch.float32, device=x.device) if scale is None else scale
+        normed = torch.empty((M, N), dtype=torch.float32, device=x.device) if want_normed else None
+        ffi.check(self._lib.bitnet_b200_tp_xchg_sum_rmsnorm_actquant(
+            self._h, C.byref(xc), _dev_ptr(act_scale, torch.float32, "act_scale"), _dev_ptr(x, torch.float32, "x"),
+            _dev_ptr(gamma, torch.float32, "gamma"), float(eps), M, N, _dev_ptr(q, torch.int8, "q"),
+            _dev_ptr(scale, torch.float32, "scale"), None if normed is None else normed.data_ptr()))
+        return (q, scale, normed) if want_normed else (q, scale)
 
     def residual_acc(self, acc, act_scale, x):
         """x += act_scale[m] * float(acc[m, n]) in place."""

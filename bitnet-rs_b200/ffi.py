@@ -27,7 +27,14 @@ SYMBOLS = [
     "bitnet_b200_model_weight_bytes",
     "bitnet_b200_row_absmax", "bitnet_b200_actquant_i8_absmax", "bitnet_b200_residual_acc",
     "bitnet_b200_rope_attn_decode",
+    "bitnet_b200_tp_xchg_sum_rmsnorm_actquant", "bitnet_b200_tp_xchg_max_actquant",
 ]
+
+
+class TpXchg(C.Structure):
+    """bitnet_b200_tp_xchg: one cross-GPU exchange point (include/bitnet_b200.h, Part 5)"""
+    _fields_ = [("peer_data", C.c_void_p * 8), ("peer_flags", C.c_void_p * 8), ("counters", C.c_void_p),
+                ("n_ranks", C.c_int), ("rank", C.c_int), ("slot", C.c_int), ("phase", C.c_int)]
 
 
 class ModelConfig(C.Structure):
@@ -112,6 +119,8 @@ def lib():
         l.bitnet_b200_actquant_i8_absmax.argtypes = [vp, vp, vp, i32, i32, vp, vp]
         l.bitnet_b200_residual_acc.argtypes = [vp, vp, vp, vp, i32, i32]
         l.bitnet_b200_rope_attn_decode.argtypes = [vp] * 7 + [i32] * 5 + [vp]
+        l.bitnet_b200_tp_xchg_sum_rmsnorm_actquant.argtypes = [vp, C.POINTER(TpXchg), vp, vp, vp, C.c_float, i32, i32, vp, vp, vp]
+        l.bitnet_b200_tp_xchg_max_actquant.argtypes = [vp, C.POINTER(TpXchg), vp, i32, i32, vp, vp]
         for fn in (l.bitnet_b200_qk256_gemv, l.bitnet_b200_qk256_gemv_scalar):
             fn.argtypes = [vp, sz, sz, sz, vp, sz, vp, sz, vp, sz]
         l.bitnet_b200_version.restype = C.c_char_p

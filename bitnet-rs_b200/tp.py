@@ -103,11 +103,73 @@ def shard_layer(shape, w, rank, tp):
 
 
 # --------------------------------------------------------------------------------------------
+class TpFabric:
+    """The peer-visible buffers of the fused exchanges (csrc/tp_xchg.cuh) for one rank and the pointers to every
+    rank's copy. Per rank, one block of `nbytes` laid out as
+        acc_o [M, H] i32 | acc_down [M, H] i32 | amax_o [M] f32 | amax_down [M] f32 | flags [4][8] u32
+    `local` is this rank's block as a uint8 tensor, `bases[r]` the address of rank r's block on THIS device."""
+    SLOT_O_MAX, SLOT_O_SUM, SLOT_DOWN_MAX, SLOT_DOWN_SUM = 0, 1, 2, 3
+
+    @staticmethod
+    def nbytes(M, H):
+        return 2 * M * H * 4 + 2 * M * 4 + 4 * 8 * 4
+
+    def __init__(self, torch, local, bases, rank, M, H):
+        self.torch, self.local, self.bases, self.rank, self.n = torch, local, list(bases), rank, len(bases)
+        self.M, self.H = M, H
+        o = 0
+        self.off = {}
+        for name, n in (("acc_o", M * H * 4), ("acc_down", M * H * 4), ("amax_o", M * 4), ("amax_down", M * 4), ("flags", 128)):
+            self.off[name] = o
+            o += n
+        self.acc_o = local[self.off["acc_o"]:self.off["acc_o"] + M * H * 4].view(torch.int32).view(M, H)
+        self.acc_down = local[self.off["acc_down"]:self.off["acc_down"] + M * H * 4].view(torch.int32).view(M, H)
+        self.amax_o = local[self.off["amax_o"]:self.off["amax_o"] + M * 4].view(torch.float32)
+        self.amax_down = local[self.off["amax_down"]:self.off["amax_down"] + M * 4].view(torch.float32)
+        self.counters = torch.zeros(8, dtype=torch.int32, device=local.device)   # local, not peer-visible
+        self._data_of = {self.SLOT_O_MAX: "amax_o", self.SLOT_O_SUM: "acc_o", self.SLOT_DOWN_MAX: "amax_down",
+                         self.SLOT_DOWN_SUM: "acc_down"}
+
+    @classmethod
+    def emulated(cls, torch, device, n_ranks, M, H):
+        """n_ranks fabrics on ONE device (tests): plain device tensors, every 'peer' pointer is local."""
+        blocks = [torch.zeros(cls.nbytes(M, H), dtype=torch.uint8, device=device) for _ in range(n_ranks)]
+        bases = [b.data_ptr() for b in blocks]
+        return [cls(torch, blocks[r], bases, r, M, H) for r in range(n_ranks)]
+
+    @classmethod
+    def symmetric(cls, torch, dist, device, M, H):
+        """One rank per GPU: torch symmetric memory (P2P-mapped over NVLink) is the plumbing for the addresses."""
+        import torch.distributed._symmetric_memory as symm_mem
+        local = symm_mem.empty(cls.nbytes(M, H), dtype=torch.uint8, device=device)
+        local.zero_()
+        hdl = symm_mem.rendezvous(local, dist.group.WORLD)
+        torch.cuda.synchronize()
+        dist.barrier()
+        fab = cls(torch, local, [int(p) for p in hdl.buffer_ptrs], dist.get_rank(), M, H)
+        fab._hdl = hdl
+        return fab
+
+    def desc(self, slot, phase):
+        from . import ffi
+        xc = ffi.TpXchg()
+        for r in range(self.n):
+            xc.peer_data[r] = self.bases[r] + self.off[self._data_of[slot]]
+            xc.peer_flags[r] = self.bases[r] + self.off["flags"]
+        xc.counters = self.counters.data_ptr()
+        xc.n_ranks, xc.rank, xc.slot, xc.phase = self.n, self.rank, slot, phase
+        return xc
+
+
+# --------------------------------------------------------------------------------------------
 class TPDecoder:
     """One rank's shard of a ternary decoder; `step_gen` yields ("max" | "sum" | "gather", tensor)
     at every exchange and expects the tensor to hold the reduced value when resumed."""
 
-    def __init__(self, ctx, shape, rank=0, tp=1, layer_fn=fast_layer, n_layers=None):
+    def __init__(self, ctx, shape, rank=0, tp=1, layer_fn=fast_layer, n_layers=None, fabric=None, emulated=False):
+        """fabric: a TpFabric -> the exchanges are pulled by the consumer kernels themselves (no collective calls);
+        emulated: several ranks share one GPU, so every exchange kernel is split into a signal launch and a work
+        launch with a lockstep point between them."""
         import torch
         if shape.layout != LAYOUT_QK256:
             raise ValueError("the TP decoder covers the QK256 layout (int32 partials reduce exactly)")
@@ -138,6 +200,7 @@ class TPDecoder:
         self.emb_shard = self.emb[self.v0:self.v0 + shape.vocab // tp]
         self.weight_bytes = sum(e[k].nbytes for e in self.layers for k in ("wqkv", "wo", "wgu", "wdown"))
         self._pos_host = 0   # host mirror of self.pos: the kernels index the caches and RoPE tables with it unchecked
+        self.fabric, self.emulated = fabric, emulated
 
     def reset(self):
         self.pos.zero_()
@@ -166,6 +229,44 @@ class TPDecoder:
             yield "sum", acc
             ctx.residual_acc(acc, sd, x)
 
+    def _xchg(self, slot, fn):
+        """Run exchange kernel fn(desc) for `slot`: one launch on a real rank; signal, lockstep point, work when emulated."""
+        if self.emulated:
+            fn(self.fabric.desc(slot, 1))
+            yield "sync", None
+            return fn(self.fabric.desc(slot, 2))
+        return fn(self.fabric.desc(slot, 3))
+        yield  # pragma: no cover (makes this a generator in both branches)
+
+    def layers_fused_gen(self, x):
+        """layers_gen with the four exchanges of a layer fused into their consumers (csrc/tp_xchg.cuh): 11 launches per
+        layer, no collective call. Returns the final-norm output (the last exchange applies the final norm)."""
+        ctx, s, fab = self.ctx, self.shape, self.fabric
+        q8, s8 = ctx.rmsnorm_actquant(x, self.layers[0]["attn_norm"], s.rms_eps)
+        xn = None
+        for l, L in enumerate(self.layers):
+            qkv = ctx.linear_i8(L["wqkv"], q8, s8)
+            att = ctx.rope_attn_decode(qkv, self.cos, self.sin, self.kc[l], self.vc[l], self.pos, self.nh, self.nkv,
+                                       s.head_dim, s.max_ctx)
+            ctx.row_absmax(att, absmax=fab.amax_o)
+            q8o, so = yield from self._xchg(fab.SLOT_O_MAX, lambda d: ctx.tp_xchg_max_actquant(d, att))
+            ctx.linear_i8(L["wo"], q8o, so, acc_out=fab.acc_o)
+            q8, s8 = yield from self._xchg(fab.SLOT_O_SUM, lambda d: ctx.tp_xchg_sum_rmsnorm_actquant(
+                d, so, x, L["ffn_norm"], s.rms_eps))
+            gu = ctx.linear_i8(L["wgu"], q8, s8)
+            h, _ = ctx.row_absmax(gu, swiglu=True, absmax=fab.amax_down)
+            q8d, sd = yield from self._xchg(fab.SLOT_DOWN_MAX, lambda d: ctx.tp_xchg_max_actquant(d, h))
+            ctx.linear_i8(L["wdown"], q8d, sd, acc_out=fab.acc_down)
+            last = l + 1 == len(self.layers)
+            gamma = self.final_norm if last else self.layers[l + 1]["attn_norm"]
+            r = yield from self._xchg(fab.SLOT_DOWN_SUM, lambda d: ctx.tp_xchg_sum_rmsnorm_actquant(
+                d, sd, x, gamma, s.rms_eps, want_normed=last))
+            if last:
+                xn = r[2]
+            else:
+                q8, s8 = r
+        return xn
+
     def step_gen(self):
         """One greedy decode step: self.tokens [B] -> self.tokens, self.pos += 1."""
         torch, s = self.torch, self.shape
@@ -173,16 +274,33 @@ class TPDecoder:
             raise ValueError("TPDecoder: context full (position %d, max_ctx %d): call reset()" % (self._pos_host, s.max_ctx))
         self._pos_host += 1
         x = self.emb[self.tokens].float()
-        yield from self.layers_gen(x)
-        _, _, xn = self.ctx.rmsnorm_actquant(x, self.final_norm, s.rms_eps, want_normed=True)
-        logits = torch.matmul(xn.half(), self.emb_shard.t()).float()              # library GEMM, vocab shard
-        val, idx = logits.max(dim=1)
+        if self.fabric is not None:
+            xn = yield from self.layers_fused_gen(x)
+        else:
+            yield from self.layers_gen(x)
+            _, _, xn = self.ctx.rmsnorm_actquant(x, self.final_norm, s.rms_eps, want_normed=True)
+        # LM head on the vocabulary shard: a library f16 GEMM (outside the ternary path). The f32 row is
+        # fed as hi + lo f16 halves (xn = hi + lo to ~2^-22), so the logits are those of f32 activations x f16 weights
+        # up to fp32 summation order -- not the f16-rounded activations of round 1 -- and ties go to the LOWEST index,
+        # as the device argmax of the single-GPU path does (torch.max / argmax do not promise that).
+        hi = xn.half()
+        lo = (xn - hi.float()).half()
+        try:     # f16 x f16 with an f32 result (aten::mm.dtype, CUDA): the f16 output rounding would undo the split
+            both = torch.mm(torch.cat([hi, lo], dim=0), self.emb_shard.t(), out_dtype=torch.float32)
+        except (TypeError, RuntimeError, NotImplementedError):
+            both = torch.matmul(torch.cat([hi, lo], dim=0), self.emb_shard.t()).float()
+        logits = both[:s.batch] + both[s.batch:]
+        val = logits.max(dim=1).values
+        big = torch.iinfo(torch.int64).max
+        ar = torch.arange(logits.shape[1], device=self.dev)
+        idx = torch.where(logits == val[:, None], ar[None, :], torch.full_like(ar, big)[None, :]).min(dim=1).values
         pair = torch.stack([val, (idx + self.v0).float()], dim=1).contiguous()    # [B, 2]
         gathered = torch.empty((self.tp, s.batch, 2), dtype=torch.float32, device=self.dev)
         gathered[self.rank] = pair
         yield "gather", gathered                                                    # all ranks' (max, argmax)
-        best = gathered[:, :, 0].argmax(dim=0)
-        self.tokens.copy_(gathered[best, torch.arange(s.batch, device=self.dev), 1].long())
+        gv, gi = gathered[:, :, 0], gathered[:, :, 1]
+        best = gv.max(dim=0).values
+        self.tokens.copy_(torch.where(gv == best[None, :], gi, torch.full_like(gi, float(s.vocab))).min(dim=0).values.long())
         self.pos += 1
         self.last_hidden = x
 
@@ -190,6 +308,8 @@ class TPDecoder:
 def run_distributed(gen, dist, group=None):
     """Drive one rank's generator with torch.distributed collectives (NCCL) on the current stream."""
     for op, t in gen:
+        if op == "sync":
+            continue
         if op == "max":
             dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
         elif op == "sum":
@@ -215,6 +335,8 @@ def run_emulated(gens):
             raise RuntimeError("ranks fell out of lockstep")
         op = ys[0][0]
         ts = [y[1] for y in ys]
+        if op == "sync":
+            continue
         if op == "max":
             r = torch.stack(ts).amax(dim=0)
             for t in ts:

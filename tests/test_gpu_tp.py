@@ -79,3 +79,109 @@ def test_decoder_tp_equals_tp1(ctx, b200, tp_n):
             assert torch.equal(d.last_hidden, ref.last_hidden), "hidden state differs at step %d" % step
             assert torch.equal(d.tokens, ref.tokens)
     assert int(ref.pos) == 4
+
+
+# ---- fused exchanges: the consumer kernels pull their peers' buffers themselves (csrc/tp_xchg.cuh) ---------------
+@pytest.mark.parametrize("tp_n", [1, 2, 4])
+def test_decoder_fused_exchanges_equal_collective_path(ctx, b200, tp_n):
+    # same shards, same kernels around the exchanges; the all-reduces are replaced by kernels that read the peers'
+    # partial accumulators / absmax directly (here: N emulated ranks on one GPU, signal and work launches split).
+    # Bar: hidden state and tokens bit-identical to the tp = 1 decoder that uses no exchange at all.
+    from bitnet_rs_b200 import tp
+    shape = b200.ModelShape(hidden=1024, ffn=2048, n_layers=2, n_heads=8, n_kv_heads=4, head_dim=128,
+                            vocab=4096, max_ctx=16, batch=16)
+    ref = b200.TPDecoder(ctx, shape, 0, 1)
+    fabs = b200.TpFabric.emulated(torch, torch.device("cuda", 0), tp_n, shape.batch, shape.hidden)
+    ranks = [b200.TPDecoder(ctx, shape, r, tp_n, fabric=fabs[r], emulated=True) for r in range(tp_n)]
+    tok0 = (torch.arange(shape.batch, device="cuda") * 7919) % shape.vocab
+    for d in [ref] + ranks:
+        d.tokens.copy_(tok0)
+    for step in range(5):
+        tp.run_emulated([ref.step_gen()])
+        tp.run_emulated([d.step_gen() for d in ranks])
+        for d in ranks:
+            assert torch.equal(d.last_hidden, ref.last_hidden), "hidden state differs at step %d" % step
+            assert torch.equal(d.tokens, ref.tokens)
+    assert int(ranks[0].fabric.counters[0]) == 5 * shape.n_layers       # one epoch per exchange and slot
+
+
+def test_fused_exchange_kernels_match_the_three_step_form(ctx, b200, oracle):
+    # tp_xchg_sum_rmsnorm_actquant == all-reduce(SUM) ; residual_acc ; rmsnorm_actquant, bit for bit, incl. `normed`
+    M, H, n = 7, 4096, 4
+    fabs = b200.TpFabric.emulated(torch, torch.device("cuda", 0), n, M, H)
+    g = torch.Generator(device="cuda").manual_seed(3)
+    parts = [torch.randint(-200000, 200000, (M, H), dtype=torch.int32, device="cuda", generator=g) for _ in range(n)]
+    for r in range(n):
+        fabs[r].acc_down.copy_(parts[r])
+    sc = torch.rand(M, device="cuda", generator=g) * 1e-3
+    gamma = torch.rand(H, device="cuda", generator=g) + 0.5
+    x0 = torch.randn(M, H, device="cuda", generator=g)
+    total = torch.stack(parts).sum(dim=0, dtype=torch.int32)
+    xr = x0.clone()
+    ctx.residual_acc(total, sc, xr)
+    qr, sr, nr = ctx.rmsnorm_actquant(xr, gamma, 1e-5, want_normed=True)
+    for r in range(n):
+        ctx.tp_xchg_sum_rmsnorm_actquant(fabs[r].desc(fabs[r].SLOT_DOWN_SUM, 1), sc, x0, gamma, 1e-5)   # signal only
+    for r in range(n):
+        x = x0.clone()
+        q, s, nm = ctx.tp_xchg_sum_rmsnorm_actquant(fabs[r].desc(fabs[r].SLOT_DOWN_SUM, 2), sc, x, gamma, 1e-5, want_normed=True)
+        assert torch.equal(x, xr) and torch.equal(q, qr) and torch.equal(s, sr) and torch.equal(nm, nr)
+    # absmax exchange
+    K = 1536
+    xs = [torch.randn(M, K, device="cuda", generator=g) * (r + 1) for r in range(n)]
+    for r in range(n):
+        ctx.row_absmax(xs[r], absmax=fabs[r].amax_o)
+    am = torch.stack([f.amax_o for f in fabs]).amax(dim=0)
+    for r in range(n):
+        ctx.tp_xchg_max_actquant(fabs[r].desc(fabs[r].SLOT_O_MAX, 1), xs[r])
+    for r in range(n):
+        q, s = ctx.tp_xchg_max_actquant(fabs[r].desc(fabs[r].SLOT_O_MAX, 2), xs[r])
+        q2, s2 = ctx.actquant_i8_absmax(xs[r], am)
+        assert torch.equal(q, q2) and torch.equal(s, s2)
+
+
+def test_tp1_decoder_matches_the_oracle_model(ctx, b200, oracle):
+    # the decoder-level glue of the TP path (tp_rope_kv / tp_attn_decode kernels, vocabulary-sharded LM head with
+    # lowest-index ties) against the CPU oracle model on a small GQA shape, batch > 1: same greedy tokens
+    from bitnet_rs_b200 import tp
+    shape = b200.ModelShape(hidden=512, ffn=1024, n_layers=2, n_heads=8, n_kv_heads=2, head_dim=64,
+                            vocab=2048, max_ctx=16, batch=3)
+    dec = b200.TPDecoder(ctx, shape, 0, 1)
+    om = oracle.Model(shape, n_seqs=shape.batch)
+    for l in range(shape.n_layers):
+        om.set_layer(l, tp.fast_layer(shape, l))
+    emb, fn = b200.synth_embedding(shape)
+    om.set_embedding(emb, fn)
+    om.set_rope(*b200.rope_tables(shape))
+    toks = [5, 77, 1234]
+    dec.tokens.copy_(torch.tensor(toks, device="cuda"))
+    for step in range(6):
+        tp.run_emulated([dec.step_gen()])
+        toks = [om.step(t, seq=b) for b, t in enumerate(toks)]
+        assert dec.tokens.cpu().tolist() == toks, "step %d" % step
+    om.close()
+
+
+def test_8b_geometry_two_layer_decoder_matches_the_oracle_model(ctx, b200, oracle):
+    # configs[4] geometry (hidden 4096, FFN 14336, GQA 32/8, head 128), 2 layers, small vocabulary: the tp = 2 fused
+    # path against the CPU oracle model
+    from bitnet_rs_b200 import tp
+    shape = b200.ModelShape(hidden=4096, ffn=14336, n_layers=2, n_heads=32, n_kv_heads=8, head_dim=128,
+                            vocab=1024, max_ctx=8, batch=2)
+    fabs = b200.TpFabric.emulated(torch, torch.device("cuda", 0), 2, shape.batch, shape.hidden)
+    ranks = [b200.TPDecoder(ctx, shape, r, 2, fabric=fabs[r], emulated=True) for r in range(2)]
+    om = oracle.Model(shape, n_seqs=shape.batch)
+    for l in range(shape.n_layers):
+        om.set_layer(l, tp.fast_layer(shape, l))
+    emb, fn = b200.synth_embedding(shape)
+    om.set_embedding(emb, fn)
+    om.set_rope(*b200.rope_tables(shape))
+    toks = [11, 900]
+    for d in ranks:
+        d.tokens.copy_(torch.tensor(toks, device="cuda"))
+    for step in range(4):
+        tp.run_emulated([d.step_gen() for d in ranks])
+        toks = [om.step(t, seq=b) for b, t in enumerate(toks)]
+        for d in ranks:
+            assert d.tokens.cpu().tolist() == toks, "step %d" % step
+    om.close()
