@@ -41,7 +41,7 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--layout", default="qk256", choices=["qk256", "bitnet32"])
     ap.add_argument("--prompt", type=int, default=32, help="synthetic prompt tokens decoded before timing")
-    ap.add_argument("--workload", default="2b4t-decode", choices=["2b4t-decode", "8b-tp", "sweep"],
+    ap.add_argument("--workload", default="2b4t-decode", choices=["2b4t-decode", "8b-tp", "sweep", "prefill"],
                     help="2b4t-decode = BASELINE.json configs[1] (the judged line); 8b-tp = configs[4]: 8B-class "
                          "batch-64 decode, tensor-parallel over the launched ranks (NCCL all-reduce)")
     ap.add_argument("--tp-layers", type=int, default=0, help="8b-tp: use fewer layers (smoke runs only)")
@@ -49,6 +49,9 @@ def parse():
     ap.add_argument("--cpu-budget-s", type=float, default=20.0)
     ap.add_argument("--tp-exchange", choices=["fused", "nccl", "both"], default="both",
                     help="8b-tp workload: how the row-parallel layers exchange (fused NVLink pulls, NCCL collectives, or both)")
+    ap.add_argument("--prefill-layers", type=int, default=30)
+    ap.add_argument("--no-fused-epilogue", action="store_true", help="prefill: the round-1 pipeline (stand-alone SwiGLU pass)")
+    ap.add_argument("--no-gemm-record", action="store_true", help="skip the prefill GEMM sub-record of the default line")
     ap.add_argument("--no-tp", action="store_true", help="N > 1: skip the tensor-parallel sub-record of the default workload")
     return ap.parse_args()
 
@@ -71,6 +74,8 @@ class ClockSampler:
         self.index, self.rows, self.proc = index, [], None
 
     def start(self):
+        if os.environ.get("BENCH_NO_CLOCKS"):   # diagnostics: is the poller itself visible in the number?
+            return
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
@@ -337,6 +342,143 @@ def run_tp(args):
         dist.destroy_process_group()
 
 
+def int8_library_peak(torch, sustained_iters=60):
+    """cuBLASLt int8 GEMM 8192^3 (torch._int_mm) timed in THIS run: the library denominator beside the 4 500 TOPS nominal."""
+    n = 8192
+    a = torch.randint(-127, 128, (n, n), dtype=torch.int8, device="cuda")
+    b = torch.randint(-127, 128, (n, n), dtype=torch.int8, device="cuda").t().contiguous().t()
+    for _ in range(3):
+        torch._int_mm(a, b)
+    torch.cuda.synchronize()
+    best = 1e30
+    for _ in range(5):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        torch._int_mm(a, b)
+        e1.record()
+        torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(sustained_iters):
+        torch._int_mm(a, b)
+    e1.record()
+    torch.cuda.synchronize()
+    ops = 2.0 * n ** 3
+    return ops / best / 1e9, ops / (e0.elapsed_time(e1) / sustained_iters) / 1e9
+
+
+def prefill_measure(torch, b2, ctx, tokens, batch, n_layers, reps, fused=True):
+    """BASELINE.json configs[3]: the ternary-linear pipeline of a 2B-4T-shape prefill (M = tokens * batch rows) --
+    RMSNorm+act-quant, qkv GEMM, act-quant, o GEMM, RMSNorm+act-quant, gate/up GEMM (+ SwiGLU in its epilogue when
+    `fused`), act-quant, down GEMM -- per layer, CUDA events. Attention is outside the ternary path:
+    the act-quant before o reads a stand-in buffer of the attention output's shape."""
+    from bitnet_rs_b200 import tp
+    M = tokens * batch
+    s = b2.ModelShape.bitnet_2b4t()
+    H, F, QD = s.hidden, s.ffn, s.n_heads * s.head_dim
+    layers = []
+    for l in range(n_layers):
+        w = tp.shard_layer(s, tp.fast_layer(s, l), 0, 1)          # tp = 1: the fused qkv / interleaved gate-up tensors
+        ent = {k: ctx.weight(w[k][0], s.layout, w[k][1], w[k][2]) for k in ("wqkv", "wo", "wgu", "wdown")}
+        ent["attn_norm"] = torch.from_numpy(w["attn_norm"]).cuda()
+        ent["ffn_norm"] = torch.from_numpy(w["ffn_norm"]).cuda()
+        layers.append(ent)
+    x = torch.randn(M, H, device="cuda")
+    att = torch.randn(M, QD, device="cuda")
+    qH = torch.empty(M, H, dtype=torch.int8, device="cuda")
+    qQ = torch.empty(M, QD, dtype=torch.int8, device="cuda")
+    qF = torch.empty(M, F, dtype=torch.int8, device="cuda")
+    sc = torch.empty(M, device="cuda")
+    qkv = torch.empty(M, QD + 2 * s.n_kv_heads * s.head_dim, device="cuda")
+    y = torch.empty(M, H, device="cuda")
+    gu = None if fused else torch.empty(M, 2 * F, device="cuda")
+    h = torch.empty(M, F, device="cuda")
+
+    def one_pass():
+        for L in layers:
+            ctx.rmsnorm_actquant(x, L["attn_norm"], s.rms_eps, q=qH, scale=sc)
+            ctx.linear_i8(L["wqkv"], qH, sc, y=qkv)
+            ctx.actquant_i8(att, q=qQ, scale=sc)
+            ctx.linear_i8(L["wo"], qQ, sc, y=y)
+            ctx.rmsnorm_actquant(y, L["ffn_norm"], s.rms_eps, q=qH, scale=sc)
+            if fused:
+                ctx.linear_i8_swiglu(L["wgu"], qH, sc, h=h)
+                ctx.actquant_i8(h, q=qF, scale=sc)
+            else:
+                ctx.linear_i8(L["wgu"], qH, sc, y=gu)
+                h2, am = ctx.row_absmax(gu, swiglu=True)
+                ctx.actquant_i8_absmax(h2, am, q=qF, scale=sc)
+            ctx.linear_i8(L["wdown"], qF, sc, y=y)
+
+    def gemms():
+        for L in layers:
+            ctx.linear_i8(L["wqkv"], qH, sc, y=qkv)
+            ctx.linear_i8(L["wo"], qQ, sc, y=y)
+            if fused:
+                ctx.linear_i8_swiglu(L["wgu"], qH, sc, h=h)
+            else:
+                ctx.linear_i8(L["wgu"], qH, sc, y=gu)
+            ctx.linear_i8(L["wdown"], qF, sc, y=y)
+
+    def best_of(fn):
+        fn()
+        torch.cuda.synchronize()
+        best = 1e30
+        for _ in range(reps):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn()
+            e1.record()
+            torch.cuda.synchronize()
+            best = min(best, e0.elapsed_time(e1))
+        return best
+
+    l0 = b2.launch_count()
+    one_pass()
+    launches = b2.launch_count() - l0
+    ms_all, ms_gemm = best_of(one_pass), best_of(gemms)
+    # the gate/up GEMM alone (the largest; K = 2560)
+    L = layers[0]
+    ms_gu = best_of(lambda: [ctx.linear_i8_swiglu(L["wgu"], qH, sc, h=h) if fused else ctx.linear_i8(L["wgu"], qH, sc, y=gu) for _ in range(4)]) / 4
+    per_layer = sum(r * c for r, c in s.proj_shapes().values())
+    ops = 2.0 * M * per_layer * n_layers
+    return {"M": M, "n_layers": n_layers, "ms_linears_and_quant": ms_all, "ms_gemm_only": ms_gemm, "int8_TOP": ops / 1e12,
+            "TOPS_gemm_only": ops / ms_gemm / 1e9, "TOPS_with_quant": ops / ms_all / 1e9, "launches_per_pass": int(launches),
+            "gateup_ms": ms_gu, "gateup_TOPS": 2.0 * M * 2 * F * H / ms_gu / 1e9, "fused_swiglu_epilogue": bool(fused),
+            "prefill_tok_per_s_linears_only": M / (ms_all * 1e-3)}
+
+
+def run_prefill(args):
+    """--workload prefill: BASELINE.json configs[3], one JSON line (tensor-bound roofline)."""
+    import torch
+    import bitnet_rs_b200 as b2
+    torch.cuda.set_device(0)
+    ctx = b2.Context(0)
+    sampler = ClockSampler(0)
+    sampler.start()
+    r = prefill_measure(torch, b2, ctx, 2048, 8, args.prefill_layers, 3, fused=not args.no_fused_epilogue)
+    clocks = sampler.stop()
+    burst, sustained = int8_library_peak(torch)
+    line = {
+        "metric": "2B-4T prefill int8 TOPS (ternary linears + act-quant)", "value": r["TOPS_with_quant"], "unit": "TOPS",
+        "n_gpus": 1, "steps": 3, "warmup": 1, "ms_per_step": r["ms_linears_and_quant"], "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "int8", "data": "synthetic",
+        "config": {"workload": "2B-4T-shape prefill of a 2048-token synthetic prompt, batch 8 (M = %d token rows), %d layers, "
+                               "QK256, tcgen05 kind::i8 GEMM path; linears + act-quant, attention not run "
+                               "(BASELINE.json configs[3])" % (r["M"], r["n_layers"]),
+                   "l2": "per layer 1.2 GB of activations / outputs stream through HBM (> 126 MB L2)"},
+        "clocks": clocks, "gpu_launches": r["launches_per_pass"] * 3, "launches_per_step": r["launches_per_pass"],
+        "roofline": {"bound": "tensor", "kernel": "gemm_i8_tcgen05_kernel, all four projections of %d layers" % r["n_layers"],
+                     "achieved": r["TOPS_gemm_only"] / 1e3, "peak": 4.5, "unit": "PFLOP/s (int8 ops)", "frac": r["TOPS_gemm_only"] / 4500.0,
+                     "peak_source": "nominal dense int8 4.5 POPS (MEASURED_PEAKS.json holds no int8 figure)",
+                     "library_int8_TOPS_burst": burst, "library_int8_TOPS_sustained": sustained,
+                     "frac_of_library_sustained": r["TOPS_gemm_only"] / sustained, "traffic": None},
+        "prefill": r,
+    }
+    print(json.dumps(line), flush=True)
+
+
 def _sweep_weight_bytes(rng, layout_name, rows, cols):
     if layout_name == "qk256":
         return rng.integers(0, 256, rows * cols // 4, dtype=np.uint8)
@@ -463,6 +605,8 @@ def main():
         return run_tp(args)
     if args.workload == "sweep":
         return run_sweep(args)
+    if args.workload == "prefill":
+        return run_prefill(args)
 
     import torch
     import bitnet_rs_b200 as b2
@@ -548,6 +692,19 @@ def main():
     except Exception:
         pass
 
+    # ---- N = 1: the prefill regime in short (BASELINE.json configs[3]): 2 layers' worth of the M = 16384 pipeline ----
+    gemm_rec = None
+    if world == 1 and not args.no_gemm_record:
+        try:
+            r = prefill_measure(torch, b2, ctx, 2048, 8, 2, 2, fused=True)
+            gemm_rec = {"workload": "2B-4T-shape prefill, 2048 tokens x batch 8 (M = 16384), 2 of the 30 layers (identical shapes), "
+                                    "tcgen05 kind::i8 GEMM path with the SwiGLU epilogue; `bench.py --workload prefill` runs all 30",
+                        "TOPS_gemm_only": r["TOPS_gemm_only"], "TOPS_with_quant": r["TOPS_with_quant"],
+                        "gateup_M16384_TOPS": r["gateup_TOPS"], "gateup_ms": r["gateup_ms"],
+                        "frac_of_4500_TOPS_nominal": r["TOPS_gemm_only"] / 4500.0, "ms_per_layer": r["ms_linears_and_quant"] / 2}
+        except Exception as ex:
+            gemm_rec = {"error": "%s: %s" % (type(ex).__name__, str(ex)[:200])}
+
     # ---- N > 1: the Megatron path on the same ranks (BASELINE.json configs[4]) --------------------
     tp_rec = None
     if dist is not None and not args.no_tp:
@@ -600,6 +757,8 @@ def main():
         }
         if tp_rec is not None:
             line["tp"] = tp_rec
+        if gemm_rec is not None:
+            line["gemm"] = gemm_rec
         if world == 1 and not args.no_cpu_baseline:
             try:
                 v, cores, sample, _, _, single = cpu_decode_tok_s(shape, 8, 1, args.cpu_budget_s)

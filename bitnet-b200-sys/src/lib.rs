@@ -109,6 +109,10 @@ extern "C" {
         ctx: *mut bitnet_b200_ctx, w: *const bitnet_b200_weight, q: *const i8, act_scale: *const c_float, m: c_int,
         y: *mut c_float, acc_out: *mut i32,
     ) -> c_int;
+    pub fn bitnet_b200_linear_i8_swiglu(
+        ctx: *mut bitnet_b200_ctx, w: *const bitnet_b200_weight, q: *const i8, act_scale: *const c_float, m: c_int,
+        h: *mut c_float,
+    ) -> c_int;
     pub fn bitnet_b200_fused_linear(
         ctx: *mut bitnet_b200_ctx, w: *const bitnet_b200_weight, x: *const c_float, gamma: *const c_float,
         eps: c_float, m: c_int, epilogue: c_int, y: *mut c_float, residual: *const c_float, q_out: *mut i8,

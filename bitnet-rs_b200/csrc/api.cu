@@ -33,7 +33,7 @@ int launch_gemv_fast(const bitnet_b200_ctx*, const bitnet_b200_weight*, int M, i
                        const float* residual, int32_t* acc_out, int8_t* q_out, float* scale_out, float* normed_out,
                        bool pdl);
 int launch_gemm_i8(const bitnet_b200_ctx*, const bitnet_b200_weight*, const int8_t*, const float*,
-                   int, float*, int32_t*);
+                   int, float*, int32_t*, float*);
 bool gemm_i8_supported(const bitnet_b200_weight*, int M);
 int launch_gemm_f16(const bitnet_b200_ctx*, const bitnet_b200_weight*, const int8_t*, const float*, int, float*);
 bool gemm_f16_supported(const bitnet_b200_weight*, int M);
@@ -416,7 +416,7 @@ int bitnet_b200_linear_i8(bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, con
     // per-32-block accumulators are only materialised by the GEMV
     const bool force_gemv = acc_out && w->layout == BITNET_B200_LAYOUT_BITNET32_F16;
     if (!force_gemv && gemm_i8_supported(w, M))
-        return launch_gemm_i8(ctx, w, q, act_scale, M, y, acc_out);
+        return launch_gemm_i8(ctx, w, q, act_scale, M, y, acc_out, nullptr);
     if (!acc_out && gemm_f16_supported(w, M))  // BitNet32-F16, M >= 9: tcgen05 kind::f16 on s * LUT[code]
         return launch_gemm_f16(ctx, w, q, act_scale, M, y);
     if (M <= 8 && !getenv("BITNET_B200_NO_STREAM")) {  // decode fast path (gemv_stream.cu); 1 = shape not covered
@@ -426,6 +426,18 @@ int bitnet_b200_linear_i8(bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, con
         if (rc != 1) return rc;
     }
     return launch_gemv_i8(ctx, w, q, act_scale, M, y, acc_out, nullptr);
+}
+
+int bitnet_b200_linear_i8_swiglu(bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, const int8_t* q, const float* act_scale,
+                                 int M, float* h) {
+    if (!ctx || !w || !q || !act_scale || !h) return fail("linear_i8_swiglu: NULL argument");
+    if (M <= 0) return fail("linear_i8_swiglu: M must be > 0");
+    if (w->device != ctx->device) return fail("linear_i8_swiglu: weight lives on another device");
+    if (w->rows & 1) return fail("linear_i8_swiglu: the weight needs interleaved (gate, up) rows, i.e. an even row count");
+    B200_CUDA(cudaSetDevice(ctx->device));
+    if (!gemm_i8_supported(w, M))
+        return fail("linear_i8_swiglu: batched / prefill path only (QK256, M >= 9, cols % 128 == 0); decode uses fused_linear(EPI_SWIGLU)");
+    return launch_gemm_i8(ctx, w, q, act_scale, M, nullptr, nullptr, h);
 }
 
 int bitnet_b200_fused_linear(bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, const float* x,

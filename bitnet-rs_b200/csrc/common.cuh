@@ -153,6 +153,24 @@ __device__ __forceinline__ uint4 decode16(uint32_t w, uint32_t lut) {
     return make_uint4(prmt(lut, 0u, x), prmt(lut, 0u, y), prmt(lut, 0u, x >> 16), prmt(lut, 0u, y >> 16));
 }
 
+// The same decode with the three shifts issued as IMAD.HI on the FMA pipe. Slower where the decode feeds mma.sync
+// directly (above), but the tcgen05 GEMM's decoder warps, which also issue the shared-memory stores of the expanded
+// tile, measured 12 % faster with it (gate/up at M = 16384: 0.56 ms vs 0.71 ms with SHF).
+__device__ __forceinline__ uint4 decode16_fma(uint32_t w, uint32_t lut) {
+    const uint32_t x = w & 0x33333333u;
+    const uint32_t y = __umulhi(w, 0x40000000u) & 0x33333333u;
+    return make_uint4(prmt(lut, 0u, x), prmt(lut, 0u, y), prmt(lut, 0u, __umulhi(x, 0x10000u)),
+                      prmt(lut, 0u, __umulhi(y, 0x10000u)));
+}
+
+// SwiGLU glue silu(g) * u (crates/bitnet-transformer/src/lib.rs:756-789), ONE formula for every kernel that applies
+// it (decode epilogues, the GEMM epilogue, the stand-alone passes), so all paths agree bit for bit:
+//   g / (1 + exp(-g)) with the accurate expf and the approximate division (MUFU.RCP-based, <= 2 ulp).
+// The IEEE division it replaces took its slow path (a ~100-instruction subroutine) whenever exp(-g) overflowed to
+// inf or the quotient was denormal -- every strongly negative gate -- which made the GEMM's SwiGLU epilogue 4.6 x
+// slower than its MMA loop. __fdividef(g, inf) = -0 for g < 0, exactly what g / inf gives.
+__device__ __forceinline__ float silu_mul(float g, float u) { return __fmul_rn(__fdividef(g, 1.0f + expf(-g)), u); }
+
 // ---- PTX: mbarrier, 1-D bulk copy (TMA), programmatic dependent launch ----------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(void* bar, uint32_t count) {

@@ -527,7 +527,7 @@ __device__ __forceinline__ void mega_gemv_phase(const MegaParams& p, const MegaS
 #pragma unroll
             for (int j = 1; j < MEGA_MAXB; ++j) as = m == j ? sc[j] : as;
             const float v0 = __fmul_rn(as, (float)a0), v1 = __fmul_rn(as, (float)a1);
-            ll_store(out, (size_t)m * half + q.t0 * 8 + pr, __fmul_rn(v0 / (1.0f + expf(-v0)), v1), ep_out);
+            ll_store(out, (size_t)m * half + q.t0 * 8 + pr, silu_mul(v0, v1), ep_out);
         }
     } else if (tid < nout) {
         int a = 0;

@@ -60,6 +60,7 @@ struct GemmParams {
     const float* act_scale;  // [M]
     float* y;                // [M, N]
     int32_t* acc_out;        // optional [M, N]
+    float* h_out;            // EPI_SWIGLU: [M, N/2] = silu(row 2i) * row 2i+1 instead of y (gate/up rows interleaved)
     int32_t* scratch;        // split-K partials
     int* counters;           // split-K tickets, zero between launches
     uint32_t lut;
@@ -90,6 +91,9 @@ __device__ __forceinline__ Item item_of(const GemmParams& p, int it) {
     return r;
 }
 
+// SWIGLU = the epilogue applies the SwiGLU glue (EPI_SWIGLU); a separate instantiation so that the plain kernel's code
+// (and its scheduling, which the added path perturbed by 17 % when it shared one body) stays exactly as it was.
+template <bool SWIGLU>
 __global__ void __launch_bounds__(G_THREADS, 1)
 gemm_i8_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_codes, const __grid_constant__ CUtensorMap tm_q,
                        const GemmParams p) {
@@ -246,7 +250,7 @@ gemm_i8_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_codes, const __gri
 #pragma unroll
                             for (int j = 0; j < 4; ++j)
                                 *reinterpret_cast<uint4*>(a_tile + a_off[u] + (((half * 4 + (uint32_t)j) ^ rx[u]) << 4)) =
-                                    decode16(ws[j], p.lut);
+                                    decode16_fma(ws[j], p.lut);
                         }
                         fence_proxy_async_smem();  // generic-proxy stores -> visible to the tensor core (async proxy)
                         mbar_arrive(&a_full[sa]);  // every writer arrives itself, after its own proxy fence
@@ -279,7 +283,37 @@ gemm_i8_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_codes, const __gri
             mbar_wait(&tmem_full[acc], (nacc >> 1) & 1u);
             tc_fence_after();
             const uint32_t t_addr = tmem_d + ((uint32_t)(qd * 32) << 16) + acc * 256u;
-            if (p.S == 1) {
+            if (SWIGLU) {
+                // SwiGLU epilogue (crates/bitnet-transformer/src/lib.rs:756-789): adjacent TMEM lanes hold the (gate, up)
+                // rows of one FFN column; silu(gate) * up (common.cuh: silu_mul, the formula of every SwiGLU site) is
+                // stored instead of y: HALF the bytes, and the following act-quant reads them once instead of a glue
+                // pass reading y and writing h. The lane pair splits the tokens: the even lane (gate row) finishes the
+                // even tokens, the odd lane (up row) the odd ones -- one exchange and one silu per lane per two tokens.
+                // A loop of its own: sharing the c0 loop with the plain epilogue cost the plain path 17 % (scheduling).
+                const size_t hN = (size_t)(p.N >> 1);
+                const bool odd = lane & 1;
+#pragma unroll 1
+                for (int c0 = 0; c0 < mv; c0 += 32) {
+                    uint32_t r[32];
+                    float sl = slv[0];
+#pragma unroll
+                    for (int c = 1; c < 8; ++c) sl = (c0 == 32 * c) ? slv[c] : sl;
+                    tmem_ld_32x32(t_addr + (uint32_t)c0, r);
+                    float* hp = p.h_out + (size_t)(w.m0 + c0) * hN + (n >> 1);
+#pragma unroll
+                    for (int j = 0; j < 32; j += 2) {
+                        const float v0 = __fmul_rn(__shfl_sync(0xffffffffu, sl, j), (float)(int)r[j]);
+                        const float v1 = __fmul_rn(__shfl_sync(0xffffffffu, sl, j + 1), (float)(int)r[j + 1]);
+                        const float got = __shfl_xor_sync(0xffffffffu, odd ? v0 : v1, 1);
+                        const float hv = odd ? silu_mul(got, v1) : silu_mul(v0, got);
+                        const int jj = j + (odd ? 1 : 0);
+                        if (nv && c0 + jj < mv) hp[(size_t)jj * hN] = hv;
+                    }
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+            } else if (p.S == 1) {
 #pragma unroll 1
                 for (int c0 = 0; c0 < mv; c0 += 32) {
                     uint32_t r[32];
@@ -378,8 +412,9 @@ bool gemm_i8_supported(const bitnet_b200_weight* w, int M) {
 int gemm_split_override = 0;  // test knob: force a split-K factor (0 = heuristic)
 
 int launch_gemm_i8(const bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, const int8_t* q, const float* act_scale,
-                   int M, float* y, int32_t* acc_out) {
+                   int M, float* y, int32_t* acc_out, float* h_out) {
     if (!gemm_i8_supported(w, M)) return fail("linear_i8 GEMM: shape not covered by the tcgen05 kernel");
+    if (h_out && ((w->rows & 1) || acc_out)) return fail("linear_i8 GEMM: the SwiGLU epilogue needs an even row count and no acc_out");
     if (reinterpret_cast<uintptr_t>(q) & 15) return fail("linear_i8 GEMM: q must be 16-byte aligned");
     if (!ctx->gemm_scratch || !ctx->gemm_counters) {
         // first GEMM on this context: allocate the split-K scratch (cudaMalloc is illegal under graph capture,
@@ -404,6 +439,7 @@ int launch_gemm_i8(const bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, cons
     p.act_scale = act_scale;
     p.y = y;
     p.acc_out = acc_out;
+    p.h_out = h_out;
     p.scratch = ctx->gemm_scratch;
     p.counters = ctx->gemm_counters;
     p.lut = w->lut_word;
@@ -428,7 +464,7 @@ int launch_gemm_i8(const bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, cons
         if (tiles > G_MAX_TILE_COUNTERS) continue;
         for (int si = 0; si < 6; ++si) {
             const int S = s_c[si];
-            if (S > 1 && (S > nkb / 2 || (size_t)tiles * BN * G_ROWS * 4 > G_SCRATCH_BYTES)) continue;
+            if (S > 1 && (h_out || S > nkb / 2 || (size_t)tiles * BN * G_ROWS * 4 > G_SCRATCH_BYTES)) continue;  // SwiGLU epilogue: single-pass tiles only
             const long items = tiles * S;
             const double rounds = (double)div_ceil((size_t)items, (size_t)ctx->num_sms);
             const double t_kb = 0.43 * BN / 256.0 > 0.30 ? 0.43 * BN / 256.0 : 0.30;  // measured: MMA-bound vs issue-bound
@@ -442,7 +478,7 @@ int launch_gemm_i8(const bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, cons
         }
     }
     if (!bestBN) return fail("linear_i8 GEMM: no tile shape for this problem");
-    if (gemm_split_override > 0 && gemm_split_override <= nkb) bestS = gemm_split_override;
+    if (gemm_split_override > 0 && gemm_split_override <= nkb && !h_out) bestS = gemm_split_override;
     p.BN = bestBN;
     p.n_mt = (int)div_ceil((size_t)M, (size_t)p.BN);
     p.S = bestS;
@@ -466,11 +502,13 @@ int launch_gemm_i8(const bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, cons
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 16 && !attr_set[dev]) {
-        B200_CUDA(cudaFuncSetAttribute(gemm_i8_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        B200_CUDA(cudaFuncSetAttribute(gemm_i8_tcgen05_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        B200_CUDA(cudaFuncSetAttribute(gemm_i8_tcgen05_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         attr_set[dev] = true;
     }
     const int grid = p.n_items < ctx->num_sms ? p.n_items : ctx->num_sms;
-    gemm_i8_tcgen05_kernel<<<grid, G_THREADS, smem, ctx->stream>>>(tm_codes, tm_q, p);
+    if (h_out) gemm_i8_tcgen05_kernel<true><<<grid, G_THREADS, smem, ctx->stream>>>(tm_codes, tm_q, p);
+    else gemm_i8_tcgen05_kernel<false><<<grid, G_THREADS, smem, ctx->stream>>>(tm_codes, tm_q, p);
     B200_LAUNCH_CHECK("gemm_i8_tcgen05_kernel");
     return 0;
 }

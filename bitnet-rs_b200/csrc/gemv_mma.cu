@@ -130,12 +130,12 @@ __global__ void __launch_bounds__(512) gemv_mma_kernel(const MmaParams p) {
             if (!(g & 1)) {
                 const int half = p.N / 2;
                 if (rA < p.N) {
-                    if (m0 < p.M) p.y[(size_t)m0 * half + (rA >> 1)] = __fmul_rn(vA0 / (1.0f + expf(-vA0)), uA0);
-                    if (m1 < p.M) p.y[(size_t)m1 * half + (rA >> 1)] = __fmul_rn(vA1 / (1.0f + expf(-vA1)), uA1);
+                    if (m0 < p.M) p.y[(size_t)m0 * half + (rA >> 1)] = silu_mul(vA0, uA0);
+                    if (m1 < p.M) p.y[(size_t)m1 * half + (rA >> 1)] = silu_mul(vA1, uA1);
                 }
                 if (rB < p.N) {
-                    if (m0 < p.M) p.y[(size_t)m0 * half + (rB >> 1)] = __fmul_rn(vB0 / (1.0f + expf(-vB0)), uB0);
-                    if (m1 < p.M) p.y[(size_t)m1 * half + (rB >> 1)] = __fmul_rn(vB1 / (1.0f + expf(-vB1)), uB1);
+                    if (m0 < p.M) p.y[(size_t)m0 * half + (rB >> 1)] = silu_mul(vB0, uB0);
+                    if (m1 < p.M) p.y[(size_t)m1 * half + (rB >> 1)] = silu_mul(vB1, uB1);
                 }
             }
         } else {

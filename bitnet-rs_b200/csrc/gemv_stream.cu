@@ -273,7 +273,7 @@ __global__ void __launch_bounds__(MT >= 4 ? 512 : 1024) gemv_stream_kernel(const
                 const int row = row_begin + 2 * pr;
                 if (p.epi == EPI_SWIGLU) {
                     // rows (2i, 2i+1) = (gate_i, up_i): h_i = silu(gate) * up
-                    p.y[(size_t)m * (p.N / 2) + (row >> 1)] = __fmul_rn(v0 / (1.0f + expf(-v0)), v1);
+                    p.y[(size_t)m * (p.N / 2) + (row >> 1)] = silu_mul(v0, v1);
                 } else {
                     const size_t oi = (size_t)m * p.N + row;
                     if (p.epi == EPI_RESIDUAL) {

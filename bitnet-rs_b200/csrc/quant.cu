@@ -56,7 +56,7 @@ __device__ __forceinline__ float fused_value(const float* __restrict__ xr,
                                              const float* __restrict__ gamma, float inv_rms, int k) {
     if (MODE == 2) {
         const float g = xr[2 * k], u = xr[2 * k + 1];
-        return (g / (1.0f + expf(-g))) * u;
+        return silu_mul(g, u);
     }
     float v = xr[k];
     if (MODE == 1) v = v * inv_rms * gamma[k];
@@ -85,10 +85,10 @@ __global__ void __launch_bounds__(1024) actquant_fast_kernel(const float* __rest
             if (k0 + 4 <= K) {
                 const float4 a = *reinterpret_cast<const float4*>(xr + 2 * k0);
                 const float4 b = *reinterpret_cast<const float4*>(xr + 2 * k0 + 4);
-                v[j * 4 + 0] = (a.x / (1.0f + expf(-a.x))) * a.y;
-                v[j * 4 + 1] = (a.z / (1.0f + expf(-a.z))) * a.w;
-                v[j * 4 + 2] = (b.x / (1.0f + expf(-b.x))) * b.y;
-                v[j * 4 + 3] = (b.z / (1.0f + expf(-b.z))) * b.w;
+                v[j * 4 + 0] = silu_mul(a.x, a.y);
+                v[j * 4 + 1] = silu_mul(a.z, a.w);
+                v[j * 4 + 2] = silu_mul(b.x, b.y);
+                v[j * 4 + 3] = silu_mul(b.z, b.w);
             } else {
                 for (int e = 0; e < 4; ++e)
                     if (k0 + e < K) v[j * 4 + e] = fused_value<2>(xr, gamma, 1.f, k0 + e);

@@ -48,7 +48,7 @@ __global__ void __launch_bounds__(256) tp_row_absmax_kernel(const float* __restr
         float v;
         if (MODE == 2) {
             const float2 gu = *reinterpret_cast<const float2*>(xr + 2 * (size_t)k);
-            v = (gu.x / (1.0f + expf(-gu.x))) * gu.y;
+            v = silu_mul(gu.x, gu.y);
             h[(size_t)row * K + k] = v;
         } else {
             v = xr[k];

@@ -122,6 +122,18 @@ class Context:
             M, _dev_ptr(y, torch.float32, "y"), None if acc is None else acc.data_ptr()))
         return (y, acc) if (want_acc or acc_out is not None) else y
 
+    def linear_i8_swiglu(self, w, q, act_scale, h=None):
+        """linear_i8 on an interleaved (gate, up) weight with SwiGLU in the GEMM epilogue: h [M, rows/2] (M >= 9)."""
+        torch = _torch()
+        M = q.shape[0]
+        if q.shape[1] != w.cols:
+            raise ValueError("q has %d columns, weight has %d" % (q.shape[1], w.cols))
+        h = torch.empty((M, w.rows // 2), dtype=torch.float32, device=q.device) if h is None else h
+        ffi.check(self._lib.bitnet_b200_linear_i8_swiglu(
+            self._h, w._h, _dev_ptr(q, torch.int8, "q"), _dev_ptr(act_scale, torch.float32, "act_scale"), M,
+            _dev_ptr(h, torch.float32, "h")))
+        return h
+
     def fused_linear(self, w, x, gamma=None, eps=1e-5, epilogue=EPI_STORE, y=None, residual=None, want_q=False):
         """[RMSNorm ->] act-quant -> ternary linear -> epilogue in ONE launch (decode, M <= 4)."""
         torch = _torch()

@@ -140,6 +140,12 @@ int bitnet_b200_rmsnorm_actquant(bitnet_b200_ctx* ctx, const float* x, const flo
  * It exists so the bit-exact check can read the accumulators directly. */
 int bitnet_b200_linear_i8(bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, const int8_t* q,
                           const float* act_scale, int M, float* y, int32_t* acc_out);
+/* linear_i8 with the SwiGLU glue in the GEMM's epilogue (batched decode / prefill, M >= 9, QK256): the weight holds
+ * interleaved (gate, up) rows [2F, K]; h[m, i] = silu(y[m, 2i]) * y[m, 2i+1] with y = the linear_i8 result, bit for
+ * bit, and y itself is never written (half the output bytes, and the following act-quant reads h once).
+ * crates/bitnet-transformer/src/lib.rs:756-789. h: [M, F] f32, DEVICE. */
+int bitnet_b200_linear_i8_swiglu(bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, const int8_t* q,
+                                 const float* act_scale, int M, float* h);
 /* The decode fast path as ONE launch (gemv_stream.cu): [RMSNorm ->] per-token absmax int8
  * quantise -> ternary linear -> epilogue. It is the composition of rmsnorm_actquant /
  * actquant_i8 and linear_i8 above, bit for bit, with the activation work done in the GEMV's

@@ -313,6 +313,19 @@ def test_linear_qk256_gemm_prefill_sizes(ctx, b200, rows, cols, M):
     assert torch.equal(y2, _torch_acc_qk256(qs, rows, cols, q).float() * s[:, None])
 
 
+@pytest.mark.parametrize("rows,cols,M", [(256, 512, 9), (13824, 2560, 64), (13824, 2560, 1000), (1024, 2560, 4096), (640, 1024, 300)])
+def test_linear_qk256_gemm_swiglu_epilogue(ctx, b200, oracle, rows, cols, M):
+    # SwiGLU in the GEMM epilogue == the plain GEMM followed by the stand-alone glue kernel, bit for bit
+    qs, q, s = _qk256_case(oracle, rows, cols, M, rows + M + 5)
+    w = ctx.weight(qs, b200.LAYOUT_QK256, rows, cols)
+    y = ctx.linear_i8(w, dev(q), dev(s))
+    h_ref, _ = ctx.row_absmax(y, swiglu=True)
+    h = ctx.linear_i8_swiglu(w, dev(q), dev(s))
+    assert torch.equal(h, h_ref)
+    g, u = y[:, 0::2], y[:, 1::2]
+    assert torch.allclose(h, torch.nn.functional.silu(g) * u, rtol=1e-5, atol=1e-6)
+
+
 @pytest.mark.parametrize("lut_name", ["MAP_B", "MAP_C"])
 def test_linear_qk256_gemm_other_code_maps(ctx, b200, oracle, lut_name):
     rows, cols, M = 192, 1024, 70
