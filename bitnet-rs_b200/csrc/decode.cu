@@ -481,7 +481,8 @@ static int mega_setup(bitnet_b200_model* m) {
     if (m->mega >= 0) return 0;
     m->mega = 0;
     const auto& c = m->cfg;
-    if (getenv("BITNET_B200_NO_MEGA") || c.layout != BITNET_B200_LAYOUT_QK256) return 0;
+    if (getenv("BITNET_B200_NO_MEGA")) return 0;
+    if (c.layout != BITNET_B200_LAYOUT_QK256 && getenv("BITNET_B200_NO_MEGA_BITNET32")) return 0;
     if (!m->have_emb || !m->have_rope || m->layers_set != c.n_layers) return 0;
     int coop = 0;
     cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, m->ctx->device);
@@ -490,13 +491,16 @@ static int mega_setup(bitnet_b200_model* m) {
     p = MegaParams{};
     p.L = c.n_layers; p.B = c.batch; p.H = c.hidden; p.F = c.ffn; p.NH = c.n_heads; p.NKV = c.n_kv_heads;
     p.D = c.head_dim; p.V = c.vocab; p.max_ctx = c.max_ctx; p.eps = c.rms_eps;
+    p.layout = c.layout == BITNET_B200_LAYOUT_QK256 ? 0 : 1;
     m->mega_smem = mega_plan(&p, m->ctx->num_sms);
     if (!m->mega_smem) return 0;
     std::vector<MegaLayer> tab((size_t)c.n_layers);
     for (int l = 0; l < c.n_layers; ++l) {
         const LayerW& L = m->layers[(size_t)l];
         for (const bitnet_b200_weight* w : {L.wqkv, L.wo, L.wgateup, L.wdown})
-            if (w->code_stride != w->cols / 4 || w->lut_word != m->layers[0].wqkv->lut_word) return 0;
+            if (w->code_stride != w->cols / 4 || w->lut_word != m->layers[0].wqkv->lut_word ||
+                (p.layout == 1 && (!w->f16_scales_exact || !w->scales)))  // clamped / overflowing block scales: per-projection graph
+                return 0;
     }
     // fragment-major copies of every code plane (decode_mega.cu: mega_repack_kernel), made once
     for (int l = 0; l < c.n_layers; ++l) {
@@ -504,9 +508,11 @@ static int mega_setup(bitnet_b200_model* m) {
         uint8_t* fm[4] = {nullptr, nullptr, nullptr, nullptr};
         int j = 0;
         for (const bitnet_b200_weight* w : {L.wqkv, L.wo, L.wgateup, L.wdown}) {
-            if (dmalloc((void**)&fm[j], w->rows * w->cols / 4)) return -1;
+            if (dmalloc((void**)&fm[j], mega_repacked_bytes(p.layout, (int)w->rows, (int)w->cols))) return -1;
             m->mega_codes.push_back(fm[j]);
-            if (mega_repack_weight(w->codes, (int)w->rows, (int)w->cols, fm[j], m->ctx->stream)) return -1;
+            if (mega_repack_weight(w->codes, p.layout == 1 ? w->scales : nullptr, w->scale_policy == BITNET_B200_SCALE_ABS_CLAMP,
+                                   (int)w->rows, (int)w->cols, fm[j], m->ctx->stream))
+                return -1;
             ++j;
         }
         tab[(size_t)l] = MegaLayer{fm[0], fm[1], fm[2], fm[3], L.attn_norm, L.ffn_norm};

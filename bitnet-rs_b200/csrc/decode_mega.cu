@@ -40,9 +40,10 @@ namespace b200 {
 constexpr int MEGA_NW = 15;                         // consumer warps
 constexpr int MEGA_CONS = MEGA_NW * 32;             // consumer threads
 constexpr int MEGA_THREADS = MEGA_CONS + 32;        // + the producer warp
-constexpr int MEGA_SLOT_BYTES = 30720;              // ring slot: 240 k-chunk fragments of 128 B = three 16-row tiles at K = 2560,
-                                                    // one at K = 6912, six LM-head rows at H = 2560
-constexpr int MEGA_SLOT_KC = MEGA_SLOT_BYTES / 128; // k-chunks (32 columns of a 16-row tile) per slot
+// ring slot size (MegaParams::slot_bytes): QK256 30720 B = 240 k-chunk fragments of 128 B = three 16-row tiles at K = 2560,
+// one at K = 6912, six LM-head rows at H = 2560; BitNet32-F16 34560 B = 216 k-chunks of (128 B codes + 32 B scales)
+constexpr int MEGA_SLOT_QK256 = 30720, MEGA_SLOT_BN32 = 34560;
+constexpr int MEGA_CHUNK_QK256 = 128, MEGA_CHUNK_BN32 = 160;  // bytes of a tile per k-chunk
 constexpr int MEGA_MAXB = 4;                        // tokens per step
 constexpr int MEGA_MAX_SLOTS = 8;
 constexpr int MEGA_MAX_LAYERS = 64;
@@ -394,27 +395,53 @@ __device__ __forceinline__ void mega_store_partial(int* rw, int i, int B, const 
 // while they fly (its MMAs have long completed), then PRMT decode + IMMA on two accumulator chains. Fully unrolled
 // over MAXC on purpose: ~11 instructions per chunk, 1-3 KB of code; the rolled form measured 2 x slower (LDS latency
 // and loop overhead exposed in every chunk).
-template <int MAXC>
-__device__ __forceinline__ void mega_tile(const unsigned char* base, const uint2 (&b)[MAXC], int nc, uint32_t lut, int* rw, int i,
-                                          int B, bool have_prev, const int (&p0)[4], const int (&p1)[4], int (&c0)[4], int (&c1)[4]) {
+template <int MAXC, bool BN32>
+__device__ __forceinline__ void mega_tile(const unsigned char* base, int soff, const uint2 (&b)[MAXC], int nc, uint32_t lut, int* rw,
+                                          int i, int B, bool have_prev, const int (&p0)[4], const int (&p1)[4], int (&c0)[4],
+                                          int (&c1)[4]) {
     uint32_t w[MAXC];
 #pragma unroll
     for (int c = 0; c < MAXC; ++c) w[c] = *reinterpret_cast<const uint32_t*>(base + (c < nc ? c : 0) * 128);
     if (have_prev) mega_store_partial(rw, i - 1, B, p0, p1);
+    if (!BN32) {
 #pragma unroll
-    for (int j = 0; j < 4; ++j) c0[j] = c1[j] = 0;
+        for (int j = 0; j < 4; ++j) c0[j] = c1[j] = 0;
 #pragma unroll
-    for (int c = 0; c < MAXC; ++c) {
-        const uint4 d = decode16(w[c], lut);
-        if (c & 1) mma_s8_m16n8k32(c1, d.x, d.y, d.z, d.w, b[c].x, b[c].y);
-        else mma_s8_m16n8k32(c0, d.x, d.y, d.z, d.w, b[c].x, b[c].y);
+        for (int c = 0; c < MAXC; ++c) {
+            const uint4 d = decode16(w[c], lut);
+            if (c & 1) mma_s8_m16n8k32(c1, d.x, d.y, d.z, d.w, b[c].x, b[c].y);
+            else mma_s8_m16n8k32(c0, d.x, d.y, d.z, d.w, b[c].x, b[c].y);
+        }
+    } else {
+        // BitNet32-F16: a k-chunk IS one 32-column block, so every IMMA result gets its rows' block scales
+        // (crates/bitnet-models/src/quant/i2s.rs:66-140: w = s * LUT[code]) before it joins the f32 row sums:
+        // y = sum_blk s[row, blk] * acc_i32[row, blk], the per-block accumulators exact as in the reference's dequantise-
+        // then-dot up to f32 summation order. Scales of rows (g, g + 8) sit side by side: one LDS.32, two cvt.
+        float f[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int c = 0; c < MAXC; ++c) {
+            const uint4 d = decode16(w[c], lut);
+            int t4[4] = {0, 0, 0, 0};
+            mma_s8_m16n8k32(t4, d.x, d.y, d.z, d.w, b[c].x, b[c].y);
+            const uint32_t sp = *reinterpret_cast<const uint32_t*>(base + soff + (c < nc ? c : 0) * 32);
+            const float2 sf = __half22float2(*reinterpret_cast<const __half2*>(&sp));
+            f[0] = fmaf(sf.x, (float)t4[0], f[0]);
+            f[1] = fmaf(sf.x, (float)t4[1], f[1]);
+            f[2] = fmaf(sf.y, (float)t4[2], f[2]);
+            f[3] = fmaf(sf.y, (float)t4[3], f[3]);
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            c0[j] = __float_as_int(f[j]);  // the partial travels as raw bits; c1 = 0 keeps mega_store_partial's add a no-op
+            c1[j] = 0;
+        }
     }
 }
 
 // The warp's k-chunks of every tile of the CTA: B fragments in registers for the whole phase; the per-warp partial of
 // a tile goes to sm.red. A ring slot carries o.T consecutive tiles (one bulk copy, one full / empty barrier pair):
 // the mbarrier probe costs ~200 cycles even when the data is there, so it is paid once per slot, not per tile.
-template <int MAXC>
+template <int MAXC, bool BN32>
 __device__ __forceinline__ void mega_tiles(const MegaParams& p, const MegaSmem& sm, const MegaOp& o, int nloc, int kc0, int nc,
                                            RingPos& rp, int& wi) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -427,7 +454,9 @@ __device__ __forceinline__ void mega_tiles(const MegaParams& p, const MegaSmem& 
         if (c < nc) b[c] = *reinterpret_cast<const uint2*>(arow + 32 * c);
     }
     const uint32_t NS = (uint32_t)p.n_slots, lut = p.lut;
-    const int tile_bytes = o.KC * 128;
+    const int tile_bytes = o.tile_bytes;
+    // BitNet32-F16: from the lane's fragment word of chunk 0 to its (row g, row g + 8) scale pair of chunk 0
+    const int soff = BN32 ? o.KC * 128 + kc0 * 32 + g * 4 - (kc0 * 32 + lane) * 4 : 0;
     RingPos r = rp;
     int* rw = sm.red + warp * p.red_ld;
     wtrace(p, wi, 3);
@@ -446,7 +475,7 @@ __device__ __forceinline__ void mega_tiles(const MegaParams& p, const MegaSmem& 
             MEGA_TRACE_ONLY(const long long tw0 = clock64();)
             mbar_wait(&sm.full[r.slot], r.par);
             MEGA_TRACE_ONLY(wcyc += clock64() - tw0;)
-            base = sm.ring + (size_t)r.slot * MEGA_SLOT_BYTES + (size_t)(kc0 * 32 + lane) * 4;
+            base = sm.ring + (size_t)r.slot * p.slot_bytes + (size_t)(kc0 * 32 + lane) * 4;
         }
     };
     auto leave = [&]() {
@@ -456,7 +485,7 @@ __device__ __forceinline__ void mega_tiles(const MegaParams& p, const MegaSmem& 
 #pragma unroll 1
     for (int i = 0; i < nloc; i += 2) {  // two bodies per trip: the accumulator sets alternate without register moves
         enter(i);
-        mega_tile<MAXC>(base, b, nc, lut, rw, i, B, i > 0, e0, e1, a0, a1);
+        mega_tile<MAXC, BN32>(base, soff, b, nc, lut, rw, i, B, i > 0, e0, e1, a0, a1);
         leave();
         wtrace(p, wi, 4);
         if (i + 1 >= nloc) {
@@ -464,7 +493,7 @@ __device__ __forceinline__ void mega_tiles(const MegaParams& p, const MegaSmem& 
             break;
         }
         enter(i + 1);
-        mega_tile<MAXC>(base, b, nc, lut, rw, i + 1, B, true, a0, a1, e0, e1);
+        mega_tile<MAXC, BN32>(base, soff, b, nc, lut, rw, i + 1, B, true, a0, a1, e0, e1);
         leave();
         wtrace(p, wi, 4);
         if (i + 2 >= nloc) {
@@ -504,10 +533,16 @@ __device__ __forceinline__ void mega_gemv_phase(const MegaParams& p, const MegaS
     mega_prologue(p, sm, pro, xin, ep_out - 1u, gamma, o.K, kc0, nc, sc, par, wi);
     prof_stamp(p, pi);  // prologue done
     // exact instances for the shapes that matter (2B-4T: 80 and 216 k-chunks over 15 warps = 6 and 15 each), generic otherwise
-    if (o.KC <= 6 * MEGA_NW) mega_tiles<6>(p, sm, o, q.nloc, kc0, nc, rp, wi);
-    else if (o.KC <= 10 * MEGA_NW) mega_tiles<10>(p, sm, o, q.nloc, kc0, nc, rp, wi);
-    else if (o.KC <= 15 * MEGA_NW) mega_tiles<15>(p, sm, o, q.nloc, kc0, nc, rp, wi);
-    else mega_tiles<MEGA_MAXC>(p, sm, o, q.nloc, kc0, nc, rp, wi);
+    if (p.layout == 0) {
+        if (o.KC <= 6 * MEGA_NW) mega_tiles<6, false>(p, sm, o, q.nloc, kc0, nc, rp, wi);
+        else if (o.KC <= 10 * MEGA_NW) mega_tiles<10, false>(p, sm, o, q.nloc, kc0, nc, rp, wi);
+        else if (o.KC <= 15 * MEGA_NW) mega_tiles<15, false>(p, sm, o, q.nloc, kc0, nc, rp, wi);
+        else mega_tiles<MEGA_MAXC, false>(p, sm, o, q.nloc, kc0, nc, rp, wi);
+    } else {
+        if (o.KC <= 6 * MEGA_NW) mega_tiles<6, true>(p, sm, o, q.nloc, kc0, nc, rp, wi);
+        else if (o.KC <= 15 * MEGA_NW) mega_tiles<15, true>(p, sm, o, q.nloc, kc0, nc, rp, wi);
+        else mega_tiles<MEGA_MAXC, true>(p, sm, o, q.nloc, kc0, nc, rp, wi);
+    }
     wtrace(p, wi, 5);
     cons_sync();
     wtrace(p, wi, 9);
@@ -517,26 +552,47 @@ __device__ __forceinline__ void mega_gemv_phase(const MegaParams& p, const MegaS
         const int half = N >> 1;
         if (tid < q.nloc * 8 * B) {
             const int m = tmod, pr = tdiv;
-            int a0 = 0, a1 = 0;
-#pragma unroll
-            for (int w = 0; w < MEGA_NW; ++w) {
-                a0 += sm.red[w * red_ld + (2 * pr) * B + m];
-                a1 += sm.red[w * red_ld + (2 * pr + 1) * B + m];
-            }
             float as = sc[0];
 #pragma unroll
             for (int j = 1; j < MEGA_MAXB; ++j) as = m == j ? sc[j] : as;
-            const float v0 = __fmul_rn(as, (float)a0), v1 = __fmul_rn(as, (float)a1);
+            float v0, v1;
+            if (p.layout == 0) {
+                int a0 = 0, a1 = 0;
+#pragma unroll
+                for (int w = 0; w < MEGA_NW; ++w) {
+                    a0 += sm.red[w * red_ld + (2 * pr) * B + m];
+                    a1 += sm.red[w * red_ld + (2 * pr + 1) * B + m];
+                }
+                v0 = __fmul_rn(as, (float)a0);
+                v1 = __fmul_rn(as, (float)a1);
+            } else {  // BitNet32-F16: f32 row sums of the warps' K slices, in warp order
+                float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+                for (int w = 0; w < MEGA_NW; ++w) {
+                    a0 += __int_as_float(sm.red[w * red_ld + (2 * pr) * B + m]);
+                    a1 += __int_as_float(sm.red[w * red_ld + (2 * pr + 1) * B + m]);
+                }
+                v0 = __fmul_rn(as, a0);
+                v1 = __fmul_rn(as, a1);
+            }
             ll_store(out, (size_t)m * half + q.t0 * 8 + pr, silu_mul(v0, v1), ep_out);
         }
     } else if (tid < nout) {
-        int a = 0;
-#pragma unroll
-        for (int w = 0; w < MEGA_NW; ++w) a += sm.red[w * red_ld + tid];
         float as = sc[0];
 #pragma unroll
         for (int j = 1; j < MEGA_MAXB; ++j) as = om == j ? sc[j] : as;
-        float v = __fmul_rn(as, (float)a);
+        float v;
+        if (p.layout == 0) {
+            int a = 0;
+#pragma unroll
+            for (int w = 0; w < MEGA_NW; ++w) a += sm.red[w * red_ld + tid];
+            v = __fmul_rn(as, (float)a);
+        } else {
+            float a = 0.f;
+#pragma unroll
+            for (int w = 0; w < MEGA_NW; ++w) a += __int_as_float(sm.red[w * red_ld + tid]);
+            v = __fmul_rn(as, a);
+        }
         if (epi == 1) {
             const float rv = rprobe.y == ep_res ? __uint_as_float(rprobe.x) : ll_wait1(resid + (size_t)om * N + orow, ep_res);
             v = __fadd_rn(rv, v);
@@ -828,7 +884,7 @@ __device__ __forceinline__ void mega_logits_rows(const MegaParams& p, const Mega
             mbar_wait(&sm.full[r.slot], r.par);
             waited = true;
         }
-        const uint4* wrow = reinterpret_cast<const uint4*>(sm.ring + (size_t)r.slot * MEGA_SLOT_BYTES + (size_t)(j - cbase) * H * 2);
+        const uint4* wrow = reinterpret_cast<const uint4*>(sm.ring + (size_t)r.slot * p.slot_bytes + (size_t)(j - cbase) * H * 2);
         float acc[NB];
 #pragma unroll
         for (int m = 0; m < NB; ++m) acc[m] = 0.f;
@@ -913,7 +969,7 @@ __device__ __forceinline__ void mega_logits_phase(const MegaParams& p, const Meg
     }
     const int rpc = (V + G - 1) / G;
     const int r0 = min(V, cta * rpc), r1 = min(V, r0 + rpc);
-    const int RL = MEGA_SLOT_BYTES / (H * 2);
+    const int RL = p.slot_bytes / (H * 2);
     switch (p.B) {
         case 1: mega_logits_rows<1>(p, sm, xn, r0, r1, RL, rp); break;
         case 2: mega_logits_rows<2>(p, sm, xn, r0, r1, RL, rp); break;
@@ -952,14 +1008,14 @@ __device__ __forceinline__ void mega_producer(const MegaParams& p, const MegaSme
             const uint8_t* w = op == 0 ? L.wqkv : (op == 1 ? L.wo : (op == 2 ? L.wgu : L.wdown));
             const MegaOp& o = p.op[op];
             const PhaseGeom q = phase_geom(o, cta);
-            const size_t tile_bytes = (size_t)o.KC * 128;
+            const size_t tile_bytes = (size_t)o.tile_bytes;
             for (int i = 0; i < q.nloc; i += o.T, ++n) {  // one slot = up to o.T consecutive tiles = one bulk copy
                 const uint32_t slot = n % NS, bytes = (uint32_t)(min(o.T, q.nloc - i) * tile_bytes);
                 MEGA_TRACE_ONLY(const long long tw0 = clock64(); const bool free_now = n < NS || mbar_try_wait(&sm.empty[slot], ((n / NS) - 1u) & 1u);)
                 if (n >= NS) mbar_wait_backoff(&sm.empty[slot], ((n / NS) - 1u) & 1u);
                 MEGA_TRACE_ONLY(pw += clock64() - tw0; pfree += free_now ? 1 : 0;)
                 mbar_expect_tx(&sm.full[slot], bytes);
-                bulk_g2s(sm.ring + (size_t)slot * MEGA_SLOT_BYTES, w + (size_t)(q.t0 + i) * tile_bytes, bytes, &sm.full[slot]);
+                bulk_g2s(sm.ring + (size_t)slot * p.slot_bytes, w + (size_t)(q.t0 + i) * tile_bytes, bytes, &sm.full[slot]);
             }
         }
     }
@@ -969,14 +1025,14 @@ __device__ __forceinline__ void mega_producer(const MegaParams& p, const MegaSme
     if (p.mode == 0) {
         const int rpc = (p.V + G - 1) / G;
         const int r0 = min(p.V, cta * rpc), r1 = min(p.V, r0 + rpc);
-        const int RL = MEGA_SLOT_BYTES / (p.H * 2);
+        const int RL = p.slot_bytes / (p.H * 2);
         for (int rr = r0; rr < r1; rr += RL, ++n) {
             const int nr = min(RL, r1 - rr);
             const uint32_t slot = n % NS;
             if (n >= NS) mbar_wait_backoff(&sm.empty[slot], ((n / NS) - 1u) & 1u);
             const uint32_t bytes = (uint32_t)nr * (uint32_t)p.H * 2u;
             mbar_expect_tx(&sm.full[slot], bytes);
-            bulk_g2s(sm.ring + (size_t)slot * MEGA_SLOT_BYTES, p.emb + (size_t)rr * p.H, bytes, &sm.full[slot]);
+            bulk_g2s(sm.ring + (size_t)slot * p.slot_bytes, p.emb + (size_t)rr * p.H, bytes, &sm.full[slot]);
         }
     }
 }
@@ -1165,10 +1221,12 @@ size_t mega_plan(MegaParams* p, int num_sms) {
     if (p->H % 32 || p->F % 32 || QD % 32) return 0;             // whole k-chunks
     const int kmax = p->H > p->F ? (p->H > QD ? p->H : QD) : (p->F > QD ? p->F : QD);
     if (kmax > 32 * MEGA_MAXC * MEGA_NW) return 0;               // k-chunks per warp (register arrays)
-    if (kmax / 32 > MEGA_SLOT_KC) return 0;                      // a 16-row tile fits one ring slot
+    const int slot_bytes = p->layout == 1 ? MEGA_SLOT_BN32 : MEGA_SLOT_QK256, chunk_bytes = p->layout == 1 ? MEGA_CHUNK_BN32 : MEGA_CHUNK_QK256;
+    p->slot_bytes = slot_bytes;
+    if (kmax / 32 * chunk_bytes > slot_bytes) return 0;          // a 16-row tile fits one ring slot
     if (QKV % 16 || p->H % 16 || (2 * p->F) % 16) return 0;      // whole 16-row tiles
     if (p->D % 32 || p->D > 256 || MEGA_CONS % (p->D / 4)) return 0;
-    if (p->H * 2 > MEGA_SLOT_BYTES || (p->H * 2) % 16) return 0; // one LM-head row per slot at least
+    if (p->H * 2 > slot_bytes || (p->H * 2) % 16) return 0;      // one LM-head row per slot at least
     const int Ns[4] = {QKV, p->H, 2 * p->F, p->H}, Ks[4] = {p->H, QD, p->H, p->F};
     int tiles_max = 0;
     for (int i = 0; i < 4; ++i) {
@@ -1176,7 +1234,8 @@ size_t mega_plan(MegaParams* p, int num_sms) {
         o.N = Ns[i];
         o.K = Ks[i];
         o.KC = Ks[i] / 32;
-        o.T = MEGA_SLOT_KC / o.KC;  // >= 1: kmax <= 32 * MEGA_SLOT_KC (checked above)
+        o.tile_bytes = o.KC * chunk_bytes;
+        o.T = slot_bytes / o.tile_bytes;  // >= 1 (checked above)
         const int NT = Ns[i] / 16;
         o.tq = NT / num_sms;
         o.tr = NT % num_sms;
@@ -1194,11 +1253,11 @@ size_t mega_plan(MegaParams* p, int num_sms) {
                  attn_b = ((size_t)p->attn_floats * 4 + 127) & ~(size_t)127, stage_b = ((size_t)stage_floats * 4 + 127) & ~(size_t)127;
     const size_t shared_b = attn_b > stage_b ? attn_b : stage_b;
     const size_t cap = 227 * 1024, rest = red_b + act_b + shared_b;
-    if ((size_t)MEGA_OFF_RING + rest + 3 * (size_t)MEGA_SLOT_BYTES > cap) return 0;
-    int slots = (int)((cap - MEGA_OFF_RING - rest) / MEGA_SLOT_BYTES);
+    if ((size_t)MEGA_OFF_RING + rest + 3 * (size_t)slot_bytes > cap) return 0;
+    int slots = (int)((cap - MEGA_OFF_RING - rest) / slot_bytes);
     if (slots > MEGA_MAX_SLOTS) slots = MEGA_MAX_SLOTS;
     p->n_slots = slots;
-    p->off_red = MEGA_OFF_RING + slots * MEGA_SLOT_BYTES;  // MEGA_SLOT_BYTES is a multiple of 128
+    p->off_red = MEGA_OFF_RING + slots * slot_bytes;  // both slot sizes are multiples of 128
     p->off_act = p->off_red + (int)red_b;
     p->off_attn = p->off_act + (int)act_b;
     p->off_stage = p->off_attn;
@@ -1210,9 +1269,11 @@ size_t mega_plan(MegaParams* p, int num_sms) {
 // out: [N/16 tiles][K/32 k-chunks][32 lanes] words; the word of lane (g, t) carries, in slot order,
 //   a0 = row g, k 4t..4t+3 | a1 = row g+8, same k | a2 = row g, k 16+4t.. | a3 = row g+8, k 16+4t..
 // of its tile and k-chunk, so that decode16() returns the A fragment of mma.sync.m16n8k32 as it stands.
-__global__ void mega_repack_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int N, int K) {
+__global__ void mega_repack_kernel(const uint32_t* __restrict__ in, const __half* __restrict__ scales, int abs_scales,
+                                   uint32_t* __restrict__ out, int N, int K) {
     const size_t total = (size_t)N * K / 16;
     const int KC = K >> 5, wpr = K >> 4;
+    const size_t tile_words = (size_t)KC * (scales ? MEGA_CHUNK_BN32 : MEGA_CHUNK_QK256) / 4;
     for (size_t o = (size_t)blockIdx.x * blockDim.x + threadIdx.x; o < total; o += (size_t)gridDim.x * blockDim.x) {
         const int lane = (int)(o & 31);
         const size_t tk = o >> 5;
@@ -1228,11 +1289,27 @@ __global__ void mega_repack_kernel(const uint32_t* __restrict__ in, uint32_t* __
             const uint32_t src = in[row * wpr + (k >> 4)];
             w |= code_of(src, k & 15) << code_bitpos(s);
         }
-        out[o] = w;
+        out[tile * tile_words + (size_t)kc * 32 + lane] = w;
+        if (scales && t == 0) {
+            // BitNet32-F16: the block scales of rows (g, g + 8) of this k-chunk as one f16 pair behind the tile's codes.
+            // SCALE_ABS_CLAMP: |s| -- the clamp to [1e-3, 1e3] is the identity here (weights whose scales it would change
+            // are not handed to this kernel: bitnet_b200_weight::f16_scales_exact)
+            __half lo = scales[(tile * 16 + g) * (size_t)KC + kc], hi = scales[(tile * 16 + g + 8) * (size_t)KC + kc];
+            if (abs_scales) {
+                lo = __habs(lo);
+                hi = __habs(hi);
+            }
+            const uint32_t pair = (uint32_t)__half_as_ushort(lo) | ((uint32_t)__half_as_ushort(hi) << 16);
+            out[tile * tile_words + (size_t)KC * 32 + (size_t)kc * 8 + g] = pair;
+        }
     }
 }
-int mega_repack_weight(const uint8_t* codes, int N, int K, uint8_t* out, cudaStream_t st) {
-    mega_repack_kernel<<<1024, 256, 0, st>>>(reinterpret_cast<const uint32_t*>(codes), reinterpret_cast<uint32_t*>(out), N, K);
+size_t mega_repacked_bytes(int layout, int N, int K) {
+    return (size_t)(N / 16) * (K / 32) * (layout == 1 ? MEGA_CHUNK_BN32 : MEGA_CHUNK_QK256);
+}
+int mega_repack_weight(const uint8_t* codes, const __half* scales, int scale_abs_clamp, int N, int K, uint8_t* out, cudaStream_t st) {
+    mega_repack_kernel<<<1024, 256, 0, st>>>(reinterpret_cast<const uint32_t*>(codes), scales, scale_abs_clamp,
+                                             reinterpret_cast<uint32_t*>(out), N, K);
     B200_LAUNCH_CHECK("mega_repack_kernel");
     return 0;
 }

@@ -14,6 +14,7 @@ struct MegaLayer {
 struct MegaOp {
     int N, K, KC;      // rows, columns, k-chunks (K / 32)
     int T;             // consecutive 16-row tiles per ring slot (one bulk copy, one barrier pair)
+    int tile_bytes;    // bytes of one 16-row tile in the fragment-major copy (codes [+ f16 block scales])
     int tq, tr;        // tiles per CTA: the first tr CTAs own tq + 1 contiguous tiles, the others tq
 };
 
@@ -41,6 +42,8 @@ struct MegaParams {
     int prefetch;            // 1 = L2 prefetches inside the grid barriers (diagnostics knob BITNET_B200_MEGA_NOPF)
     int mode;                // 0 = full decode step; 1 = the 4L ternary GEMVs only, no dependencies
     int n_slots, act_bytes, attn_floats;
+    int layout;              // 0 = QK256, 1 = BitNet32-F16 (per-32-column f16 block scales travel with the codes)
+    int slot_bytes;          // ring slot size (mega_plan)
     int off_red, off_act, off_attn, off_stage;  // shared-memory offsets of the shape-dependent pieces (mega_plan)
     int red_ld;              // ints per warp in the partial-sum buffer: (tiles per CTA at most) * 16 * B
     unsigned long long* prof;  // optional diagnostics buffer (decode_mega.cu: prof_stamp / wtrace), or nullptr
@@ -49,7 +52,8 @@ struct MegaParams {
 
 // decode_mega.cu
 size_t mega_plan(MegaParams* p, int num_sms);  // 0 = shape not covered
-int mega_repack_weight(const uint8_t* codes, int N, int K, uint8_t* out, cudaStream_t st);
+int mega_repack_weight(const uint8_t* codes, const __half* scales, int scale_abs_clamp, int N, int K, uint8_t* out, cudaStream_t st);
+size_t mega_repacked_bytes(int layout, int N, int K);
 int launch_decode_mega(const MegaParams& p, size_t smem, int num_sms, cudaStream_t st);
 
 }  // namespace b200

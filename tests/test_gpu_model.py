@@ -152,3 +152,20 @@ def test_context_length_and_token_id_guards(b200):
     m.reset()
     assert np.array_equal(m.decode(np.array([3], np.int32)), first)
     m.close()
+
+
+def test_bitnet32_layout_runs_in_the_persistent_kernel(b200, oracle):
+    # BitNet32-F16 (the layout the reference's own timing is quoted on) through the one-kernel step: 2B-4T projection
+    # shapes, 2 layers; greedy tokens identical to the CPU oracle model, logit cosine > 0.99, ONE launch per step
+    shape = b200.ModelShape.bitnet_2b4t(n_layers=2, vocab=4096, max_ctx=24, layout=b200.LAYOUT_BITNET32_F16)
+    B = shape.batch
+    ctx, gm, cm = _build(b200, oracle, shape, B)
+    toks = np.array([17], np.int32)
+    for step in range(12):
+        nxt, logits = gm.decode(toks, want_logits=True)
+        ct, cl = cm.step(int(toks[0]), seq=0, want_logits=True)
+        assert int(nxt[0]) == ct, "step %d" % step
+        assert _cos(logits[0], cl) > 0.99
+        toks = nxt.copy()
+    assert gm.launches_per_step == 1
+    gm.close()
