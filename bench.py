@@ -51,6 +51,7 @@ def parse():
                     help="8b-tp workload: how the row-parallel layers exchange (fused NVLink pulls, NCCL collectives, or both)")
     ap.add_argument("--prefill-layers", type=int, default=30)
     ap.add_argument("--no-fused-epilogue", action="store_true", help="prefill: the round-1 pipeline (stand-alone SwiGLU pass)")
+    ap.add_argument("--no-bitnet32-record", action="store_true", help="skip the BitNet32-F16 decode sub-record of the default line")
     ap.add_argument("--no-gemm-record", action="store_true", help="skip the prefill GEMM sub-record of the default line")
     ap.add_argument("--no-tp", action="store_true", help="N > 1: skip the tensor-parallel sub-record of the default workload")
     return ap.parse_args()
@@ -692,6 +693,32 @@ def main():
     except Exception:
         pass
 
+    # ---- N = 1: the same decode on the other on-disk layout (BitNet32-F16: 10-byte blocks with an inline f16 scale) ----
+    bn32_rec = None
+    if world == 1 and shape.layout == b2.LAYOUT_QK256 and not args.no_bitnet32_record:
+        try:
+            sh2 = b2.ModelShape.bitnet_2b4t(max_ctx=PROMPT + 2 * (W + K) + 8, layout=b2.LAYOUT_BITNET32_F16)
+            m2 = b2.Model(ctx, sh2)
+            m2.load_synthetic()
+            t2 = None
+            for i in range(PROMPT):
+                t2 = m2.decode(np.array([(i * 7919) % sh2.vocab], np.int32))
+            m2.decode_device(W)
+            torch.cuda.synchronize()
+            f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            f0.record()
+            m2.decode_device(K)
+            f1.record()
+            torch.cuda.synchronize()
+            ms2 = f0.elapsed_time(f1)
+            bn32_rec = {"layout": "BitNet32-F16", "tok_s": B * K / (ms2 * 1e-3), "ms_per_step": ms2 / K,
+                        "launches_per_step": m2.launches_per_step, "ratio_to_qk256": (B * K / (ms2 * 1e-3)) / (B * K / (ms_dev * 1e-3)),
+                        "weight_mb": sh2.ternary_bytes() / 1e6}
+            m2.close()
+            del m2
+        except Exception as ex:
+            bn32_rec = {"error": "%s: %s" % (type(ex).__name__, str(ex)[:200])}
+
     # ---- N = 1: the prefill regime in short (BASELINE.json configs[3]): 2 layers' worth of the M = 16384 pipeline ----
     gemm_rec = None
     if world == 1 and not args.no_gemm_record:
@@ -759,6 +786,8 @@ def main():
             line["tp"] = tp_rec
         if gemm_rec is not None:
             line["gemm"] = gemm_rec
+        if bn32_rec is not None:
+            line["bitnet32"] = bn32_rec
         if world == 1 and not args.no_cpu_baseline:
             try:
                 v, cores, sample, _, _, single = cpu_decode_tok_s(shape, 8, 1, args.cpu_budget_s)
