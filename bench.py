@@ -480,6 +480,9 @@ def run_prefill(args):
     print(json.dumps(line), flush=True)
 
 
+SWEEP_SHAPES = {"qkv": (3840, 2560), "o": (2560, 2560), "gate/up": (6912, 2560), "down": (2560, 6912)}
+
+
 def _sweep_weight_bytes(rng, layout_name, rows, cols):
     if layout_name == "qk256":
         return rng.integers(0, 256, rows * cols // 4, dtype=np.uint8)
@@ -529,7 +532,7 @@ def run_sweep(args):
     ctx = b2.Context(0)
     peak, peak_src = measured_peak()
     i8_peak = 4500.0            # TOPS, nominal dense int8/fp8 (B200_PROFILING.md); f16 path: 2250 TFLOP/s
-    ms = [1, 16, 64, 512, 4096]
+    ms = [1, 8, 16, 32, 64, 512, 4096]
     rows_out = []
 
     def graph_time(fn, iters, reps=5):

@@ -32,6 +32,9 @@ int launch_gemv_fast(const bitnet_b200_ctx*, const bitnet_b200_weight*, int M, i
                        const float* act_scale, const float* x, const float* gamma, float eps, int epi, float* y,
                        const float* residual, int32_t* acc_out, int8_t* q_out, float* scale_out, float* normed_out,
                        bool pdl);
+bool gemm_small_supported(const bitnet_b200_ctx*, const bitnet_b200_weight*, int M);
+int launch_gemm_small(const bitnet_b200_ctx*, const bitnet_b200_weight*, const int8_t*, const float*, int M, float* y,
+                      int32_t* acc_out, bool pdl);
 int launch_gemm_i8(const bitnet_b200_ctx*, const bitnet_b200_weight*, const int8_t*, const float*,
                    int, float*, int32_t*, float*);
 bool gemm_i8_supported(const bitnet_b200_weight*, int M);
@@ -415,6 +418,11 @@ int bitnet_b200_linear_i8(bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, con
     B200_CUDA(cudaSetDevice(ctx->device));
     // per-32-block accumulators are only materialised by the GEMV
     const bool force_gemv = acc_out && w->layout == BITNET_B200_LAYOUT_BITNET32_F16;
+    if (!force_gemv && M >= 9 && M <= 64) {
+        // batched-decode regime: mma.sync kernel without the tcgen05 pipeline's fixed cost (gemm_small.cu)
+        const int rc = launch_gemm_small(ctx, w, q, act_scale, M, y, acc_out, getenv("BITNET_B200_PDL_API") != nullptr);
+        if (rc != 1) return rc;
+    }
     if (!force_gemv && gemm_i8_supported(w, M))
         return launch_gemm_i8(ctx, w, q, act_scale, M, y, acc_out, nullptr);
     if (!acc_out && gemm_f16_supported(w, M))  // BitNet32-F16, M >= 9: tcgen05 kind::f16 on s * LUT[code]

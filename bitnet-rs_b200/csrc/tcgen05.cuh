@@ -56,6 +56,13 @@ __device__ __forceinline__ void tma_load_2d(void* dst_smem, const CUtensorMap* t
         ::"r"(smem_u32(dst_smem)), "l"(tm), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
         : "memory");
 }
+// 3-D tiled TMA load: box at (c0 = innermost byte coordinate, c1, c2)
+__device__ __forceinline__ void tma_load_3d(void* dst_smem, const CUtensorMap* tm, int c0, int c1, int c2, void* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+        ::"r"(smem_u32(dst_smem)), "l"(tm), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
 // true in exactly one lane of the (converged) warp
 __device__ __forceinline__ bool elect_one() {
     uint32_t pred;
@@ -136,5 +143,22 @@ static inline int make_map_2d(CUtensorMap* tm, const void* ptr, size_t inner, si
     return 0;
 }
 
+// The same matrix seen as [col_blocks][rows][box_inner bytes]: the third coordinate walks along the row in steps of
+// box_inner bytes (its stride is SMALLER than the row pitch), so that one box {box_inner, box_rows, nblk} brings nblk
+// consecutive swizzled [box_rows x box_inner] tiles -- the shared-memory image of nblk 2-D boxes -- with ONE TMA op.
+static inline int make_map_colblocks(CUtensorMap* tm, const void* ptr, size_t inner, size_t rows, size_t pitch, int box_rows,
+                                     int box_inner, int nblk) {
+    EncodeTiledFn fn = encode_tiled_fn();
+    if (!fn) return fail("linear_i8 GEMM: cuTensorMapEncodeTiled is not available from this driver");
+    const cuuint64_t gdim[3] = {(cuuint64_t)box_inner, (cuuint64_t)rows, (cuuint64_t)div_ceil(inner, (size_t)box_inner)};
+    const cuuint64_t gstr[2] = {(cuuint64_t)pitch, (cuuint64_t)box_inner};
+    const cuuint32_t box[3] = {(cuuint32_t)box_inner, (cuuint32_t)box_rows, (cuuint32_t)nblk};
+    const cuuint32_t estr[3] = {1u, 1u, 1u};
+    const CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<void*>(ptr), gdim, gstr, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, box_inner == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
+                          CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail("linear_i8 GEMM: cuTensorMapEncodeTiled (3-D) failed (" + std::to_string((int)r) + ")");
+    return 0;
+}
 
 }  // namespace b200

@@ -253,7 +253,8 @@ def test_linear_qk256_model_shapes(ctx, b200, oracle, rows, cols, M):
     (384, 128, 40), (2560, 2560, 257), (6912, 2560, 1000), (3840, 2560, 9), (2560, 6912, 12), (4096, 512, 64),
     (13824, 2560, 2048),
 ])
-def test_linear_qk256_gemm_tcgen05(ctx, b200, oracle, rows, cols, M):
+def test_linear_qk256_gemm_tcgen05(ctx, b200, oracle, rows, cols, M, monkeypatch):
+    monkeypatch.setenv("BITNET_B200_SMALLM_MAX", "0")   # M <= 64 would otherwise take gemm_small.cu (tested below)
     qs, q, s = _qk256_case(oracle, rows, cols, M, rows + cols + M)
     w = ctx.weight(qs, b200.LAYOUT_QK256, rows, cols)
     y, acc = ctx.linear_i8(w, dev(q), dev(s), want_acc=True)
@@ -262,6 +263,71 @@ def test_linear_qk256_gemm_tcgen05(ctx, b200, oracle, rows, cols, M):
     assert np.array_equal(y.cpu().numpy(), ry)
     y2 = ctx.linear_i8(w, dev(q), dev(s))
     assert torch.equal(y2, y)
+
+
+# ---- M = 9..64: the mma.sync batched-decode kernel (gemm_small.cu); same bit-exact bar -------------------
+@pytest.mark.parametrize("rows,cols,M", [
+    (8, 256, 9), (9, 512, 16), (100, 1024, 17), (17, 4096, 24), (33, 768, 25), (65, 1280, 33), (128, 256, 48),
+    (640, 2560, 64), (3840, 2560, 9), (3840, 2560, 32), (2560, 2560, 64), (13824, 2560, 16), (13824, 2560, 64),
+    (2560, 6912, 12), (2560, 6912, 64), (4096, 4096, 64), (1024, 14336, 40), (4096, 2048, 64), (6144, 4096, 20),
+    (4096, 7168, 64), (1000, 3072, 57),
+])
+def test_linear_qk256_gemm_small(ctx, b200, oracle, rows, cols, M, monkeypatch):
+    qs, q, s = _qk256_case(oracle, rows, cols, M, rows + cols + M)
+    w = ctx.weight(qs, b200.LAYOUT_QK256, rows, cols)
+    racc, ry = oracle.linear_qk256_i8(qs, rows, cols, q, s)
+    l0 = b200.launch_count()
+    y, acc = ctx.linear_i8(w, dev(q), dev(s), want_acc=True)
+    assert b200.launch_count() - l0 == 1
+    assert np.array_equal(acc.cpu().numpy(), racc)
+    assert np.array_equal(y.cpu().numpy(), ry)
+    y2 = ctx.linear_i8(w, dev(q), dev(s))
+    assert torch.equal(y2, y)
+    # and the same integers from the tcgen05 GEMM on the other side of the routing boundary
+    monkeypatch.setenv("BITNET_B200_SMALLM_MAX", "0")
+    y3, acc3 = ctx.linear_i8(w, dev(q), dev(s), want_acc=True)
+    assert torch.equal(acc3, acc) and torch.equal(y3, y)
+
+
+# a spread of the planner's search space (row warps, k warps, segments per warp, cluster K split): warp grids, ragged row
+# groups, ragged last chunks (zero-filled by the TMA unit), ring wrap-around (more chunks than stages), DSMEM reduction
+@pytest.mark.parametrize("rows,cols,M,plans", [
+    (200, 2560, 64, ["1,5,2,1", "1,3,2,2", "1,10,1,2", "1,4,2,3", "1,10,1,1", "2,3,2,2", "1,8,1,3", "1,9,2,2", "2,2,1,2",
+                     "2,8,1,1", "1,16,1,2", "2,5,4,1"]),
+    (2560, 6912, 16, ["1,4,4,2", "1,15,2,2", "2,6,2,5", "2,5,2,6", "2,4,4,2", "1,3,2,3", "1,7,2,2", "1,4,2,7", "1,13,2,3",
+                      "2,8,1,7", "1,2,1,1"]),
+    (4096, 4096, 33, ["1,4,1,1", "2,3,2,6", "2,8,1,4", "1,2,4,1", "1,6,1,6", "1,3,4,1", "2,2,2,2", "1,16,1,2", "2,2,1,4",
+                      "2,8,1,1", "2,8,2,2"]),
+    (77, 14336, 24, ["1,6,1,1", "1,4,1,1", "1,11,2,2", "1,5,4,1", "2,7,2,1", "2,5,2,4", "2,5,4,6", "2,2,4,2", "1,9,4,4",
+                     "2,8,1,7", "1,16,1,7"]),
+])
+def test_linear_qk256_gemm_small_every_plan(ctx, b200, oracle, rows, cols, M, plans, monkeypatch):
+    qs, q, s = _qk256_case(oracle, rows, cols, M, rows * 3 + M)
+    w = ctx.weight(qs, b200.LAYOUT_QK256, rows, cols)
+    racc, ry = oracle.linear_qk256_i8(qs, rows, cols, q, s)
+    for plan in plans:
+        monkeypatch.setenv("BITNET_B200_SMALLM_PLAN", plan)
+        l0 = b200.launch_count()
+        y, acc = ctx.linear_i8(w, dev(q), dev(s), want_acc=True)
+        assert b200.launch_count() - l0 == 1, plan
+        assert np.array_equal(acc.cpu().numpy(), racc), plan
+        assert np.array_equal(y.cpu().numpy(), ry), plan
+
+
+def test_linear_qk256_gemm_small_extremes_and_maps(ctx, b200, oracle):
+    # all-(+/-127) activations against all-(+2) / all-(-2) codes: the largest |acc| the layout allows
+    rows, cols, M = 96, 14336, 64
+    for lut_name, byte in (("MAP_A", 0xFF), ("MAP_A", 0x00), ("MAP_B", 0xAA), ("MAP_C", 0x55)):
+        qs = np.full(rows * cols // 4, byte, np.uint8)
+        q = np.full((M, cols), 127, np.int8)
+        q[1::2] = -127
+        s = np.linspace(0.5, 2.0, M).astype(np.float32)
+        lut = getattr(oracle, lut_name)
+        w = ctx.weight(qs, b200.LAYOUT_QK256, rows, cols, lut=lut)
+        y, acc = ctx.linear_i8(w, dev(q), dev(s), want_acc=True)
+        racc, ry = oracle.linear_qk256_i8(qs, rows, cols, q, s, lut=lut)
+        assert np.array_equal(acc.cpu().numpy(), racc)
+        assert np.array_equal(y.cpu().numpy(), ry)
 
 
 def test_linear_qk256_gemm_cold_weights_repeated(ctx, b200):
