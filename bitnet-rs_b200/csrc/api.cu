@@ -418,8 +418,9 @@ int bitnet_b200_linear_i8(bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, con
     B200_CUDA(cudaSetDevice(ctx->device));
     // per-32-block accumulators are only materialised by the GEMV
     const bool force_gemv = acc_out && w->layout == BITNET_B200_LAYOUT_BITNET32_F16;
-    if (!force_gemv && M >= 9 && M <= 64) {
-        // batched-decode regime: mma.sync kernel without the tcgen05 pipeline's fixed cost (gemm_small.cu)
+    if (!force_gemv && M <= 64) {
+        // batched-decode regime: mma.sync kernel without the tcgen05 pipeline's fixed cost (gemm_small.cu). 1 = not its
+        // shape, or the other kernel of this M range (tcgen05 GEMM / GEMV) measured faster on it: fall through
         const int rc = launch_gemm_small(ctx, w, q, act_scale, M, y, acc_out, getenv("BITNET_B200_PDL_API") != nullptr);
         if (rc != 1) return rc;
     }

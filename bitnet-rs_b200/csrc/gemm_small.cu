@@ -1,4 +1,4 @@
-// gemm_small.cu -- ternary linear for the batched-decode regime, QK256 layout, M = 9..64 tokens.
+// gemm_small.cu -- ternary linear for the batched-decode regime, QK256 layout, M = 1..64 tokens.
 //
 // Same contract as the other linear_i8 kernels (i2s_qk256.rs:346-372 per token; the reference loops gemv_qk256 over
 // the tokens, quantized_linear.rs forward_qk256): int32 accumulation of LUT[code] * int8 activation over all of K,
@@ -31,9 +31,12 @@
 //   * int32 accumulators stay in registers over the whole K range (2 x NT x 4 per lane); the KW partial sums meet in
 //     shared memory (the ring, once drained), and with a K split the CTAs of the cluster read each other's reduced
 //     tiles through distributed shared memory, each finishing 1 / ksplit of the outputs. No global scratch, no atomics.
+#include <algorithm>
+#include <cstdio>
 #include <map>
 #include <mutex>
 #include <tuple>
+#include <vector>
 
 #include "common.cuh"
 #include "tcgen05.cuh"
@@ -133,7 +136,6 @@ gemm_small_kernel(const __grid_constant__ CUtensorMap tm_codes, const __grid_con
         }
         mbar_fence_init();
     }
-    __syncthreads();
     pdl_launch_dependents();
 
     // ---- one lane of warp 0 doubles as the producer ---------------------------------------------------------------
@@ -151,11 +153,13 @@ gemm_small_kernel(const __grid_constant__ CUtensorMap tm_codes, const __grid_con
         tma_load_3d(st, &tm_q, 0, 0, kc / 128, &full[s]);  // CK / 128 boxes of 8 NT rows x 128 bytes
     };
     if (tid == 0) {
-        // the weights do not depend on the previous kernel: fill the ring with them before griddepcontrol.wait
+        // the weights do not depend on the previous kernel: fill the ring with them before griddepcontrol.wait; the
+        // first loads are in flight before the other warps have even passed the barrier below
         for (int i = 0; i < p.NS; ++i) issue_weights(i);
         pdl_wait();  // the activations are what the previous kernel wrote
         for (int i = 0; i < p.NS; ++i) issue_acts(i);
     }
+    __syncthreads();  // barrier inits visible to every waiter
     {
         // ---- consumers ---------------------------------------------------------------------------------------
         const int g = lane >> 2, t = lane & 3;
@@ -271,7 +275,7 @@ struct SmallPlan {
 
 static int small_nt(int M) {
     const int nt = (M + 7) / 8;
-    return nt <= 2 ? 2 : nt <= 3 ? 3 : nt <= 4 ? 4 : nt <= 6 ? 6 : 8;
+    return nt <= 1 ? 1 : nt <= 2 ? 2 : nt <= 3 ? 3 : nt <= 4 ? 4 : nt <= 6 ? 6 : 8;
 }
 
 // fill the derived fields of a (RW, KW, U, ksplit) choice; false = not realisable for this shape
@@ -318,6 +322,7 @@ static int small_occ_nt(int threads, size_t smem) {
 }
 static int small_occupancy(const SmallPlan& pl) {
     switch (pl.NT) {
+        case 1: return small_occ_nt<1>(pl.threads, pl.smem);
         case 2: return small_occ_nt<2>(pl.threads, pl.smem);
         case 3: return small_occ_nt<3>(pl.threads, pl.smem);
         case 4: return small_occ_nt<4>(pl.threads, pl.smem);
@@ -326,71 +331,48 @@ static int small_occupancy(const SmallPlan& pl) {
     }
 }
 
-// Heuristic: estimated cycles per SM for a candidate, smaller = better. The terms are the three streams a CTA
-// overlaps -- tensor pipe (2 clk per IMMA per SM), activations from L2, weights from HBM -- plus a fixed cost per chunk
-// (barrier round trip) and per CTA; CTAs beyond one wave of the 148 SMs queue.
-static double small_cost(const bitnet_b200_ctx* ctx, const SmallPlan& pl, int M, int N, int K) {
-    const double ctas = (double)pl.grid_x * pl.ksplit;
+// Cost model, microseconds: a least-squares fit over ~2600 timed (shape, M, plan) points on a B200
+// (tools/smallm_tune.py; shapes of the 2B-4T and 8B-class models, whole and tp = 2 shards, M = 16 / 32 / 64). It ranks
+// the candidates for the autotuner below and is the fallback where nothing can be timed (first use of a shape inside a
+// CUDA graph capture); on the fitted set its pick is within 1.2x of the best plan on average.
+static double small_cost(const bitnet_b200_ctx* ctx, const SmallPlan& pl) {
     const int occ = small_occupancy(pl);
-    const double slots = (double)ctx->num_sms * occ;
-    const double waves = ceil(ctas / slots);
-    const double imma = (double)pl.RW * pl.KW * pl.U * 4 * pl.NT * 2.0 * occ;  // co-resident CTAs share the pipe
-    const double l2 = (double)M * pl.CK / 40.0 * occ;
-    double chunk = imma > l2 ? imma : l2;
-    const double lat = 350.0;  // un-overlapped barrier + issue latency per chunk
-    if (chunk < lat) chunk = lat;
-    const double fixed = 1500.0 + (pl.ksplit > 1 ? 1200.0 : 0.0) + 40.0 * pl.RW * 2 * pl.NT;
-    const double hbm_floor = (double)N * K / 4 / (21.0 * ctx->num_sms);
-    double body = waves * pl.npr * chunk;
-    if (body < hbm_floor) body = hbm_floor;
-    return body + waves * fixed;
+    const double ctas = (double)pl.grid_x * pl.ksplit;
+    const double rounds = ceil(ctas / ((double)ctx->num_sms * occ));
+    double conc = ceil(ctas / ctx->num_sms);
+    if (conc > occ) conc = occ;
+    const double per_sm = rounds * conc;  // CTAs one SM executes, worst case
+    const double imma = (double)pl.npr * pl.CK / 32 * 2 * pl.RW * pl.NT;
+    const double wbytes = (double)pl.npr * pl.CK / 4 * 32 * pl.RW, abytes = (double)pl.npr * pl.CK * pl.NT * 8;
+    const double t_imma = imma * 2.9 / 1900 * per_sm, t_bytes = (wbytes + abytes) / 42 / 1900 * per_sm,
+                 t_w = wbytes / 23 / 1900 * per_sm;
+    double t_max = t_imma > t_bytes ? t_imma : t_bytes;
+    if (t_w > t_max) t_max = t_w;
+    const int jobs = pl.RW * 2 * pl.NT;
+    return 1.864 + 1.581 * rounds + 1.352 * rounds * (pl.ksplit > 1) + 2.334 * t_imma + 0.354 * t_bytes - 0.523 * t_w +
+           0.466 * rounds * pl.npr / pl.NS - 1.686 * rounds * jobs * pl.KW / 256.0 - 0.175 * t_max;
 }
 
-static bool plan_small(const bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, int M, SmallPlan* best) {
-    if (w->layout != BITNET_B200_LAYOUT_QK256) return false;
-    if (M < 9 || M > 64) return false;
-    if (w->cols % 256 != 0 || w->code_stride != w->cols / 4 || w->rows < 1) return false;
-    if (const char* e = getenv("BITNET_B200_SMALLM_PLAN")) {  // tuning knob: "RW,KW,U,ksplit"
-        SmallPlan pl{};
-        if (sscanf(e, "%d,%d,%d,%d", &pl.RW, &pl.KW, &pl.U, &pl.ksplit) == 4 && small_derive(w, M, &pl)) {
-            *best = pl;
-            return true;
-        }
-        *best = SmallPlan{};
-        best->NT = -1;  // forced plan not realisable: launch_gemm_small reports it instead of rerouting silently
-        return false;
-    }
-    static std::mutex mu;
-    static std::map<std::tuple<size_t, size_t, int>, SmallPlan> cache;  // (rows, cols, M) -> plan
-    const auto key = std::make_tuple(w->rows, w->cols, M);
-    {
-        std::lock_guard<std::mutex> lk(mu);
-        auto it = cache.find(key);
-        if (it != cache.end()) {
-            *best = it->second;
-            return best->NT != 0;
-        }
-    }
-    bool found = false;
-    double bc = 0;
+static bool small_shape_ok(const bitnet_b200_weight* w, int M) {
+    return w->layout == BITNET_B200_LAYOUT_QK256 && M >= 1 && M <= 64 && w->cols % 256 == 0 &&
+           w->code_stride == w->cols / 4 && w->rows >= 1;
+}
+
+// every realisable plan of the search space, cheapest (by the model) first
+static std::vector<std::pair<double, SmallPlan>> small_candidates(const bitnet_b200_ctx* ctx, const bitnet_b200_weight* w,
+                                                                  int M) {
+    std::vector<std::pair<double, SmallPlan>> v;
     for (int RW = 1; RW <= 2; ++RW)
-        for (int KW = 4; KW * RW <= SMALL_MAX_CONS; ++KW)
+        for (int KW = 2; KW * RW <= SMALL_MAX_CONS; ++KW)
             for (int U = 1; U <= 4; U *= 2)
                 for (int ks = 1; ks <= 8; ++ks) {
                     SmallPlan pl{};
                     pl.RW = RW, pl.KW = KW, pl.U = U, pl.ksplit = ks;
                     if (!small_derive(w, M, &pl)) continue;
-                    const double c = small_cost(ctx, pl, M, (int)w->rows, (int)w->cols);
-                    if (!found || c < bc) {
-                        found = true;
-                        bc = c;
-                        *best = pl;
-                    }
+                    v.emplace_back(small_cost(ctx, pl), pl);
                 }
-    if (!found) *best = SmallPlan{};
-    std::lock_guard<std::mutex> lk(mu);
-    cache[key] = *best;
-    return found;
+    std::sort(v.begin(), v.end(), [](const auto& a, const auto& b) { return a.first < b.first; });
+    return v;
 }
 
 // largest M routed here by linear_i8 (above it the tcgen05 GEMM takes over). BITNET_B200_SMALLM_MAX is read per call
@@ -400,10 +382,8 @@ int gemm_small_max_m() {
     return e ? atoi(e) : 64;
 }
 
-bool gemm_small_supported(const bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, int M) {
-    if (M > gemm_small_max_m()) return false;
-    SmallPlan pl;
-    return plan_small(ctx, w, M, &pl);
+bool gemm_small_supported(const bitnet_b200_ctx*, const bitnet_b200_weight* w, int M) {
+    return M <= gemm_small_max_m() && small_shape_ok(w, M);
 }
 
 template <int NT>
@@ -445,14 +425,8 @@ static int launch_small_nt(const bitnet_b200_ctx* ctx, const SmallPlan& pl, cons
     return 0;
 }
 
-// 1 = shape not covered, 0 = ok, -1 = error (same contract as launch_gemv_mma)
-int launch_gemm_small(const bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, const int8_t* q, const float* act_scale,
-                      int M, float* y, int32_t* acc_out, bool pdl) {
-    SmallPlan pl{};
-    if (M > gemm_small_max_m()) return 1;
-    if (!plan_small(ctx, w, M, &pl))
-        return pl.NT == -1 ? fail("linear_i8: BITNET_B200_SMALLM_PLAN is not realisable for this shape") : 1;
-    if (reinterpret_cast<uintptr_t>(q) & 15) return 1;
+static int run_small_plan(const bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, const SmallPlan& pl, const int8_t* q,
+                          const float* act_scale, int M, float* y, int32_t* acc_out, bool pdl) {
     SmallParams p{};
     p.codes = w->codes;
     p.q = q;
@@ -468,12 +442,150 @@ int launch_gemm_small(const bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, c
     p.npr = pl.npr;
     p.stage_bytes = pl.stage_bytes, p.w_off = pl.w_off, p.red_off = pl.red_off, p.ring_off = pl.ring_off;
     switch (pl.NT) {
+        case 1: return launch_small_nt<1>(ctx, pl, p, pdl);
         case 2: return launch_small_nt<2>(ctx, pl, p, pdl);
         case 3: return launch_small_nt<3>(ctx, pl, p, pdl);
         case 4: return launch_small_nt<4>(ctx, pl, p, pdl);
         case 6: return launch_small_nt<6>(ctx, pl, p, pdl);
         default: return launch_small_nt<8>(ctx, pl, p, pdl);
     }
+}
+
+// ---- plan selection: timed once per (device, rows, cols, token-tile count) ------------------------------------------
+// The first eager call on a shape times the model's best SMALL_TUNE_CANDS plans and the tcgen05 GEMM on the caller's own
+// operands (every candidate writes the same integers, so the output is the call's result whichever ran last), weights
+// evicted from L2 between runs (decode streams each layer's weights from HBM), and keeps the fastest: the routing
+// between the two kernels falls out of the same measurement. Nothing can be timed inside a CUDA graph capture: a shape
+// first seen there uses the model's pick and the M <= 32 routing rule, without caching it.
+// BITNET_B200_SMALLM_AUTOTUNE=0 disables the timing (model only); BITNET_B200_SMALLM_VERBOSE=1 prints the choice.
+constexpr int SMALL_TUNE_CANDS = 20;
+struct SmallChoice {
+    bool use_alt;  // the other kernel of this M range measured faster: tcgen05 GEMM (M >= 9) / GEMV (M <= 8)
+    SmallPlan pl;
+    float us_small, us_alt;
+};
+int launch_gemv_fast(const bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, int M, int pro, const int8_t* q,
+                     const float* act_scale, const float* x, const float* gamma, float eps, int epi, float* y,
+                     const float* residual, int32_t* acc_out, int8_t* q_out, float* scale_out, float* normed_out, bool pdl);
+bool gemv_fast_supported(const bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, int M, bool f32_prologue);
+bool gemm_i8_supported(const bitnet_b200_weight* w, int M);
+int launch_gemm_i8(const bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, const int8_t* q, const float* act_scale, int M,
+                   float* y, int32_t* acc_out, float* h_out);
+
+static bool small_autotune(const bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, const int8_t* q, const float* act_scale,
+                           int M, float* y, int32_t* acc_out, SmallChoice* out) {
+    auto cands = small_candidates(ctx, w, M);
+    if (cands.empty()) return false;
+    if ((int)cands.size() > SMALL_TUNE_CANDS) cands.resize(SMALL_TUNE_CANDS);
+    static void* flush[16] = {};
+    constexpr size_t FLUSH_BYTES = 256u << 20;  // > L2
+    const int dev = ctx->device;
+    if (dev >= 0 && dev < 16 && !flush[dev] && cudaMalloc(&flush[dev], FLUSH_BYTES) != cudaSuccess) {
+        cudaGetLastError();
+        flush[dev] = nullptr;
+    }
+    cudaEvent_t e0, e1;
+    if (cudaEventCreate(&e0) != cudaSuccess || cudaEventCreate(&e1) != cudaSuccess) return false;
+    auto timed = [&](auto&& launch) -> float {
+        float best = 1e30f;
+        for (int rep = 0; rep < 5; ++rep) {
+            if (dev >= 0 && dev < 16 && flush[dev]) cudaMemsetAsync(flush[dev], rep & 1, FLUSH_BYTES, ctx->stream);
+            cudaEventRecord(e0, ctx->stream);
+            if (launch() != 0) {  // e.g. a cluster shape this device cannot co-schedule: not a candidate
+                cudaGetLastError();
+                return 1e30f;
+            }
+            cudaEventRecord(e1, ctx->stream);
+            if (cudaEventSynchronize(e1) != cudaSuccess) {
+                cudaGetLastError();
+                return 1e30f;
+            }
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, e0, e1);
+            if (rep > 0 && ms < best) best = ms;
+        }
+        return best * 1e3f;
+    };
+    out->us_small = 1e30f;
+    for (const auto& c : cands) {
+        const float us = timed([&] { return run_small_plan(ctx, w, c.second, q, act_scale, M, y, acc_out, false); });
+        if (us < out->us_small) {
+            out->us_small = us;
+            out->pl = c.second;
+        }
+    }
+    out->us_alt = 1e30f;
+    if (M >= 9 && gemm_i8_supported(w, M))
+        out->us_alt = timed([&] { return launch_gemm_i8(ctx, w, q, act_scale, M, y, acc_out, nullptr); });
+    if (M <= 8 && gemv_fast_supported(ctx, w, M, false))
+        out->us_alt = timed([&] {
+            return launch_gemv_fast(ctx, w, M, /*PRO_Q8*/ 0, q, act_scale, nullptr, nullptr, 0.f, /*EPI_STORE*/ 0, y, nullptr, acc_out,
+                                    nullptr, nullptr, nullptr, false);
+        });
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    if (out->us_small >= 1e29f && out->us_alt >= 1e29f) return false;
+    out->use_alt = out->us_alt < out->us_small;
+    return true;
+}
+
+// 1 = shape not covered (or the tcgen05 GEMM measured faster: the caller falls through to it), 0 = ok, -1 = error
+int launch_gemm_small(const bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, const int8_t* q, const float* act_scale,
+                      int M, float* y, int32_t* acc_out, bool pdl) {
+    if (M > gemm_small_max_m() || !small_shape_ok(w, M)) return 1;
+    if (reinterpret_cast<uintptr_t>(q) & 15) return 1;
+    if (const char* e = getenv("BITNET_B200_SMALLM_PLAN")) {  // tuning / test knob: "RW,KW,U,ksplit"
+        SmallPlan pl{};
+        if (sscanf(e, "%d,%d,%d,%d", &pl.RW, &pl.KW, &pl.U, &pl.ksplit) != 4 || !small_derive(w, M, &pl))
+            return fail("linear_i8: BITNET_B200_SMALLM_PLAN is not realisable for this shape");
+        return run_small_plan(ctx, w, pl, q, act_scale, M, y, acc_out, pdl);
+    }
+    static std::mutex mu;
+    static std::map<std::tuple<int, size_t, size_t, int>, SmallChoice> chosen;
+    const auto key = std::make_tuple(ctx->device, w->rows, w->cols, small_nt(M));
+    SmallChoice ch{};
+    bool have = false;
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        auto it = chosen.find(key);
+        if (it != chosen.end()) {
+            ch = it->second;
+            have = true;
+        }
+    }
+    if (!have) {
+        cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+        cudaStreamIsCapturing(ctx->stream, &cs);
+        const char* at = getenv("BITNET_B200_SMALLM_AUTOTUNE");
+        const bool tune = cs == cudaStreamCaptureStatusNone && !(at && at[0] == '0');
+        if (tune) {
+            std::lock_guard<std::mutex> lk(mu);  // one tuner at a time: the timings must not overlap each other
+            auto it = chosen.find(key);
+            if (it != chosen.end()) {
+                ch = it->second;
+                have = true;
+            } else if (small_autotune(ctx, w, q, act_scale, M, y, acc_out, &ch)) {
+                chosen[key] = ch;
+                have = true;
+                if (getenv("BITNET_B200_SMALLM_VERBOSE"))
+                    fprintf(stderr, "[bitnet_b200] linear_i8 %zux%zu M=%d: %s (gemm_small RW=%d KW=%d U=%d ksplit=%d: %.1f us, %s: %.1f us)\n",
+                            w->rows, w->cols, M, ch.use_alt ? "alternative" : "gemm_small", ch.pl.RW, ch.pl.KW, ch.pl.U,
+                            ch.pl.ksplit, ch.us_small, M >= 9 ? "tcgen05 gemm" : "gemv", ch.us_alt);
+                // the call's result is already in y / acc_out (every candidate computed it)
+                return 0;
+            }
+        }
+        if (!have) {  // model only
+            auto cands = small_candidates(ctx, w, M);
+            if (cands.empty()) return 1;
+            ch.pl = cands.front().second;
+            ch.use_alt = (M > 32 && gemm_i8_supported(w, M)) || (M <= 8 && gemv_fast_supported(ctx, w, M, false));
+        }
+    }
+    if (ch.use_alt) return 1;
+    SmallPlan pl = ch.pl;
+    if (!small_derive(w, M, &pl)) return 1;  // same NT bucket, this M: derived fields do not depend on M beyond NT
+    return run_small_plan(ctx, w, pl, q, act_scale, M, y, acc_out, pdl);
 }
 
 }  // namespace b200

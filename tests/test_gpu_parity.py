@@ -223,18 +223,21 @@ def _qk256_case(oracle, rows, cols, M, seed):
 
 @pytest.mark.parametrize("rows,cols", [(8, 256), (9, 512), (33, 300), (7, 777), (100, 1024), (17, 4096)])
 @pytest.mark.parametrize("M", [1, 2, 3, 4, 5, 8, 9, 16, 17])
-def test_linear_qk256_small(ctx, b200, oracle, rows, cols, M):
+def test_linear_qk256_small(ctx, b200, oracle, rows, cols, M, monkeypatch):
     qs, q, s = _qk256_case(oracle, rows, cols, M, rows + M)
     w = ctx.weight(qs, b200.LAYOUT_QK256, rows, cols)
     y, acc = ctx.linear_i8(w, dev(q), dev(s), want_acc=True)
     racc, ry = oracle.linear_qk256_i8(qs, rows, cols, q, s)
     assert np.array_equal(acc.cpu().numpy(), racc)
     assert np.array_equal(y.cpu().numpy(), ry)          # one exact int->f32 and one multiply
+    monkeypatch.setenv("BITNET_B200_SMALLM_MAX", "0")   # the GEMV (M <= 8) / tcgen05 GEMM alone, without gemm_small.cu
+    y2, acc2 = ctx.linear_i8(w, dev(q), dev(s), want_acc=True)
+    assert torch.equal(acc2, acc) and torch.equal(y2, y)
 
 
 @pytest.mark.parametrize("rows,cols", SHAPES_2B + [(4096, 4096), (1024, 14336)])
-@pytest.mark.parametrize("M", [1, 16])
-def test_linear_qk256_model_shapes(ctx, b200, oracle, rows, cols, M):
+@pytest.mark.parametrize("M", [1, 8, 16])
+def test_linear_qk256_model_shapes(ctx, b200, oracle, rows, cols, M, monkeypatch):
     qs, q, s = _qk256_case(oracle, rows, cols, M, rows ^ cols)
     w = ctx.weight(qs, b200.LAYOUT_QK256, rows, cols)
     assert w.nbytes == rows * cols // 4
@@ -244,6 +247,9 @@ def test_linear_qk256_model_shapes(ctx, b200, oracle, rows, cols, M):
     assert np.array_equal(y.cpu().numpy(), ry)
     y2 = ctx.linear_i8(w, dev(q), dev(s))                      # the no-accumulator path
     assert torch.equal(y2, y)
+    monkeypatch.setenv("BITNET_B200_SMALLM_MAX", "0")          # the GEMV / tcgen05 GEMM alone, without gemm_small.cu
+    y3, acc3 = ctx.linear_i8(w, dev(q), dev(s), want_acc=True)
+    assert torch.equal(acc3, acc) and torch.equal(y3, y)
 
 
 # ---- M > 16: the tcgen05 kind::i8 GEMM (gemm_tcgen05.cu); same bit-exact bar as the GEMV -------
@@ -265,9 +271,9 @@ def test_linear_qk256_gemm_tcgen05(ctx, b200, oracle, rows, cols, M, monkeypatch
     assert torch.equal(y2, y)
 
 
-# ---- M = 9..64: the mma.sync batched-decode kernel (gemm_small.cu); same bit-exact bar -------------------
+# ---- M = 1..64: the mma.sync batched-decode kernel (gemm_small.cu); same bit-exact bar -------------------
 @pytest.mark.parametrize("rows,cols,M", [
-    (8, 256, 9), (9, 512, 16), (100, 1024, 17), (17, 4096, 24), (33, 768, 25), (65, 1280, 33), (128, 256, 48),
+    (640, 2560, 1), (4096, 4096, 3), (2560, 6912, 8), (8, 256, 9), (9, 512, 16), (100, 1024, 17), (17, 4096, 24), (33, 768, 25), (65, 1280, 33), (128, 256, 48),
     (640, 2560, 64), (3840, 2560, 9), (3840, 2560, 32), (2560, 2560, 64), (13824, 2560, 16), (13824, 2560, 64),
     (2560, 6912, 12), (2560, 6912, 64), (4096, 4096, 64), (1024, 14336, 40), (4096, 2048, 64), (6144, 4096, 20),
     (4096, 7168, 64), (1000, 3072, 57),
@@ -276,13 +282,18 @@ def test_linear_qk256_gemm_small(ctx, b200, oracle, rows, cols, M, monkeypatch):
     qs, q, s = _qk256_case(oracle, rows, cols, M, rows + cols + M)
     w = ctx.weight(qs, b200.LAYOUT_QK256, rows, cols)
     racc, ry = oracle.linear_qk256_i8(qs, rows, cols, q, s)
-    l0 = b200.launch_count()
-    y, acc = ctx.linear_i8(w, dev(q), dev(s), want_acc=True)
-    assert b200.launch_count() - l0 == 1
+    y, acc = ctx.linear_i8(w, dev(q), dev(s), want_acc=True)   # first use of a shape: times the candidate plans
     assert np.array_equal(acc.cpu().numpy(), racc)
     assert np.array_equal(y.cpu().numpy(), ry)
-    y2 = ctx.linear_i8(w, dev(q), dev(s))
+    l0 = b200.launch_count()
+    y2 = ctx.linear_i8(w, dev(q), dev(s))                       # the chosen plan (or the tcgen05 GEMM, if that won)
+    assert b200.launch_count() - l0 == 1
     assert torch.equal(y2, y)
+    monkeypatch.setenv("BITNET_B200_SMALLM_AUTOTUNE", "0")      # the cost model's pick, on a shape not seen before
+    w1 = ctx.weight(qs[:(rows - 1) * (cols // 4)], b200.LAYOUT_QK256, rows - 1, cols) if rows > 1 else None
+    if w1 is not None:
+        y4, acc4 = ctx.linear_i8(w1, dev(q), dev(s), want_acc=True)
+        assert np.array_equal(acc4.cpu().numpy(), racc[:, :rows - 1])
     # and the same integers from the tcgen05 GEMM on the other side of the routing boundary
     monkeypatch.setenv("BITNET_B200_SMALLM_MAX", "0")
     y3, acc3 = ctx.linear_i8(w, dev(q), dev(s), want_acc=True)
@@ -298,6 +309,7 @@ def test_linear_qk256_gemm_small(ctx, b200, oracle, rows, cols, M, monkeypatch):
                       "2,8,1,7", "1,2,1,1"]),
     (4096, 4096, 33, ["1,4,1,1", "2,3,2,6", "2,8,1,4", "1,2,4,1", "1,6,1,6", "1,3,4,1", "2,2,2,2", "1,16,1,2", "2,2,1,4",
                       "2,8,1,1", "2,8,2,2"]),
+    (3840, 2560, 5, ["1,10,2,1", "2,5,4,1", "1,4,1,5", "1,16,4,1", "2,8,1,3", "1,2,1,5"]),
     (77, 14336, 24, ["1,6,1,1", "1,4,1,1", "1,11,2,2", "1,5,4,1", "2,7,2,1", "2,5,2,4", "2,5,4,6", "2,2,4,2", "1,9,4,4",
                      "2,8,1,7", "1,16,1,7"]),
 ])

@@ -20,7 +20,7 @@ def derive(N, K, M, RW, KW, U, ks):
     if RW * KW > 16:
         return None
     nt = (M + 7) // 8
-    NT = 2 if nt <= 2 else 3 if nt <= 3 else 4 if nt <= 4 else 6 if nt <= 6 else 8
+    NT = 1 if nt <= 1 else 2 if nt <= 2 else 3 if nt <= 3 else 4 if nt <= 4 else 6 if nt <= 6 else 8
     CK = 128 * U * KW
     if CK % 256:
         return None
