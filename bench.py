@@ -583,7 +583,7 @@ def run_sweep(args):
                        "us": round(us, 3), "alg_bytes": alg, "GBs": round(alg / us / 1e3, 1),
                        "hbm_frac": round(alg / us / 1e3 / peak, 4), "TOPS": round(tops, 1),
                        "tensor_frac": round(tops / (i8_peak if lname == "qk256" else i8_peak / 2), 4),
-                       "path": "gemv" if M <= 8 else "tcgen05 gemm", "weight_copies": len(ws),
+                       "path": b2.last_linear_kernel(), "weight_copies": len(ws),
                        "gpu_launches": b2.launch_count() - l0}
                 if M == 1 and cpu is not None:
                     row["cpu_baseline"] = cpu

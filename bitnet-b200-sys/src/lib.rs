@@ -183,6 +183,7 @@ extern "C" {
 
     pub fn bitnet_b200_version() -> *const c_char;
     pub fn bitnet_b200_launch_count() -> u64;
+    pub fn bitnet_b200_last_linear_kernel() -> *const c_char;
 }
 
 /// The library's thread-local error text (`bitnet_cpp_get_last_error`), empty when none.

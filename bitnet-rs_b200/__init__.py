@@ -8,7 +8,7 @@ fast path. There is no CPU fallback: without the compiled CUDA library every cal
 
 Import as `bitnet_rs_b200` (the shim module at the repo root maps the hyphenated directory).
 """
-from .ffi import LIB_PATH, B200Error, build, lib, last_error, launch_count  # noqa: F401
+from .ffi import LIB_PATH, B200Error, build, lib, last_error, launch_count, last_linear_kernel  # noqa: F401
 from .provider import (  # noqa: F401
     B200Kernel,
     I2SQk256NoScale,

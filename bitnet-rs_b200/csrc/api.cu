@@ -11,6 +11,7 @@ namespace b200 {
 
 static thread_local std::string t_err;
 std::atomic<uint64_t> g_launches{0};
+thread_local const char* g_last_linear_kernel = "none";
 
 void set_error(const std::string& msg) { t_err = msg; }
 void clear_error() { t_err.clear(); }
@@ -422,18 +423,26 @@ int bitnet_b200_linear_i8(bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, con
         // batched-decode regime: mma.sync kernel without the tcgen05 pipeline's fixed cost (gemm_small.cu). 1 = not its
         // shape, or the other kernel of this M range (tcgen05 GEMM / GEMV) measured faster on it: fall through
         const int rc = launch_gemm_small(ctx, w, q, act_scale, M, y, acc_out, getenv("BITNET_B200_PDL_API") != nullptr);
-        if (rc != 1) return rc;
+        if (rc != 1) return rc;  // g_last_linear_kernel set by the launcher (two variants)
     }
-    if (!force_gemv && gemm_i8_supported(w, M))
+    if (!force_gemv && gemm_i8_supported(w, M)) {
+        g_last_linear_kernel = "gemm_tcgen05";
         return launch_gemm_i8(ctx, w, q, act_scale, M, y, acc_out, nullptr);
-    if (!acc_out && gemm_f16_supported(w, M))  // BitNet32-F16, M >= 9: tcgen05 kind::f16 on s * LUT[code]
+    }
+    if (!acc_out && gemm_f16_supported(w, M)) {  // BitNet32-F16, M >= 9: tcgen05 kind::f16 on s * LUT[code]
+        g_last_linear_kernel = "gemm_f16_tcgen05";
         return launch_gemm_f16(ctx, w, q, act_scale, M, y);
+    }
     if (M <= 8 && !getenv("BITNET_B200_NO_STREAM")) {  // decode fast path (gemv_stream.cu); 1 = shape not covered
         const int rc = launch_gemv_fast(ctx, w, M, /*PRO_Q8*/ 0, q, act_scale, nullptr, nullptr, 0.f, /*EPI_STORE*/ 0,
                                           y, nullptr, acc_out, nullptr, nullptr, nullptr,
                                           getenv("BITNET_B200_PDL_API") != nullptr);
-        if (rc != 1) return rc;
+        if (rc != 1) {
+            g_last_linear_kernel = "gemv_fast";
+            return rc;
+        }
     }
+    g_last_linear_kernel = "gemv";
     return launch_gemv_i8(ctx, w, q, act_scale, M, y, acc_out, nullptr);
 }
 
@@ -614,5 +623,6 @@ int bitnet_b200_qk256_gemv_scalar(float* output, size_t out_len, size_t rows, si
 
 const char* bitnet_b200_version(void) { return "bitnet_b200 0.1.0 (sm_100a)"; }
 uint64_t bitnet_b200_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+const char* bitnet_b200_last_linear_kernel(void) { return b200::g_last_linear_kernel; }
 
 }  // extern "C"

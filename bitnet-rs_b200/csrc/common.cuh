@@ -23,6 +23,7 @@ int fail(const std::string& msg);
 int fail_cuda(const char* what, cudaError_t e);
 extern std::atomic<uint64_t> g_launches;
 inline void count_launch(uint64_t n = 1) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+extern thread_local const char* g_last_linear_kernel;  // diagnostics: bitnet_b200_last_linear_kernel()
 
 #define B200_CUDA(expr)                                                  \
     do {                                                                 \

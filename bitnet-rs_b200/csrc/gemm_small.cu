@@ -57,6 +57,9 @@ struct SmallParams {
     int N, K, M, stride;
     int RW, KW, U, ksplit, NS, CK, npr;
     uint32_t stage_bytes, w_off, red_off, ring_off;
+    // activation-resident mode (gemm_small_resident_kernel)
+    int nseg, ngroups;
+    uint32_t part_off, act_off;
 };
 
 __device__ __forceinline__ void mma_s8_small(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
@@ -266,11 +269,152 @@ gemm_small_kernel(const __grid_constant__ CUtensorMap tm_codes, const __grid_con
     }
 }
 
+// ---- activation-resident variant: many row groups per CTA ------------------------------------------------------------
+// When all of the tokens' int8 activations fit in shared memory next to a weight ring (M x K <= ~128 KB: every M <= 8,
+// M <= 16 up to K = 8192, M <= 32 up to K = 4096) and there are more row groups than SMs (the gate/up projections),
+// a persistent CTA loads the activations ONCE and then only streams weights: one 3-D TMA op brings the full-K codes of a
+// row group (R rows x K / 4 bytes, 20-64 KB) into a ring stage, the warps split K as above, and the KW partial sums of
+// group i meet in a double-buffered shared block while the codes of groups i + 1 .. i + NS - 1 are already in flight.
+// One barrier per group; no cluster, no K split across CTAs. L2 -> SM activation traffic drops from (row groups) x M x K
+// to (CTAs) x M x K, and the per-CTA start-up (barrier init, first-byte latency) is paid once per SM, not per group.
+template <int NT>
+__global__ void __launch_bounds__(32 * SMALL_MAX_CONS)
+gemm_small_resident_kernel(const __grid_constant__ CUtensorMap tm_codes, const __grid_constant__ CUtensorMap tm_q,
+                           const SmallParams p) {
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem);
+    uint64_t* empty = full + SMALL_MAX_STAGES;
+    uint64_t* afull = empty + SMALL_MAX_STAGES;
+    int4* part0 = reinterpret_cast<int4*>(smem + p.part_off);
+    const unsigned char* acts = smem + p.act_off;
+    unsigned char* ring = smem + p.ring_off;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int ncons = p.RW * p.KW;
+    const int R = 32 * p.RW;
+    const int jobs = p.RW * 2 * NT;
+    constexpr uint32_t A_TILE = NT * 8 * 128;
+    const uint32_t w_tile = (uint32_t)R * 64;
+    const int my_groups = (p.ngroups - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+
+    auto issue_group = [&](int i) {  // the codes of this CTA's i-th row group, all of K: one op
+        const int s = i % p.NS;
+        mbar_expect_tx(&full[s], p.stage_bytes);
+        tma_load_3d(ring + (size_t)s * p.stage_bytes, &tm_codes, 0, ((int)blockIdx.x + i * (int)gridDim.x) * R, 0, &full[s]);
+    };
+    if (tid == 0) {
+        tma_prefetch_desc(&tm_codes);
+        tma_prefetch_desc(&tm_q);
+        for (int s = 0; s < p.NS; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], ncons);
+        }
+        mbar_init(afull, 1);
+        mbar_fence_init();
+        for (int i = 0; i < p.NS && i < my_groups; ++i) issue_group(i);
+        pdl_wait();  // the activations are what the previous kernel wrote
+        mbar_expect_tx(afull, (uint32_t)p.nseg * A_TILE);
+        tma_load_3d(smem + p.act_off, &tm_q, 0, 0, 0, afull);
+    }
+    pdl_launch_dependents();
+    __syncthreads();
+
+    const int g = lane >> 2, t = lane & 3;
+    const int kw = warp % p.KW, rw = warp / p.KW;
+    const uint32_t a_lane0 = (uint32_t)g * 128 + (uint32_t)(((2 * t) ^ g) << 4);
+    const uint32_t a_lane1 = (uint32_t)g * 128 + (uint32_t)(((2 * t + 1) ^ g) << 4);
+    const uint32_t w_row = (uint32_t)(32 * rw + g) * 64 + 8 * (t & 1);
+    const uint32_t w_sw0 = (uint32_t)((((t >> 1)) ^ (g >> 1)) << 4), w_sw1 = (uint32_t)(((2 + (t >> 1)) ^ (g >> 1)) << 4);
+    mbar_wait(afull, 0);
+#pragma unroll 1
+    for (int i = 0; i < my_groups; ++i) {
+        const int s = i % p.NS;
+        if (tid == 0 && i >= 1 && i - 1 + p.NS < my_groups) {  // refill the stage every warp has left
+            mbar_wait(&empty[(i - 1) % p.NS], ((i - 1) / p.NS) & 1);
+            issue_group(i - 1 + p.NS);
+        }
+        __syncwarp();
+        int acc[2][NT][4];
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[mt][nt][j] = 0;
+        mbar_wait(&full[s], (i / p.NS) & 1);
+        const unsigned char* st = ring + (size_t)s * p.stage_bytes;
+        // software pipeline over the warp's segments: the code words of segment n + 1 are loaded before the MMAs of
+        // segment n (3-4 warps per scheduler cannot hide an LDS -> decode -> IMMA chain on their own)
+        auto w_ptr = [&](int seg) { return st + w_row + (uint32_t)(seg >> 1) * w_tile + ((seg & 1) ? w_sw1 : w_sw0); };
+        uint2 w0 = make_uint2(0, 0), w1 = w0, w2 = w0, w3 = w0;
+        if (kw < p.nseg) {
+            const unsigned char* wp = w_ptr(kw);
+            w0 = *reinterpret_cast<const uint2*>(wp);
+            w1 = *reinterpret_cast<const uint2*>(wp + 8 * 64);
+            w2 = *reinterpret_cast<const uint2*>(wp + 16 * 64);
+            w3 = *reinterpret_cast<const uint2*>(wp + 24 * 64);
+        }
+#pragma unroll 1
+        for (int seg = kw; seg < p.nseg; seg += p.KW) {
+            const uint2 c0 = w0, c1 = w1, c2 = w2, c3 = w3;
+            if (seg + p.KW < p.nseg) {
+                const unsigned char* wp = w_ptr(seg + p.KW);
+                w0 = *reinterpret_cast<const uint2*>(wp);
+                w1 = *reinterpret_cast<const uint2*>(wp + 8 * 64);
+                w2 = *reinterpret_cast<const uint2*>(wp + 16 * 64);
+                w3 = *reinterpret_cast<const uint2*>(wp + 24 * 64);
+            }
+            const unsigned char* ap = acts + (uint32_t)seg * A_TILE;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const uint4 d0 = decode16(h ? c0.y : c0.x, p.lut);
+                const uint4 d1 = decode16(h ? c1.y : c1.x, p.lut);
+                const uint4 d2 = decode16(h ? c2.y : c2.x, p.lut);
+                const uint4 d3 = decode16(h ? c3.y : c3.x, p.lut);
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt) {
+                    const uint4 b = *reinterpret_cast<const uint4*>(ap + (h ? a_lane1 : a_lane0) + nt * 1024);
+                    mma_s8_small(acc[0][nt], d0.x, d1.x, d0.y, d1.y, b.x, b.y);
+                    mma_s8_small(acc[1][nt], d2.x, d3.x, d2.y, d3.y, b.x, b.y);
+                    mma_s8_small(acc[0][nt], d0.z, d1.z, d0.w, d1.w, b.z, b.w);
+                    mma_s8_small(acc[1][nt], d2.z, d3.z, d2.w, d3.w, b.z, b.w);
+                }
+            }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty[s]);
+        // partial sums of group i -> block i & 1; the block is rewritten two groups later, i.e. after the next barrier,
+        // which every warp only passes once it has finished reading this one
+        int4* part = part0 + (size_t)(i & 1) * jobs * p.KW * 32;
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt)
+                part[((size_t)((rw * 2 + mt) * NT + nt) * p.KW + kw) * 32 + lane] =
+                    make_int4(acc[mt][nt][0], acc[mt][nt][1], acc[mt][nt][2], acc[mt][nt][3]);
+        cons_bar(32 * ncons);
+        const int row0 = ((int)blockIdx.x + i * (int)gridDim.x) * R;
+        for (int j = warp; j < jobs; j += ncons) {
+            int4 v = make_int4(0, 0, 0, 0);
+            for (int k = 0; k < p.KW; ++k) {
+                const int4 x = part[((size_t)j * p.KW + k) * 32 + lane];
+                v.x += x.x;
+                v.y += x.y;
+                v.z += x.z;
+                v.w += x.w;
+            }
+            small_epilogue<NT>(p, j, v, row0, lane);
+        }
+    }
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 struct SmallPlan {
     int NT, RW, KW, U, ksplit, NS, CK, npr, grid_x, threads;
     uint32_t stage_bytes, w_off, red_off, ring_off;
     size_t smem;
+    int resident, nseg, ngroups;  // activation-resident persistent variant
+    uint32_t part_off, act_off;
 };
 
 static int small_nt(int M) {
@@ -307,6 +451,37 @@ static bool small_derive(const bitnet_b200_weight* w, int M, SmallPlan* pl) {
     pl->smem = 1024 + pl->ring_off + (ringb > part ? ringb : part);  // + alignment slack
     pl->grid_x = (int)div_ceil((size_t)N, (size_t)32 * pl->RW);
     pl->threads = 32 * pl->RW * pl->KW;
+    return true;
+}
+
+// the activation-resident variant of (RW, KW): false = does not fit / not worthwhile for this shape
+static bool small_derive_resident(const bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, int M, SmallPlan* pl) {
+    const int K = (int)w->cols, N = (int)w->rows;
+    if (pl->RW < 1 || pl->RW > 2 || pl->KW < 1 || pl->RW * pl->KW > SMALL_MAX_CONS) return false;
+    pl->resident = 1;
+    pl->NT = small_nt(M);
+    pl->ksplit = 1;
+    pl->nseg = K / 128;
+    if (pl->nseg > 256 || pl->nseg / 2 > 256) return false;  // TMA box extents
+    pl->U = (pl->nseg + pl->KW - 1) / pl->KW;
+    pl->CK = K;
+    pl->npr = 1;
+    pl->ngroups = (int)div_ceil((size_t)N, (size_t)32 * pl->RW);
+    if (pl->ngroups <= ctx->num_sms) return false;  // one group per CTA: nothing to keep resident for
+    const int jobs = pl->RW * 2 * pl->NT;
+    pl->part_off = 256;
+    pl->act_off = (uint32_t)((pl->part_off + 2 * jobs * pl->KW * 512 + 1023) & ~1023);
+    pl->ring_off = pl->act_off + (uint32_t)K * pl->NT * 8;
+    pl->stage_bytes = (uint32_t)(32 * pl->RW) * (uint32_t)(K / 4);
+    pl->w_off = 0, pl->red_off = 0;
+    const size_t budget = 224 * 1024;
+    if (pl->ring_off + 2 * (size_t)pl->stage_bytes > budget) return false;
+    int ns = (int)((budget - pl->ring_off) / pl->stage_bytes);
+    if (ns > SMALL_MAX_STAGES) ns = SMALL_MAX_STAGES;
+    pl->NS = ns;
+    pl->smem = 1024 + pl->ring_off + (size_t)ns * pl->stage_bytes;
+    pl->threads = 32 * pl->RW * pl->KW;
+    pl->grid_x = pl->ngroups < ctx->num_sms ? pl->ngroups : ctx->num_sms;
     return true;
 }
 
@@ -389,14 +564,15 @@ bool gemm_small_supported(const bitnet_b200_ctx*, const bitnet_b200_weight* w, i
 template <int NT>
 static int launch_small_nt(const bitnet_b200_ctx* ctx, const SmallPlan& pl, const SmallParams& p, bool pdl) {
     CUtensorMap tm_codes, tm_q;
-    if (make_map_colblocks(&tm_codes, p.codes, (size_t)p.stride, (size_t)p.N, (size_t)p.stride, 32 * pl.RW, 64, pl.CK / 256))
-        return -1;
-    if (make_map_colblocks(&tm_q, p.q, (size_t)p.K, (size_t)p.M, (size_t)p.K, 8 * NT, 128, pl.CK / 128)) return -1;
+    const int w_blk = pl.resident ? p.K / 256 : pl.CK / 256, a_blk = pl.resident ? p.K / 128 : pl.CK / 128;
+    if (make_map_colblocks(&tm_codes, p.codes, (size_t)p.stride, (size_t)p.N, (size_t)p.stride, 32 * pl.RW, 64, w_blk)) return -1;
+    if (make_map_colblocks(&tm_q, p.q, (size_t)p.K, (size_t)p.M, (size_t)p.K, 8 * NT, 128, a_blk)) return -1;
     static bool attr_set[16] = {};
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 16 && !attr_set[dev]) {
         B200_CUDA(cudaFuncSetAttribute(gemm_small_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+        B200_CUDA(cudaFuncSetAttribute(gemm_small_resident_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
         attr_set[dev] = true;
     }
     cudaLaunchConfig_t cfg{};
@@ -420,7 +596,11 @@ static int launch_small_nt(const bitnet_b200_ctx* ctx, const SmallPlan& pl, cons
     }
     cfg.attrs = attr;
     cfg.numAttrs = na;
-    B200_CUDA(cudaLaunchKernelEx(&cfg, gemm_small_kernel<NT>, tm_codes, tm_q, p));
+    if (pl.resident)
+        B200_CUDA(cudaLaunchKernelEx(&cfg, gemm_small_resident_kernel<NT>, tm_codes, tm_q, p));
+    else
+        B200_CUDA(cudaLaunchKernelEx(&cfg, gemm_small_kernel<NT>, tm_codes, tm_q, p));
+    g_last_linear_kernel = pl.resident ? "gemm_small_resident" : "gemm_small";
     count_launch();
     return 0;
 }
@@ -441,6 +621,7 @@ static int run_small_plan(const bitnet_b200_ctx* ctx, const bitnet_b200_weight* 
     p.RW = pl.RW, p.KW = pl.KW, p.U = pl.U, p.ksplit = pl.ksplit, p.NS = pl.NS, p.CK = pl.CK;
     p.npr = pl.npr;
     p.stage_bytes = pl.stage_bytes, p.w_off = pl.w_off, p.red_off = pl.red_off, p.ring_off = pl.ring_off;
+    p.nseg = pl.nseg, p.ngroups = pl.ngroups, p.part_off = pl.part_off, p.act_off = pl.act_off;
     switch (pl.NT) {
         case 1: return launch_small_nt<1>(ctx, pl, p, pdl);
         case 2: return launch_small_nt<2>(ctx, pl, p, pdl);
@@ -477,6 +658,12 @@ static bool small_autotune(const bitnet_b200_ctx* ctx, const bitnet_b200_weight*
     auto cands = small_candidates(ctx, w, M);
     if (cands.empty()) return false;
     if ((int)cands.size() > SMALL_TUNE_CANDS) cands.resize(SMALL_TUNE_CANDS);
+    static const int res_grid[6][2] = {{1, 8}, {1, 12}, {1, 16}, {2, 4}, {2, 6}, {2, 8}};  // (RW, KW) of the resident variant
+    for (const auto& rg : res_grid) {
+        SmallPlan pl{};
+        pl.RW = rg[0], pl.KW = rg[1];
+        if (small_derive_resident(ctx, w, M, &pl)) cands.emplace_back(0.0, pl);
+    }
     static void* flush[16] = {};
     constexpr size_t FLUSH_BYTES = 256u << 20;  // > L2
     const int dev = ctx->device;
@@ -536,7 +723,10 @@ int launch_gemm_small(const bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, c
     if (reinterpret_cast<uintptr_t>(q) & 15) return 1;
     if (const char* e = getenv("BITNET_B200_SMALLM_PLAN")) {  // tuning / test knob: "RW,KW,U,ksplit"
         SmallPlan pl{};
-        if (sscanf(e, "%d,%d,%d,%d", &pl.RW, &pl.KW, &pl.U, &pl.ksplit) != 4 || !small_derive(w, M, &pl))
+        if (e[0] == 'R') {  // "R,RW,KW": the activation-resident variant
+            if (sscanf(e + 1, ",%d,%d", &pl.RW, &pl.KW) != 2 || !small_derive_resident(ctx, w, M, &pl))
+                return fail("linear_i8: BITNET_B200_SMALLM_PLAN (resident) is not realisable for this shape");
+        } else if (sscanf(e, "%d,%d,%d,%d", &pl.RW, &pl.KW, &pl.U, &pl.ksplit) != 4 || !small_derive(w, M, &pl))
             return fail("linear_i8: BITNET_B200_SMALLM_PLAN is not realisable for this shape");
         return run_small_plan(ctx, w, pl, q, act_scale, M, y, acc_out, pdl);
     }
@@ -568,10 +758,11 @@ int launch_gemm_small(const bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, c
                 chosen[key] = ch;
                 have = true;
                 if (getenv("BITNET_B200_SMALLM_VERBOSE"))
-                    fprintf(stderr, "[bitnet_b200] linear_i8 %zux%zu M=%d: %s (gemm_small RW=%d KW=%d U=%d ksplit=%d: %.1f us, %s: %.1f us)\n",
-                            w->rows, w->cols, M, ch.use_alt ? "alternative" : "gemm_small", ch.pl.RW, ch.pl.KW, ch.pl.U,
-                            ch.pl.ksplit, ch.us_small, M >= 9 ? "tcgen05 gemm" : "gemv", ch.us_alt);
+                    fprintf(stderr, "[bitnet_b200] linear_i8 %zux%zu M=%d: %s (gemm_small%s RW=%d KW=%d U=%d ksplit=%d: %.1f us, %s: %.1f us)\n",
+                            w->rows, w->cols, M, ch.use_alt ? "alternative" : "gemm_small", ch.pl.resident ? " resident" : "",
+                            ch.pl.RW, ch.pl.KW, ch.pl.U, ch.pl.ksplit, ch.us_small, M >= 9 ? "tcgen05 gemm" : "gemv", ch.us_alt);
                 // the call's result is already in y / acc_out (every candidate computed it)
+                g_last_linear_kernel = "autotune";
                 return 0;
             }
         }
@@ -583,8 +774,7 @@ int launch_gemm_small(const bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, c
         }
     }
     if (ch.use_alt) return 1;
-    SmallPlan pl = ch.pl;
-    if (!small_derive(w, M, &pl)) return 1;  // same NT bucket, this M: derived fields do not depend on M beyond NT
+    SmallPlan pl = ch.pl;  // same NT bucket: the derived fields do not depend on M beyond NT
     return run_small_plan(ctx, w, pl, q, act_scale, M, y, acc_out, pdl);
 }
 

@@ -19,6 +19,7 @@ SYMBOLS = [
     "bitnet_b200_actquant_i8", "bitnet_b200_rmsnorm_actquant", "bitnet_b200_linear_i8", "bitnet_b200_linear_i8_swiglu",
     "bitnet_b200_linear_f32", "bitnet_b200_fused_linear", "bitnet_b200_i2s_matmul_f32", "bitnet_b200_version",
     "bitnet_b200_launch_count",
+    "bitnet_b200_last_linear_kernel",
     "bitnet_b200_model_create", "bitnet_b200_model_destroy", "bitnet_b200_model_set_layer",
     "bitnet_b200_model_set_embedding", "bitnet_b200_model_set_rope", "bitnet_b200_model_reset",
     "bitnet_b200_model_decode", "bitnet_b200_model_decode_device", "bitnet_b200_model_set_tokens",
@@ -126,6 +127,7 @@ def lib():
             fn.argtypes = [vp, sz, sz, sz, vp, sz, vp, sz, vp, sz]
         l.bitnet_b200_version.restype = C.c_char_p
         l.bitnet_b200_launch_count.restype = C.c_uint64
+        l.bitnet_b200_last_linear_kernel.restype = C.c_char_p
         _lib = l
     return _lib
 
@@ -142,3 +144,8 @@ def check(rc):
 
 def launch_count():
     return int(lib().bitnet_b200_launch_count())
+
+
+def last_linear_kernel():
+    """the kernel the calling thread's last linear_i8 ran (diagnostics)"""
+    return lib().bitnet_b200_last_linear_kernel().decode()

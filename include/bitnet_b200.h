@@ -275,6 +275,9 @@ int bitnet_b200_tp_xchg_max_actquant(bitnet_b200_ctx* ctx, const bitnet_b200_tp_
 const char* bitnet_b200_version(void);
 /* number of kernels this library has launched on the calling process (bench bookkeeping) */
 uint64_t bitnet_b200_launch_count(void);
+/* which kernel the calling thread's last bitnet_b200_linear_i8 ran: "gemm_small", "gemm_small_resident",
+ * "gemm_tcgen05", "gemm_f16_tcgen05", "gemv_fast" or "gemv" (diagnostics: bench labels and routing tests) */
+const char* bitnet_b200_last_linear_kernel(void);
 
 #ifdef __cplusplus
 }

@@ -297,6 +297,7 @@ def test_linear_qk256_gemm_small(ctx, b200, oracle, rows, cols, M, monkeypatch):
     # and the same integers from the tcgen05 GEMM on the other side of the routing boundary
     monkeypatch.setenv("BITNET_B200_SMALLM_MAX", "0")
     y3, acc3 = ctx.linear_i8(w, dev(q), dev(s), want_acc=True)
+    assert b200.last_linear_kernel() in ("gemm_tcgen05", "gemv_fast", "gemv")
     assert torch.equal(acc3, acc) and torch.equal(y3, y)
 
 
@@ -324,6 +325,31 @@ def test_linear_qk256_gemm_small_every_plan(ctx, b200, oracle, rows, cols, M, pl
         assert b200.launch_count() - l0 == 1, plan
         assert np.array_equal(acc.cpu().numpy(), racc), plan
         assert np.array_equal(y.cpu().numpy(), ry), plan
+
+
+# the activation-resident persistent variant (more row groups than SMs, all tokens' activations kept in shared memory):
+# every warp grid, ragged last row group, ring wrap-around (up to 7 groups per CTA), M below / at a token-tile edge
+@pytest.mark.parametrize("rows,cols,M", [(13824, 2560, 16), (13001, 2560, 32), (14336, 4096, 5), (9999, 6912, 8),
+                                         (28672, 4096, 9), (6000, 256, 24)])
+def test_linear_qk256_gemm_small_resident(ctx, b200, oracle, rows, cols, M, monkeypatch):
+    qs, q, s = _qk256_case(oracle, rows, cols, M, rows + 7 * M)
+    w = ctx.weight(qs, b200.LAYOUT_QK256, rows, cols)
+    racc, ry = oracle.linear_qk256_i8(qs, rows, cols, q, s)
+    ran = 0
+    for plan in ("R,1,8", "R,1,12", "R,1,16", "R,2,4", "R,2,6", "R,2,8"):
+        monkeypatch.setenv("BITNET_B200_SMALLM_PLAN", plan)
+        l0 = b200.launch_count()
+        try:
+            y, acc = ctx.linear_i8(w, dev(q), dev(s), want_acc=True)
+        except b200.B200Error as ex:     # a forced plan that does not fit in shared memory is refused, not rerouted
+            assert "not realisable" in str(ex)
+            continue
+        ran += 1
+        assert b200.last_linear_kernel() == "gemm_small_resident"
+        assert b200.launch_count() - l0 == 1, plan
+        assert np.array_equal(acc.cpu().numpy(), racc), plan
+        assert np.array_equal(y.cpu().numpy(), ry), plan
+    assert ran >= 2
 
 
 def test_linear_qk256_gemm_small_extremes_and_maps(ctx, b200, oracle):

@@ -77,7 +77,7 @@ def main():
             us = graph_time(lambda i: ctx.linear_i8(ws[i % len(ws)], q, s, y=y, acc_out=acc), 100)
             row = {"shape": name, "N": rows, "K": cols, "M": M, "layout": args.layout, "us": round(us, 2),
                    "GBs_weights": round(wbytes / us / 1e3, 1), "TOPS": round(2.0 * M * rows * cols / us / 1e6, 1),
-                   "launches_per_call": (b2.launch_count() - l0) / (3 + 100), "acc_out": bool(args.acc)}
+                   "kernel": b2.last_linear_kernel(), "acc_out": bool(args.acc)}
             line = json.dumps(row)
             print(line, flush=True)
             if out:
