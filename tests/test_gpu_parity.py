@@ -323,6 +323,7 @@ def test_linear_qk256_gemm_small_every_plan(ctx, b200, oracle, rows, cols, M, pl
         l0 = b200.launch_count()
         y, acc = ctx.linear_i8(w, dev(q), dev(s), want_acc=True)
         assert b200.launch_count() - l0 == 1, plan
+        assert b200.last_linear_kernel() == "gemm_small"
         assert np.array_equal(acc.cpu().numpy(), racc), plan
         assert np.array_equal(y.cpu().numpy(), ry), plan
 
