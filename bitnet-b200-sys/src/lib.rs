@@ -113,6 +113,12 @@ extern "C" {
         ctx: *mut bitnet_b200_ctx, w: *const bitnet_b200_weight, q: *const i8, act_scale: *const c_float, m: c_int,
         h: *mut c_float,
     ) -> c_int;
+    /// No counterpart in the reference: linear_i8 whose split-K scratch is
+    /// a static device array of the library (4 MiB + 32 KiB per GPU); allocates nothing; overlapping calls on a GPU race.
+    pub fn bitnet_b200_linear_i8_static_scratch(
+        ctx: *mut bitnet_b200_ctx, w: *const bitnet_b200_weight, q: *const i8, act_scale: *const c_float, m: c_int,
+        y: *mut c_float,
+    ) -> c_int;
     pub fn bitnet_b200_fused_linear(
         ctx: *mut bitnet_b200_ctx, w: *const bitnet_b200_weight, x: *const c_float, gamma: *const c_float,
         eps: c_float, m: c_int, epilogue: c_int, y: *mut c_float, residual: *const c_float, q_out: *mut i8,

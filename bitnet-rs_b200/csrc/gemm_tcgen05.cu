@@ -513,4 +513,80 @@ int launch_gemm_i8(const bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, cons
     return 0;
 }
 
+// ---- the same GEMM for callers that must not allocate (no counterpart in the reference) ----------------------------
+// bitnet_b200_linear_i8_static_scratch: the split-K scratch (ticket counters + int32 accumulation blocks) that
+// launch_gemm_i8 otherwise takes from two cudaMalloc'ed buffers of the context lives in ONE file-scope device array of a
+// fixed size. Every GPU that loads the library holds it until the process exits; every call on a GPU shares it, so calls
+// that overlap on that GPU (two streams, two host threads) race on it.
+constexpr size_t G_STATIC_COUNTER_BYTES = G_MAX_TILE_COUNTERS * sizeof(int);  // 32 KiB, at the start of the array
+constexpr size_t G_STATIC_BLOCK_BYTES = 4u << 20;                              // 4 MiB of accumulation blocks after them
+constexpr size_t G_STATIC_WORDS = (G_STATIC_COUNTER_BYTES + G_STATIC_BLOCK_BYTES) / 4;
+static __device__ __align__(256) int32_t g_static_scratch[G_STATIC_WORDS];
+
+// The name g_static_scratch is only a host-side stand-in in host code: the device address comes from
+// cudaGetSymbolAddress, once per device, with that device current.
+static int static_scratch_ptr(int device, int32_t** out) {
+    static std::mutex mu;
+    static int32_t* ptr[64] = {};
+    if (device < 0 || device >= 64) return fail("linear_i8_static_scratch: device ordinal out of range");
+    std::lock_guard<std::mutex> lk(mu);
+    if (!ptr[device]) {
+        int cur = -1;
+        B200_CUDA(cudaGetDevice(&cur));
+        if (cur != device) return fail("linear_i8_static_scratch: the context's device is not current");
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (e != cudaSuccess || !p) return fail_cuda("cudaGetSymbolAddress(g_static_scratch)", e);
+        ptr[device] = static_cast<int32_t*>(p);
+    }
+    *out = ptr[device];
+    return 0;
+}
+
+// bytes of accumulation blocks the planner of launch_gemm_i8 may use for this shape: the largest over its tile shapes
+static size_t static_scratch_need(const bitnet_b200_weight* w, int M) {
+    const size_t n_rt = div_ceil(w->rows, G_ROWS);
+    const int m16 = (int)(div_ceil((size_t)M, 16) * 16);
+    static const int bn_c[] = {16, 32, 64, 128, 256};
+    size_t need = 0;
+    for (int bi = 0; bi < 5; ++bi) {
+        int BN = bn_c[bi] < m16 ? bn_c[bi] : m16;
+        if (BN > 256) BN = 256;
+        const size_t n_mt = div_ceil((size_t)M, (size_t)BN);
+        BN = (int)(div_ceil(div_ceil((size_t)M, n_mt), 16) * 16);
+        const size_t b = n_rt * n_mt * (size_t)BN * G_ROWS * 4;
+        if (b > need) need = b;
+    }
+    return need;
+}
+
+int launch_gemm_i8_static_scratch(const bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, const int8_t* q,
+                                  const float* act_scale, int M, float* y) {
+    if (!gemm_i8_supported(w, M))
+        return fail("linear_i8_static_scratch: QK256 weights with cols % 128 == 0 and M >= 9 only (the tcgen05 GEMM)");
+    const size_t need = static_scratch_need(w, M);
+    if (need > G_STATIC_BLOCK_BYTES)
+        return fail("linear_i8_static_scratch: rows x M too large for the 4 MiB static scratch (needs " + std::to_string(need) +
+                    " bytes: 512 bytes per 128-row tile and token); use bitnet_b200_linear_i8");
+    int32_t* base = nullptr;
+    if (static_scratch_ptr(ctx->device, &base)) return -1;
+    // the array keeps what the last call left: the kernel re-zeroes what it used, but a call that was cut short (a
+    // fault, a forced split on another shape) must not leak into this one -> clear the tickets and the blocks we may use
+    B200_CUDA(cudaMemsetAsync(base, 0, G_STATIC_COUNTER_BYTES + need, ctx->stream));
+    bitnet_b200_ctx view = *ctx;  // same stream / device; scratch pointers -> the static array, nothing to allocate
+    view.gemm_counters = reinterpret_cast<int*>(base);
+    view.gemm_scratch = base + G_STATIC_COUNTER_BYTES / 4;
+    return launch_gemm_i8(&view, w, q, act_scale, M, y, nullptr, nullptr);
+}
+
 }  // namespace b200
+
+extern "C" int bitnet_b200_linear_i8_static_scratch(bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, const int8_t* q,
+                                                    const float* act_scale, int M, float* y) {
+    using namespace b200;
+    if (!ctx || !w || !q || !act_scale || !y) return fail("linear_i8_static_scratch: NULL argument");
+    if (M <= 0) return fail("linear_i8_static_scratch: M must be > 0");
+    if (w->device != ctx->device) return fail("linear_i8_static_scratch: weight lives on another device");
+    B200_CUDA(cudaSetDevice(ctx->device));
+    return launch_gemm_i8_static_scratch(ctx, w, q, act_scale, M, y);
+}

@@ -122,6 +122,20 @@ class Context:
             M, _dev_ptr(y, torch.float32, "y"), None if acc is None else acc.data_ptr()))
         return (y, acc) if (want_acc or acc_out is not None) else y
 
+    def linear_i8_static_scratch(self, w, q, act_scale, y):
+        """linear_i8 (tcgen05 GEMM, QK256, M >= 9) with the split-K scratch in the library's static device array: the call
+        allocates nothing (y is the caller's). Calls that overlap on one GPU race on the shared scratch."""
+        torch = _torch()
+        M = q.shape[0]
+        if q.shape[1] != w.cols:
+            raise ValueError("q has %d columns, weight has %d" % (q.shape[1], w.cols))
+        if y.shape != (M, w.rows):
+            raise ValueError("y must be [M, rows]")
+        ffi.check(self._lib.bitnet_b200_linear_i8_static_scratch(
+            self._h, w._h, _dev_ptr(q, torch.int8, "q"), _dev_ptr(act_scale, torch.float32, "act_scale"), M,
+            _dev_ptr(y, torch.float32, "y")))
+        return y
+
     def linear_i8_swiglu(self, w, q, act_scale, h=None):
         """linear_i8 on an interleaved (gate, up) weight with SwiGLU in the GEMM epilogue: h [M, rows/2] (M >= 9)."""
         torch = _torch()

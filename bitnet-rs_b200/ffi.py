@@ -17,6 +17,7 @@ SYMBOLS = [
     "bitnet_b200_ctx_destroy", "bitnet_b200_weight_create", "bitnet_b200_weight_destroy",
     "bitnet_b200_weight_rows", "bitnet_b200_weight_cols", "bitnet_b200_weight_nbytes",
     "bitnet_b200_actquant_i8", "bitnet_b200_rmsnorm_actquant", "bitnet_b200_linear_i8", "bitnet_b200_linear_i8_swiglu",
+    "bitnet_b200_linear_i8_static_scratch",
     "bitnet_b200_linear_f32", "bitnet_b200_fused_linear", "bitnet_b200_i2s_matmul_f32", "bitnet_b200_version",
     "bitnet_b200_launch_count",
     "bitnet_b200_last_linear_kernel",
@@ -98,6 +99,7 @@ def lib():
         l.bitnet_b200_rmsnorm_actquant.argtypes = [vp, vp, vp, C.c_float, i32, i32, vp, vp, vp]
         l.bitnet_b200_linear_i8.argtypes = [vp, vp, vp, vp, i32, vp, vp]
         l.bitnet_b200_linear_i8_swiglu.argtypes = [vp, vp, vp, vp, i32, vp]
+        l.bitnet_b200_linear_i8_static_scratch.argtypes = [vp, vp, vp, vp, i32, vp]
         l.bitnet_b200_linear_f32.argtypes = [vp, vp, vp, i32, vp]
         l.bitnet_b200_fused_linear.argtypes = [vp, vp, vp, vp, C.c_float, i32, i32, vp, vp, vp, vp]
         l.bitnet_b200_i2s_matmul_f32.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32]

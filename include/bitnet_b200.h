@@ -146,6 +146,18 @@ int bitnet_b200_linear_i8(bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, con
  * crates/bitnet-transformer/src/lib.rs:756-789. h: [M, F] f32, DEVICE. */
 int bitnet_b200_linear_i8_swiglu(bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, const int8_t* q,
                                  const float* act_scale, int M, float* h);
+/* linear_i8 for callers that must not allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc). No counterpart in the reference.
+ * Same result as bitnet_b200_linear_i8 bit for bit (the tcgen05 GEMM, QK256 weights, cols % 128 == 0, M >= 9, no
+ * acc_out), but the split-K scratch lives in a file-scope device array of the library instead of cudaMalloc'ed
+ * buffers of the context: 32 KiB of ticket counters + 4 MiB of int32 accumulation blocks, held by every GPU that loads
+ * the library until the process exits. Limit: ceil(rows / 128) * (tokens, padded per token tile to 16) * 512 bytes
+ * <= 4 MiB, e.g. 13824 x 64, 4096 x 256, 2560 x 320; larger problems are rejected with an error naming the bytes
+ * needed. The call itself allocates nothing and clears the part of the array it may use before the launch (on the
+ * context's stream). Every call on a GPU shares the array: calls that overlap on that GPU (two streams, two host
+ * threads) race on it -- serialise them or use bitnet_b200_linear_i8. */
+int bitnet_b200_linear_i8_static_scratch(bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, const int8_t* q,
+                                         const float* act_scale, int M, float* y);
 /* The decode fast path as ONE launch (gemv_stream.cu): [RMSNorm ->] per-token absmax int8
  * quantise -> ternary linear -> epilogue. It is the composition of rmsnorm_actquant /
  * actquant_i8 and linear_i8 above, bit for bit, with the activation work done in the GEMV's
