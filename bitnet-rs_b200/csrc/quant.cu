@@ -250,7 +250,7 @@ int launch_tp_xchg_sum_norm_quant(const bitnet_b200_ctx* ctx, const bitnet_b200_
 }
 
 // all-reduce(MAX) of the per-token absmax + quantize_symmetric_i8 of the local slice with it (tp_quant_absmax_kernel)
-__global__ void __launch_bounds__(256) tp_xchg_max_quant_kernel(const __grid_constant__ bitnet_b200_tp_xchg xc,
+__global__ void __launch_bounds__(1024) tp_xchg_max_quant_kernel(const __grid_constant__ bitnet_b200_tp_xchg xc,
                                                                 const float* __restrict__ x, int K, int8_t* __restrict__ q,
                                                                 float* __restrict__ scale) {
     const uint32_t epoch = xchg_begin(xc);
@@ -263,7 +263,23 @@ __global__ void __launch_bounds__(256) tp_xchg_max_quant_kernel(const __grid_con
     if (threadIdx.x == 0) scale[row] = sc;
     const float* xr = x + (size_t)row * K;
     int8_t* qr = q + (size_t)row * K;
-    for (int k = threadIdx.x; k < K; k += blockDim.x) qr[k] = (int8_t)(amax == 0.f ? 0 : quant1(xr[k], inv));
+    if (K % 4 == 0 && !(reinterpret_cast<uintptr_t>(x) & 15) && !(reinterpret_cast<uintptr_t>(q) & 3)) {
+        // 16-byte loads, four in flight per thread (tp_ops.cu: tp_quant_absmax_vec_kernel); same bits per element
+        const float4* x4 = reinterpret_cast<const float4*>(xr);
+        uint32_t* q4 = reinterpret_cast<uint32_t*>(qr);
+        const int n4 = K >> 2;
+#pragma unroll 4
+        for (int i = threadIdx.x; i < n4; i += blockDim.x) {
+            const float4 v = x4[i];
+            uint32_t o = 0;
+            if (amax != 0.f)
+                o = (uint32_t)(uint8_t)quant1(v.x, inv) | ((uint32_t)(uint8_t)quant1(v.y, inv) << 8) |
+                    ((uint32_t)(uint8_t)quant1(v.z, inv) << 16) | ((uint32_t)(uint8_t)quant1(v.w, inv) << 24);
+            q4[i] = o;
+        }
+    } else {
+        for (int k = threadIdx.x; k < K; k += blockDim.x) qr[k] = (int8_t)(amax == 0.f ? 0 : quant1(xr[k], inv));
+    }
     xchg_end(xc, epoch);
 }
 
@@ -273,7 +289,9 @@ int launch_tp_xchg_max_quant(const bitnet_b200_ctx* ctx, const bitnet_b200_tp_xc
     if (xc->n_ranks < 1 || xc->n_ranks > TP_MAX_RANKS || xc->rank < 0 || xc->rank >= xc->n_ranks || xc->slot < 0 ||
         xc->slot >= TP_SLOTS || !(xc->phase & 3))
         return fail("tp_xchg: bad descriptor (ranks 1..8, slot 0..3, phase 1..3)");
-    tp_xchg_max_quant_kernel<<<(xc->phase & 2) ? M : 1, 256, 0, ctx->stream>>>(*xc, x, K, q, scale);
+    int threads = (K / 4 + 31) / 32 * 32;  // one 16-byte item per thread where the row allows it
+    threads = threads < 64 ? 64 : threads > 1024 ? 1024 : threads;
+    tp_xchg_max_quant_kernel<<<(xc->phase & 2) ? M : 1, threads, 0, ctx->stream>>>(*xc, x, K, q, scale);
     B200_LAUNCH_CHECK("tp_xchg_max_quant_kernel");
     return 0;
 }
