@@ -163,34 +163,51 @@ __global__ void __launch_bounds__(1024) actquant_fast_kernel(const float* __rest
 // ---------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(1024) tp_xchg_sum_norm_quant_kernel(const __grid_constant__ bitnet_b200_tp_xchg xc,
                                                                       const float* __restrict__ act_scale, float* __restrict__ x,
-                                                                      const float* __restrict__ gamma, float eps, int K,
+                                                                      const float* __restrict__ gamma, float eps, int K, int nts,
                                                                       int8_t* __restrict__ q, float* __restrict__ scale,
                                                                       float* __restrict__ normed) {
+    extern __shared__ __align__(16) float xrow[];  // [K] the updated residual row
     __shared__ float shf[32];
     __shared__ double shd[32];
     const uint32_t epoch = xchg_begin(xc);
     if (!(xc.phase & 2)) return;
-    const int row = blockIdx.x, tid = threadIdx.x, nt = blockDim.x;
+    const int row = blockIdx.x, tid = threadIdx.x;
     float* xr = x + (size_t)row * K;
     const float as = act_scale[row];
+    // Phase 1, all threads: pull the peers' int32 partials, every rank's load of a 16-byte group in flight at once
+    // (NVLink latency is paid once per group, not once per rank), add, apply the residual epilogue, keep the row in
+    // shared memory. Integer sums: the order over ranks is free.
+    for (int i = tid; i < (K >> 2); i += blockDim.x) {  // K % 4 == 0 (launcher)
+        int4 pv[TP_MAX_RANKS];
+#pragma unroll
+        for (int r = 0; r < TP_MAX_RANKS; ++r)
+            if (r < xc.n_ranks) pv[r] = ld_sys_s32x4(static_cast<const int32_t*>(xc.peer_data[r]) + (size_t)row * K + 4 * i);
+        int4 a = make_int4(0, 0, 0, 0);
+#pragma unroll
+        for (int r = 0; r < TP_MAX_RANKS; ++r)
+            if (r < xc.n_ranks) { a.x += pv[r].x; a.y += pv[r].y; a.z += pv[r].z; a.w += pv[r].w; }
+        float4 xv = *reinterpret_cast<const float4*>(xr + 4 * i);
+        xv.x = __fadd_rn(xv.x, __fmul_rn(as, (float)a.x));  // as tp_residual_acc_kernel / EPI_RESIDUAL
+        xv.y = __fadd_rn(xv.y, __fmul_rn(as, (float)a.y));
+        xv.z = __fadd_rn(xv.z, __fmul_rn(as, (float)a.z));
+        xv.w = __fadd_rn(xv.w, __fmul_rn(as, (float)a.w));
+        *reinterpret_cast<float4*>(xr + 4 * i) = xv;
+        *reinterpret_cast<float4*>(xrow + 4 * i) = xv;
+    }
+    __syncthreads();
+    // Phase 2: the row statistics and the quantiser with the thread -> element map and the reduction trees of
+    // actquant_fast_kernel<1> at nts threads; threads beyond nts hold zeros, which change neither the f64 sum nor
+    // the max (x + 0.0 == x, values are magnitudes), so the bits are those of the three-kernel form.
+    const int nt = nts;
+    const bool act = tid < nts;
     float v[16];
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
         const int k0 = (tid + j * nt) * 4;
 #pragma unroll
         for (int e = 0; e < 4; ++e) v[j * 4 + e] = 0.f;
-        if (k0 + 4 <= K) {  // K % 4 == 0 (launcher)
-            int4 a = make_int4(0, 0, 0, 0);
-            for (int r = 0; r < xc.n_ranks; ++r) {
-                const int4 pv = ld_sys_s32x4(static_cast<const int32_t*>(xc.peer_data[r]) + (size_t)row * K + k0);
-                a.x += pv.x; a.y += pv.y; a.z += pv.z; a.w += pv.w;
-            }
-            float4 xv = *reinterpret_cast<const float4*>(xr + k0);
-            xv.x = __fadd_rn(xv.x, __fmul_rn(as, (float)a.x));  // as tp_residual_acc_kernel / EPI_RESIDUAL
-            xv.y = __fadd_rn(xv.y, __fmul_rn(as, (float)a.y));
-            xv.z = __fadd_rn(xv.z, __fmul_rn(as, (float)a.z));
-            xv.w = __fadd_rn(xv.w, __fmul_rn(as, (float)a.w));
-            *reinterpret_cast<float4*>(xr + k0) = xv;
+        if (act && k0 + 4 <= K) {
+            const float4 xv = *reinterpret_cast<const float4*>(xrow + k0);
             v[j * 4 + 0] = xv.x; v[j * 4 + 1] = xv.y; v[j * 4 + 2] = xv.z; v[j * 4 + 3] = xv.w;
         }
     }
@@ -203,7 +220,7 @@ __global__ void __launch_bounds__(1024) tp_xchg_sum_norm_quant_kernel(const __gr
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
         const int k0 = (tid + j * nt) * 4;
-        if (k0 + 4 <= K) {
+        if (act && k0 + 4 <= K) {
             const float4 g = *reinterpret_cast<const float4*>(gamma + k0);
             v[j * 4 + 0] = v[j * 4 + 0] * inv_rms * g.x;
             v[j * 4 + 1] = v[j * 4 + 1] * inv_rms * g.y;
@@ -223,7 +240,7 @@ __global__ void __launch_bounds__(1024) tp_xchg_sum_norm_quant_kernel(const __gr
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
         const int k0 = (tid + j * nt) * 4;
-        if (k0 + 4 > K) continue;
+        if (!act || k0 + 4 > K) continue;
         int b[4];
 #pragma unroll
         for (int e = 0; e < 4; ++e) b[e] = amax == 0.f ? 0 : quant1(v[j * 4 + e], inv);
@@ -240,11 +257,21 @@ int launch_tp_xchg_sum_norm_quant(const bitnet_b200_ctx* ctx, const bitnet_b200_
     if (xc->n_ranks < 1 || xc->n_ranks > TP_MAX_RANKS || xc->rank < 0 || xc->rank >= xc->n_ranks || xc->slot < 0 ||
         xc->slot >= TP_SLOTS || !(xc->phase & 3))
         return fail("tp_xchg: bad descriptor (ranks 1..8, slot 0..3, phase 1..3)");
-    int threads = (int)div_ceil((size_t)K, 16);   // the thread count of actquant_fast_kernel: same element map
-    threads = (int)div_ceil((size_t)threads, 32) * 32;
-    if (threads < 64) threads = 64;
+    int nts = (int)div_ceil((size_t)K, 16);   // the thread count of actquant_fast_kernel: same element map
+    nts = (int)div_ceil((size_t)nts, 32) * 32;
+    if (nts < 64) nts = 64;
+    int threads = (int)div_ceil((size_t)K / 4, 32) * 32;  // one 16-byte group per thread in the pull phase
+    threads = threads < nts ? nts : threads > 1024 ? 1024 : threads;
+    static bool attr_set[16] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 16 && !attr_set[dev]) {
+        B200_CUDA(cudaFuncSetAttribute(tp_xchg_sum_norm_quant_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+        attr_set[dev] = true;
+    }
     const int grid = (xc->phase & 2) ? M : 1;
-    tp_xchg_sum_norm_quant_kernel<<<grid, threads, 0, ctx->stream>>>(*xc, act_scale, x, gamma, eps, K, q, scale, normed);
+    tp_xchg_sum_norm_quant_kernel<<<grid, threads, (size_t)K * 4, ctx->stream>>>(*xc, act_scale, x, gamma, eps, K, nts, q, scale,
+                                                                                normed);
     B200_LAUNCH_CHECK("tp_xchg_sum_norm_quant_kernel");
     return 0;
 }
@@ -256,8 +283,12 @@ __global__ void __launch_bounds__(1024) tp_xchg_max_quant_kernel(const __grid_co
     const uint32_t epoch = xchg_begin(xc);
     if (!(xc.phase & 2)) return;
     const int row = blockIdx.x;
+    __shared__ float pm[TP_MAX_RANKS];
+    if ((int)threadIdx.x < xc.n_ranks)  // one peer per thread: one NVLink round trip, not n_ranks in a chain
+        pm[threadIdx.x] = ld_sys_f32(static_cast<const float*>(xc.peer_data[threadIdx.x]) + row);
+    __syncthreads();
     float amax = 0.f;
-    for (int r = 0; r < xc.n_ranks; ++r) amax = fmaxf(amax, ld_sys_f32(static_cast<const float*>(xc.peer_data[r]) + row));
+    for (int r = 0; r < xc.n_ranks; ++r) amax = fmaxf(amax, pm[r]);
     const float sc = amax == 0.f ? 0.f : amax / 127.f;
     const float inv = amax == 0.f ? 0.f : 1.0f / sc;
     if (threadIdx.x == 0) scale[row] = sc;

@@ -226,6 +226,201 @@ __global__ void __launch_bounds__(128) tp_attn_decode_kernel(const float* __rest
     }
 }
 
+// ---- RoPE + KV append + GQA decode attention in ONE kernel, one CTA per (KV head, sequence) ---------------------------
+// The two kernels above cost 27 us per layer at batch 64 (in-graph, tools/tp_layer_prof.py): one CTA per QUERY head re-reads
+// its group's K and V, walks the positions one dependent row load at a time, and RoPE is a launch of its own. Here the
+// CTA of a KV head rotates and appends its k / v row (kept in shared memory for the new position), and each warp owns
+// one (query head of the group, slice of the positions): q rotated in registers (a RoPE pair lives in one lane), one
+// pass over the positions with the softmax folded in (running max / sum), four positions' K and V rows in flight per
+// step, and a log-sum-exp merge of the S position slices through shared memory at the end. The K / V rows of a group are
+// read from L2 once per CTA and hit in L1 for the other query heads.
+__device__ __forceinline__ void cp_async16(void* dst_smem, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst_smem)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+template <int PER>  // head_dim / 32
+__global__ void __launch_bounds__(512) tp_rope_attn_gqa_kernel(float* __restrict__ qkv, const float* __restrict__ cos_t,
+                                                               const float* __restrict__ sin_t, float* __restrict__ kc,
+                                                               float* __restrict__ vc, float* __restrict__ att,
+                                                               const int* __restrict__ pos_p, int NH, int NKV, int max_ctx,
+                                                               int S) {
+    constexpr int D = 32 * PER, HALF = D / 2, CH = PER <= 4 ? 16 : 8;  // positions per shared-memory chunk
+    extern __shared__ __align__(16) float sm[];
+    float* knew = sm;            // [D] the rotated k row of this step
+    float* vnew = sm + D;        // [D]
+    float* mg_m = sm + 2 * D;    // [warps] slice maxima   (S > 1)
+    const int g = blockIdx.x, b = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int nwarps = blockDim.x >> 5, R = NH / NKV;
+    float* mg_l = mg_m + nwarps;      // [warps] slice sums
+    float* mg_a = mg_m + ((2 * nwarps + 3) & ~3);  // [warps][D] slice accumulators (16-byte aligned)
+    const int hq = warp / S, sp = warp - hq * S, head = g * R + hq;
+    const int pos = *pos_p;
+    float* row = qkv + (size_t)b * (NH + 2 * NKV) * D;
+    float* kb = kc + ((size_t)b * NKV + g) * max_ctx * D;
+    float* vb = vc + ((size_t)b * NKV + g) * max_ctx * D;
+    const float* cp = cos_t + (size_t)pos * HALF;
+    const float* sp_t = sin_t + (size_t)pos * HALF;
+    // k: rotate, append, keep; v: append, keep (same arithmetic as tp_rope_kv_kernel)
+    for (int i = tid; i < HALF; i += blockDim.x) {
+        const float* k = row + (size_t)(NH + g) * D;
+        const float c = cp[i], s = sp_t[i], a = k[i], bb = k[i + HALF];
+        const float r0 = a * c - bb * s, r1 = a * s + bb * c;
+        kb[(size_t)pos * D + i] = r0;
+        kb[(size_t)pos * D + i + HALF] = r1;
+        knew[i] = r0;
+        knew[i + HALF] = r1;
+    }
+    for (int i = tid; i < D; i += blockDim.x) {
+        const float v = row[(size_t)(NH + NKV + g) * D + i];
+        vb[(size_t)pos * D + i] = v;
+        vnew[i] = v;
+    }
+    // q of this warp's head: lane holds elements lane + 32 j; the RoPE partner of element e < HALF is e + HALF = the
+    // same lane, j + PER / 2
+    float qr[PER];
+    {
+        float* q = row + (size_t)head * D;
+#pragma unroll
+        for (int j = 0; j < PER; ++j) qr[j] = q[lane + 32 * j];
+#pragma unroll
+        for (int j = 0; j < PER / 2; ++j) {
+            const float c = cp[lane + 32 * j], s = sp_t[lane + 32 * j], a = qr[j], bb = qr[j + PER / 2];
+            qr[j] = a * c - bb * s;
+            qr[j + PER / 2] = a * s + bb * c;
+        }
+        if (sp == 0) {
+#pragma unroll
+            for (int j = 0; j < PER; ++j) q[lane + 32 * j] = qr[j];  // the contract says "RoPE on q in place"
+        }
+    }
+    __syncthreads();
+    const float scale = 1.0f / sqrtf((float)D);
+    float m = -INFINITY, l = 0.f, acc[PER];
+#pragma unroll
+    for (int j = 0; j < PER; ++j) acc[j] = 0.f;
+    // K / V rows go through shared memory, CH positions at a time, double-buffered with cp.async: the R query heads of
+    // the group (and the S slices) read every row, and R x S separate L2 reads of it were the limiter of the first
+    // version (25 MB of f32 K/V per layer at batch 64 turned into 100 MB of L2 -> SM traffic).
+    float* kbuf = mg_a + (S > 1 ? (size_t)nwarps * D : 0);  // [2][CH][D]
+    float* vbuf = kbuf + 2 * CH * D;                         // [2][CH][D]
+    const int nchunks = pos / CH + 1;
+    auto load_chunk = [&](int c, int buf) {
+        constexpr int D4 = D / 4;
+        for (int idx = tid; idx < CH * D4; idx += blockDim.x) {
+            const int p = c * CH + idx / D4, e = (idx % D4) * 4;
+            float* kd = kbuf + ((size_t)buf * CH) * D + (size_t)idx * 4;
+            float* vd = vbuf + ((size_t)buf * CH) * D + (size_t)idx * 4;
+            if (p < pos) {
+                cp_async16(kd, kb + (size_t)p * D + e);
+                cp_async16(vd, vb + (size_t)p * D + e);
+            } else if (p == pos) {  // this step's row: from the CTA's own copy
+                *reinterpret_cast<float4*>(kd) = *reinterpret_cast<const float4*>(knew + e);
+                *reinterpret_cast<float4*>(vd) = *reinterpret_cast<const float4*>(vnew + e);
+            }
+        }
+        cp_async_commit();
+    };
+    load_chunk(0, 0);
+    for (int c = 0; c < nchunks; ++c) {
+        if (c + 1 < nchunks) {
+            load_chunk(c + 1, (c + 1) & 1);
+            cp_async_wait<1>();
+        } else {
+            cp_async_wait<0>();
+        }
+        __syncthreads();
+        const float* kch = kbuf + ((size_t)(c & 1) * CH) * D;
+        const float* vch = vbuf + ((size_t)(c & 1) * CH) * D;
+        for (int i0 = sp; i0 < CH && c * CH + i0 <= pos; i0 += 4 * S) {
+            float sc[4];
+            bool ok[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int i = i0 + u * S;
+                ok[u] = i < CH && c * CH + i <= pos;
+                const float* kp = kch + (size_t)(ok[u] ? i : i0) * D;
+                float d = 0.f;
+#pragma unroll
+                for (int j = 0; j < PER; ++j) d = fmaf(qr[j], kp[lane + 32 * j], d);
+                sc[u] = d;
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+                for (int u = 0; u < 4; ++u) sc[u] += __shfl_xor_sync(0xffffffffu, sc[u], o);
+            }
+            float mn = m;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                sc[u] = ok[u] ? sc[u] * scale : -INFINITY;
+                mn = fmaxf(mn, sc[u]);
+            }
+            const float corr = expf(m - mn);  // first step: exp(-inf) = 0
+            float w[4], ws = 0.f;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                w[u] = expf(sc[u] - mn);      // masked positions: exp(-inf) = 0
+                ws += w[u];
+            }
+            l = l * corr + ws;
+#pragma unroll
+            for (int j = 0; j < PER; ++j) {
+                float a = acc[j] * corr;
+#pragma unroll
+                for (int u = 0; u < 4; ++u) a = fmaf(w[u], vch[(size_t)(ok[u] ? i0 + u * S : i0) * D + lane + 32 * j], a);
+                acc[j] = a;
+            }
+            m = mn;
+        }
+        __syncthreads();  // the buffer is refilled two chunks later
+    }
+    if (S > 1) {  // merge the S slices of a head (log-sum-exp); a slice that saw no position has m = -inf, l = 0
+        if (lane == 0) {
+            mg_m[warp] = m;
+            mg_l[warp] = l;
+        }
+#pragma unroll
+        for (int j = 0; j < PER; ++j) mg_a[(size_t)warp * D + lane + 32 * j] = acc[j];
+        __syncthreads();
+        if (sp != 0) return;
+        float M = -INFINITY;
+        for (int t = 0; t < S; ++t) M = fmaxf(M, mg_m[hq * S + t]);
+        l = 0.f;
+#pragma unroll
+        for (int j = 0; j < PER; ++j) acc[j] = 0.f;
+        for (int t = 0; t < S; ++t) {
+            const float f = expf(mg_m[hq * S + t] - M);
+            l = fmaf(mg_l[hq * S + t], f, l);
+#pragma unroll
+            for (int j = 0; j < PER; ++j) acc[j] = fmaf(mg_a[(size_t)(hq * S + t) * D + lane + 32 * j], f, acc[j]);
+        }
+    }
+    const float inv = 1.0f / l;
+#pragma unroll
+    for (int j = 0; j < PER; ++j) att[((size_t)b * NH + head) * D + lane + 32 * j] = acc[j] * inv;
+}
+
+static size_t rope_attn_gqa_smem(int R, int S, int D) {
+    const int warps = R * S, CH = D <= 128 ? 16 : 8;
+    return ((size_t)2 * D + ((2 * warps + 3) & ~3) + (S > 1 ? (size_t)warps * D : 0) + (size_t)4 * CH * D) * 4;
+}
+
+template <int PER>
+static int launch_rope_attn_gqa(const bitnet_b200_ctx* ctx, float* qkv, const float* cos_t, const float* sin_t, float* kc,
+                                float* vc, const int32_t* pos_dev, int B, int NH, int NKV, int max_ctx, int S, float* att) {
+    const int warps = NH / NKV * S, D = 32 * PER;
+    const size_t smem = rope_attn_gqa_smem(NH / NKV, S, D);
+    tp_rope_attn_gqa_kernel<PER><<<dim3(NKV, B), 32 * warps, smem, ctx->stream>>>(qkv, cos_t, sin_t, kc, vc, att, pos_dev, NH, NKV,
+                                                                                 max_ctx, S);
+    B200_LAUNCH_CHECK("tp_rope_attn_gqa_kernel");
+    return 0;
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -302,6 +497,18 @@ int bitnet_b200_rope_attn_decode(bitnet_b200_ctx* ctx, float* qkv, const float* 
     if (B <= 0 || NH <= 0 || NKV <= 0 || NH % NKV != 0) return fail("rope_attn_decode: invalid head counts");
     if (D % 64 != 0 || D > 256 || max_ctx <= 0 || max_ctx > 12000) return fail("rope_attn_decode: unsupported head_dim / max_ctx");
     B200_CUDA(cudaSetDevice(ctx->device));
+    {
+        // fused kernel: position slices per head from the context bound (the position itself lives on the device)
+        const int R = NH / NKV;
+        int S = max_ctx <= 256 ? 1 : max_ctx <= 1024 ? 2 : max_ctx <= 4096 ? 4 : 8;
+        while (S > 1 && (R * S > 16 || rope_attn_gqa_smem(R, S, D) > 48 * 1024)) S >>= 1;
+        const bool off = getenv("BITNET_B200_TP_ATTN_SPLIT") != nullptr;  // diagnostics / tests: the two-kernel form
+        if (!off && R * S <= 16 && rope_attn_gqa_smem(R, S, D) <= 48 * 1024) {
+            if (D == 64) return launch_rope_attn_gqa<2>(ctx, qkv, cos_t, sin_t, kc, vc, pos_dev, B, NH, NKV, max_ctx, S, att);
+            if (D == 128) return launch_rope_attn_gqa<4>(ctx, qkv, cos_t, sin_t, kc, vc, pos_dev, B, NH, NKV, max_ctx, S, att);
+            if (D == 256) return launch_rope_attn_gqa<8>(ctx, qkv, cos_t, sin_t, kc, vc, pos_dev, B, NH, NKV, max_ctx, S, att);
+        }
+    }
     tp_rope_kv_kernel<<<dim3(NH + 2 * NKV, B), D / 2, 0, ctx->stream>>>(qkv, cos_t, sin_t, kc, vc, pos_dev, NH, NKV, D, max_ctx);
     B200_LAUNCH_CHECK("tp_rope_kv_kernel");
     tp_attn_decode_kernel<<<dim3(NH, B), 128, (size_t)max_ctx * 4, ctx->stream>>>(qkv, kc, vc, att, pos_dev, NH, NKV, D, max_ctx);

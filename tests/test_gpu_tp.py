@@ -185,3 +185,42 @@ def test_8b_geometry_two_layer_decoder_matches_the_oracle_model(ctx, b200, oracl
         for d in ranks:
             assert d.tokens.cpu().tolist() == toks, "step %d" % step
     om.close()
+
+
+# the fused RoPE + KV append + GQA attention kernel against the two-kernel form it replaces and a torch fp32 reference:
+# caches and the rotated q bit-equal (same arithmetic), attention within fp32 summation-order noise. Head counts, head
+# sizes and context bounds cover 1 / 2 / 4 position slices per head, the first position, and a long context.
+@pytest.mark.parametrize("NH,NKV,D,max_ctx,pos", [(8, 2, 64, 16, 0), (8, 2, 64, 16, 9), (32, 8, 128, 128, 57), (20, 5, 128, 600, 333),
+                                                   (4, 4, 128, 2048, 1500), (16, 2, 256, 300, 77), (4, 1, 128, 5000, 4100)])
+def test_fused_rope_attention_matches_the_two_kernel_form(ctx, b200, monkeypatch, NH, NKV, D, max_ctx, pos):
+    B = 3
+    g = torch.Generator(device="cuda").manual_seed(NH * 1000 + pos)
+    qkv0 = torch.randn(B, (NH + 2 * NKV) * D, device="cuda", generator=g)
+    kc0 = torch.randn(B, NKV, max_ctx, D, device="cuda", generator=g)
+    vc0 = torch.randn(B, NKV, max_ctx, D, device="cuda", generator=g)
+    ang = torch.rand(max_ctx, D // 2, device="cuda", generator=g) * 6.28
+    cos, sin = ang.cos().contiguous(), ang.sin().contiguous()
+    posd = torch.tensor(pos, dtype=torch.int32, device="cuda")
+    outs = []
+    for split in (True, False):
+        if split:
+            monkeypatch.setenv("BITNET_B200_TP_ATTN_SPLIT", "1")
+        else:
+            monkeypatch.delenv("BITNET_B200_TP_ATTN_SPLIT")
+        qkv, kc, vc = qkv0.clone(), kc0.clone(), vc0.clone()
+        l0 = b200.launch_count()
+        att = ctx.rope_attn_decode(qkv, cos, sin, kc, vc, posd, NH, NKV, D, max_ctx)
+        torch.cuda.synchronize()
+        outs.append((qkv, kc, vc, att, b200.launch_count() - l0))
+    (q_a, k_a, v_a, att_a, n_a), (q_b, k_b, v_b, att_b, n_b) = outs
+    assert (n_a, n_b) == (2, 1)
+    assert torch.equal(k_a, k_b) and torch.equal(v_a, v_b) and torch.equal(q_a, q_b)
+    # torch fp32 reference on the rotated q and the appended caches
+    R = NH // NKV
+    q = q_b[:, :NH * D].view(B, NKV, R, D)
+    K, V = k_b[:, :, :pos + 1], v_b[:, :, :pos + 1]
+    sc = torch.einsum("bgrd,bgpd->bgrp", q.double(), K.double()) / (D ** 0.5)
+    ref = torch.einsum("bgrp,bgpd->bgrd", sc.softmax(-1), V.double()).reshape(B, NH * D).float()
+    scale = ref.abs().max().item()
+    assert (att_b - ref).abs().max().item() < 2e-5 * max(scale, 1.0)
+    assert (att_a - ref).abs().max().item() < 2e-5 * max(scale, 1.0)
