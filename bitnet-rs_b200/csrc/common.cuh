@@ -195,7 +195,8 @@ __device__ __forceinline__ bool mbar_try_wait(void* bar, uint32_t parity) {
         : "memory");
     return ok != 0;
 }
-// bounded wait: a lost completion traps (reported as a launch failure) instead of hanging the GPU
+// bounded wait: a lost completion traps (reported as a launch failure) instead of hanging the GPU. (A non-blocking
+// mbarrier.test_wait probe in front of the try_wait loop was measured: no difference in any kernel here.)
 __device__ __forceinline__ void mbar_wait(void* bar, uint32_t parity) {
     for (uint32_t it = 0; !mbar_try_wait(bar, parity); ++it)
         if (it > (1u << 28)) __trap();
