@@ -37,6 +37,7 @@
 //     that all 148 SMs stream weights; the int32 partials meet in an L2-resident block through RED.ADD,
 //     the last CTA of a tile (ticket counter) scales it into y and re-zeroes the block -- integer
 //     addition, so the result is independent of arrival order and stays bit-exact.
+#include <cstdio>
 #include <mutex>
 
 #include "tcgen05.cuh"
@@ -487,6 +488,10 @@ int launch_gemm_i8(const bitnet_b200_ctx* ctx, const bitnet_b200_weight* w, cons
     // the packed ring HBM latency (small M), the A ring the decode chain
     p.n_pk = p.BN > 128 ? 2 : 8;
     p.n_a = p.BN > 128 ? 5 : 6;
+    if (const char* e = getenv("BITNET_B200_GEMM_RINGS")) {  // tuning knob: "n_a,n_pk" (decoded-weight / packed-code stages)
+        int na = 0, npk = 0;
+        if (sscanf(e, "%d,%d", &na, &npk) == 2 && na >= 4 && na <= 8 && npk >= 2 && npk <= 8) p.n_a = na, p.n_pk = npk;
+    }
     const size_t fixed = (size_t)p.n_a * G_A_BYTES + (size_t)p.n_pk * G_PK_BYTES + 1024 + G_BAR_BYTES;
     p.n_b = (int)((227 * 1024 - fixed) / ((size_t)p.BN * 128));
     if (p.n_b > G_NB_MAX) p.n_b = G_NB_MAX;
