@@ -664,19 +664,23 @@ static bool small_autotune(const bitnet_b200_ctx* ctx, const bitnet_b200_weight*
         pl.RW = rg[0], pl.KW = rg[1];
         if (small_derive_resident(ctx, w, M, &pl)) cands.emplace_back(0.0, pl);
     }
-    static void* flush[16] = {};
-    constexpr size_t FLUSH_BYTES = 256u << 20;  // > L2
-    const int dev = ctx->device;
-    if (dev >= 0 && dev < 16 && !flush[dev] && cudaMalloc(&flush[dev], FLUSH_BYTES) != cudaSuccess) {
+    // L2 flush buffer (> L2): allocated for the duration of this one tuning pass only; without it (allocation failed) the
+    // candidates are timed L2-warm, which still ranks them
+    constexpr size_t FLUSH_BYTES = 256u << 20;
+    void* flush = nullptr;
+    if (cudaMalloc(&flush, FLUSH_BYTES) != cudaSuccess) {
         cudaGetLastError();
-        flush[dev] = nullptr;
+        flush = nullptr;
     }
     cudaEvent_t e0, e1;
-    if (cudaEventCreate(&e0) != cudaSuccess || cudaEventCreate(&e1) != cudaSuccess) return false;
+    if (cudaEventCreate(&e0) != cudaSuccess || cudaEventCreate(&e1) != cudaSuccess) {
+        if (flush) cudaFree(flush);
+        return false;
+    }
     auto timed = [&](auto&& launch) -> float {
         float best = 1e30f;
         for (int rep = 0; rep < 5; ++rep) {
-            if (dev >= 0 && dev < 16 && flush[dev]) cudaMemsetAsync(flush[dev], rep & 1, FLUSH_BYTES, ctx->stream);
+            if (flush) cudaMemsetAsync(flush, rep & 1, FLUSH_BYTES, ctx->stream);
             cudaEventRecord(e0, ctx->stream);
             if (launch() != 0) {  // e.g. a cluster shape this device cannot co-schedule: not a candidate
                 cudaGetLastError();
@@ -711,6 +715,10 @@ static bool small_autotune(const bitnet_b200_ctx* ctx, const bitnet_b200_weight*
         });
     cudaEventDestroy(e0);
     cudaEventDestroy(e1);
+    if (flush) {
+        cudaStreamSynchronize(ctx->stream);
+        cudaFree(flush);
+    }
     if (out->us_small >= 1e29f && out->us_alt >= 1e29f) return false;
     out->use_alt = out->us_alt < out->us_small;
     return true;
