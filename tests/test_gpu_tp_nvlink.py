@@ -21,4 +21,6 @@ def test_tp_decoder_on_real_ranks_is_bit_identical(world):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world), "--master-addr",
            "127.0.0.1", "--master-port", str(29540 + world), os.path.join(ROOT, "tests", "tp_nvlink_worker.py")]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
+    if r.returncode == 0 and "TP_NVLINK_UNAVAILABLE" in r.stdout:
+        pytest.skip(r.stdout.strip().splitlines()[-1])
     assert r.returncode == 0 and "TP_NVLINK_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]

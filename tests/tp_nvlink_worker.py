@@ -47,7 +47,19 @@ def main():
             ts.append(dec.tokens.clone())
         return hs, ts
 
-    fabric = b2.TpFabric.symmetric(torch, dist, torch.device("cuda", local), shape.batch, shape.hidden)
+    try:
+        fabric = b2.TpFabric.symmetric(torch, dist, torch.device("cuda", local), shape.batch, shape.hidden)
+        avail = torch.tensor([1], device="cuda")
+    except Exception as ex:      # no P2P / symmetric memory between these GPUs: nothing to test here
+        fabric, avail = None, torch.tensor([0], device="cuda")
+        why = repr(ex)
+    dist.all_reduce(avail, op=dist.ReduceOp.MIN)
+    if int(avail[0]) == 0:
+        if rank == 0:
+            print("TP_NVLINK_UNAVAILABLE: torch symmetric memory could not be set up (%s)" % (why if fabric is None else "on a peer"))
+        dist.barrier()
+        dist.destroy_process_group()
+        sys.exit(0)
     fused = b2.TPDecoder(ctx, shape, rank, world, fabric=fabric)
     h_f, t_f = run(fused, steps)
     h_g, t_g = run(fused, steps, graph=True)
