@@ -301,6 +301,25 @@ def test_linear_qk256_gemm_small(ctx, b200, oracle, rows, cols, M, monkeypatch):
     assert torch.equal(acc3, acc) and torch.equal(y3, y)
 
 
+# both sides of every routing boundary of linear_i8 on one weight: GEMV | gemm_small (M = 8 | 9), gemm_small | tcgen05
+# (M = 64 | 65), and the token-tile edges in between -- whichever kernel the first-use timing picks, the same integers
+@pytest.mark.parametrize("rows,cols", [(3840, 2560), (2560, 6912), (6144, 4096)])
+def test_linear_qk256_every_routing_boundary(ctx, b200, oracle, rows, cols):
+    qs = oracle.fill_bytes(rows * cols // 4, 0xB2000000 + rows)
+    w = ctx.weight(qs, b200.LAYOUT_QK256, rows, cols)
+    seen = set()
+    for M in (1, 4, 8, 9, 16, 17, 32, 33, 48, 49, 64, 65, 128):
+        x = oracle.fill_normal(M * cols, 1000 + M).reshape(M, cols)
+        q, s = oracle.quantize_rows_i8(x)
+        racc, ry = oracle.linear_qk256_i8(qs, rows, cols, q, s)
+        for _ in range(2):      # first call of a shape may be the timing pass, the second runs the chosen kernel
+            y, acc = ctx.linear_i8(w, dev(q), dev(s), want_acc=True)
+            assert np.array_equal(acc.cpu().numpy(), racc), (M, b200.last_linear_kernel())
+            assert np.array_equal(y.cpu().numpy(), ry), (M, b200.last_linear_kernel())
+        seen.add(b200.last_linear_kernel())
+    assert "gemm_tcgen05" in seen and ("gemm_small" in seen or "gemm_small_resident" in seen)
+
+
 # a spread of the planner's search space (row warps, k warps, segments per warp, cluster K split): warp grids, ragged row
 # groups, ragged last chunks (zero-filled by the TMA unit), ring wrap-around (more chunks than stages), DSMEM reduction
 @pytest.mark.parametrize("rows,cols,M,plans", [
