@@ -14,7 +14,19 @@ template <int VAR>
 __device__ __forceinline__ void body(uint32_t w, uint32_t lut, uint2 b, int (&c)[4]) {
     uint32_t x, y, z, v;
     if (VAR == 2) { x = w; y = w ^ lut; z = w + lut; v = w - lut; }
-    else {
+    else if (VAR == 4) {  // mixed: one of the three shifts on the FMA pipe (IMAD.HI), two on the ALU pipe (SHF)
+        const uint32_t m0 = w & 0x33333333u;
+        const uint32_t m1 = (w >> 2) & 0x33333333u;
+        x = prmt(lut, 0u, m0); y = prmt(lut, 0u, m1);
+        z = prmt(lut, 0u, __umulhi(m0, 0x10000u));
+        v = prmt(lut, 0u, m1 >> 16);
+    } else if (VAR == 5) {  // PRMT as the shifter: byte-select the upper halfword instead of shifting
+        const uint32_t m0 = w & 0x33333333u;
+        const uint32_t m1 = (w >> 2) & 0x33333333u;
+        x = prmt(lut, 0u, m0); y = prmt(lut, 0u, m1);
+        z = prmt(lut, 0u, prmt(m0, 0u, 0x4432u));
+        v = prmt(lut, 0u, prmt(m1, 0u, 0x4432u));
+    } else {
         const uint32_t m0 = w & 0x33333333u;
         const uint32_t m1 = (VAR == 1 ? (w >> 2) : __umulhi(w, 0x40000000u)) & 0x33333333u;
         x = prmt(lut, 0u, m0); y = prmt(lut, 0u, m1);
@@ -73,6 +85,8 @@ int main() {
            (double)h / tiles / (15.0 * NC), 128.0 * 15 * NC * tiles / h, cudaGetErrorString(cudaGetLastError()));
     RUN("imad.hi decode + imma, 6 chunks", 0, 6, false)
     RUN("shf decode + imma, 6 chunks", 1, 6, false)
+    RUN("mixed (1 imad.hi + 2 shf) + imma, 6 chunks", 4, 6, false)
+    RUN("prmt-as-shift decode + imma, 6 chunks", 5, 6, false)
     RUN("no decode, imma only, 6 chunks", 2, 6, false)
     RUN("imad.hi decode, no imma, 6 chunks", 3, 6, false)
     RUN("imad.hi decode + imma, 6 chunks, mbarrier", 0, 6, true)
