@@ -408,6 +408,11 @@ __device__ __forceinline__ void mega_tile(const unsigned char* base, int soff, c
         for (int j = 0; j < 4; ++j) c0[j] = c1[j] = 0;
 #pragma unroll
         for (int c = 0; c < MAXC; ++c) {
+            // the last chunk slot exists only in the warps whose K share rounds up (5 of 15 at 80 chunks): a
+            // warp-uniform skip saves its decode + IMMA in the others (the ALU pipe is what the tiles are bound by:
+            // measured 358 -> 342 us for the GEMV phases of a step. Testing the last TWO slots, or adding the same test to
+            // the BitNet32-F16 loop below, measured slower again for THIS loop -- the kernel is sensitive to code layout)
+            if (c == MAXC - 1 && nc < MAXC) break;
             const uint4 d = decode16(w[c], lut);
             if (c & 1) mma_s8_m16n8k32(c1, d.x, d.y, d.z, d.w, b[c].x, b[c].y);
             else mma_s8_m16n8k32(c0, d.x, d.y, d.z, d.w, b[c].x, b[c].y);
