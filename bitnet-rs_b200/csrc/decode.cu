@@ -11,6 +11,7 @@
 // position lives in device memory so the same graph replays for every token, and the greedy
 // token is fed back on device so a decode loop needs no host round trip.
 #include <cstdio>
+#include <cstring>
 #include <memory>
 #include <vector>
 
@@ -869,6 +870,40 @@ int bitnet_b200_model_time_linears(bitnet_b200_model* m, int reps, float* ms_per
             cudaEventDestroy(e1);
             if (rc) return -1;
             if (e != cudaSuccess) return fail_cuda("model_time_linears", e);
+            // The pass that was timed must have computed the linears: what the LAST layer's qkv and down phases left in
+            // the hand-off buffers is compared with the stand-alone GEMV on the same fixed int8 rows (QK256: the same
+            // one-multiply epilogue on the same int32 sums, bit for bit; BitNet32-F16: f32 block sums in another order).
+            {
+                const LayerW& L = m->layers[(size_t)c.n_layers - 1];
+                const bitnet_b200_weight* ws[2] = {L.wqkv, L.wdown};
+                const uint2* outs[2] = {m->mega_p.qkv, m->mega_p.x};
+                for (int k = 0; k < 2; ++k) {
+                    const size_t n = (size_t)B * ws[k]->rows;
+                    float* ref = nullptr;
+                    B200_CUDA(cudaMalloc(&ref, n * sizeof(float)));
+                    std::vector<float> h_ref(n);
+                    std::vector<uint2> h_out(n);
+                    int rc2 = launch_gemv_i8(m->ctx, ws[k], m->q8, m->s8, B, ref, nullptr, nullptr);
+                    if (!rc2 && cudaMemcpyAsync(h_ref.data(), ref, n * sizeof(float), cudaMemcpyDeviceToHost, st) != cudaSuccess) rc2 = -1;
+                    if (!rc2 && cudaMemcpyAsync(h_out.data(), outs[k], n * sizeof(uint2), cudaMemcpyDeviceToHost, st) != cudaSuccess) rc2 = -1;
+                    if (!rc2 && cudaStreamSynchronize(st) != cudaSuccess) rc2 = -1;
+                    cudaFree(ref);
+                    if (rc2) return fail("model_time_linears: could not verify the GEMV-phase pass");
+                    float amax = 0.f;
+                    for (size_t i = 0; i < n; ++i) amax = fmaxf(amax, fabsf(h_ref[i]));
+                    const float tol = m->mega_p.layout == 0 ? 0.f : 1e-4f * amax;
+                    for (size_t i = 0; i < n; ++i) {
+                        float v;
+                        memcpy(&v, &h_out[i].x, 4);
+                        if (!(fabsf(v - h_ref[i]) <= tol)) {
+                            char buf[200];
+                            snprintf(buf, sizeof buf, "model_time_linears: the GEMV-phase pass disagrees with linear_i8 (%s, element %zu: %g vs %g)",
+                                     k == 0 ? "qkv" : "down", i, (double)v, (double)h_ref[i]);
+                            return fail(buf);
+                        }
+                    }
+                }
+            }
             *ms_per_pass = ms / (float)reps;
             *launches_per_pass = 1;
             return 0;

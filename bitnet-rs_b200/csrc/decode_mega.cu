@@ -281,9 +281,19 @@ __device__ __forceinline__ void mega_prologue(const MegaParams& p, const MegaSme
     if (pro == 0) {
         cons_sync();  // the previous phase's readers of sm.red / sm.act are done
         for (int m = 0; m < p.B; ++m) {
-            const int8_t* src = p.q_fixed + (size_t)m * K + 32 * kc0 + lane;
-#pragma unroll 4
-            for (int c = 0; c < nc; ++c) qb[m * q_ld + 32 * c] = (unsigned char)src[32 * c];
+            // the warp's nc * 32 bytes as 32-bit words, all loads in flight before the first store: the four bytes of
+            // source word a of a chunk are the B-fragment bytes 8 (a & 3) + 4 (a >> 2) .. + 3 (bfrag_pos), i.e. one
+            // aligned word in shared memory. (Byte loads, four in flight, cost 1-1.4 us of L2 latency per phase here.)
+            const uint32_t* src = reinterpret_cast<const uint32_t*>(p.q_fixed + (size_t)m * K + 32 * kc0);
+            unsigned char* dstrow = sm.act + m * q_ld + 32 * kc0;
+            uint32_t v[4];
+#pragma unroll
+            for (int r = 0; r < 4; ++r) v[r] = lane + 32 * r < nc * 8 ? __ldg(src + lane + 32 * r) : 0u;
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                const int wd = lane + 32 * r, a = wd & 7;
+                if (wd < nc * 8) *reinterpret_cast<uint32_t*>(dstrow + 32 * (wd >> 3) + 8 * (a & 3) + 4 * (a >> 2)) = v[r];
+            }
             const float s = p.s_fixed[m];
 #pragma unroll
             for (int j = 0; j < MEGA_MAXB; ++j) sc[j] = j == m ? s : sc[j];
@@ -395,13 +405,16 @@ __device__ __forceinline__ void mega_store_partial(int* rw, int i, int B, const 
 // while they fly (its MMAs have long completed), then PRMT decode + IMMA on two accumulator chains. Fully unrolled
 // over MAXC on purpose: ~11 instructions per chunk, 1-3 KB of code; the rolled form measured 2 x slower (LDS latency
 // and loop overhead exposed in every chunk).
-template <int MAXC, bool BN32>
+// EXACT: every warp owns MAXC - 1 or MAXC chunks (the 2B-4T shapes: 80 and 216 chunks over 15 warps), so only the last
+// slot's address depends on nc and the other loads carry immediate offsets (no select + multiply per chunk).
+template <int MAXC, bool BN32, bool EXACT>
 __device__ __forceinline__ void mega_tile(const unsigned char* base, int soff, const uint2 (&b)[MAXC], int nc, uint32_t lut, int* rw,
                                           int i, int B, bool have_prev, const int (&p0)[4], const int (&p1)[4], int (&c0)[4],
                                           int (&c1)[4]) {
     uint32_t w[MAXC];
 #pragma unroll
-    for (int c = 0; c < MAXC; ++c) w[c] = *reinterpret_cast<const uint32_t*>(base + (c < nc ? c : 0) * 128);
+    for (int c = 0; c < MAXC; ++c)
+        w[c] = *reinterpret_cast<const uint32_t*>(base + ((EXACT && c < MAXC - 1) || c < nc ? c : 0) * 128);
     if (have_prev) mega_store_partial(rw, i - 1, B, p0, p1);
     if (!BN32) {
 #pragma unroll
@@ -446,7 +459,7 @@ __device__ __forceinline__ void mega_tile(const unsigned char* base, int soff, c
 // The warp's k-chunks of every tile of the CTA: B fragments in registers for the whole phase; the per-warp partial of
 // a tile goes to sm.red. A ring slot carries o.T consecutive tiles (one bulk copy, one full / empty barrier pair):
 // the mbarrier probe costs ~200 cycles even when the data is there, so it is paid once per slot, not per tile.
-template <int MAXC, bool BN32>
+template <int MAXC, bool BN32, bool EXACT>
 __device__ __forceinline__ void mega_tiles(const MegaParams& p, const MegaSmem& sm, const MegaOp& o, int nloc, int kc0, int nc,
                                            RingPos& rp, int& wi) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -490,7 +503,7 @@ __device__ __forceinline__ void mega_tiles(const MegaParams& p, const MegaSmem& 
 #pragma unroll 1
     for (int i = 0; i < nloc; i += 2) {  // two bodies per trip: the accumulator sets alternate without register moves
         enter(i);
-        mega_tile<MAXC, BN32>(base, soff, b, nc, lut, rw, i, B, i > 0, e0, e1, a0, a1);
+        mega_tile<MAXC, BN32, EXACT>(base, soff, b, nc, lut, rw, i, B, i > 0, e0, e1, a0, a1);
         leave();
         wtrace(p, wi, 4);
         if (i + 1 >= nloc) {
@@ -498,7 +511,7 @@ __device__ __forceinline__ void mega_tiles(const MegaParams& p, const MegaSmem& 
             break;
         }
         enter(i + 1);
-        mega_tile<MAXC, BN32>(base, soff, b, nc, lut, rw, i + 1, B, true, a0, a1, e0, e1);
+        mega_tile<MAXC, BN32, EXACT>(base, soff, b, nc, lut, rw, i + 1, B, true, a0, a1, e0, e1);
         leave();
         wtrace(p, wi, 4);
         if (i + 2 >= nloc) {
@@ -539,14 +552,16 @@ __device__ __forceinline__ void mega_gemv_phase(const MegaParams& p, const MegaS
     prof_stamp(p, pi);  // prologue done
     // exact instances for the shapes that matter (2B-4T: 80 and 216 k-chunks over 15 warps = 6 and 15 each), generic otherwise
     if (p.layout == 0) {
-        if (o.KC <= 6 * MEGA_NW) mega_tiles<6, false>(p, sm, o, q.nloc, kc0, nc, rp, wi);
-        else if (o.KC <= 10 * MEGA_NW) mega_tiles<10, false>(p, sm, o, q.nloc, kc0, nc, rp, wi);
-        else if (o.KC <= 15 * MEGA_NW) mega_tiles<15, false>(p, sm, o, q.nloc, kc0, nc, rp, wi);
-        else mega_tiles<MEGA_MAXC, false>(p, sm, o, q.nloc, kc0, nc, rp, wi);
+        if (o.KC <= 6 * MEGA_NW && o.KC >= 5 * MEGA_NW) mega_tiles<6, false, true>(p, sm, o, q.nloc, kc0, nc, rp, wi);
+        else if (o.KC <= 15 * MEGA_NW && o.KC >= 14 * MEGA_NW) mega_tiles<15, false, true>(p, sm, o, q.nloc, kc0, nc, rp, wi);
+        else if (o.KC <= 6 * MEGA_NW) mega_tiles<6, false, false>(p, sm, o, q.nloc, kc0, nc, rp, wi);
+        else if (o.KC <= 10 * MEGA_NW) mega_tiles<10, false, false>(p, sm, o, q.nloc, kc0, nc, rp, wi);
+        else if (o.KC <= 15 * MEGA_NW) mega_tiles<15, false, false>(p, sm, o, q.nloc, kc0, nc, rp, wi);
+        else mega_tiles<MEGA_MAXC, false, false>(p, sm, o, q.nloc, kc0, nc, rp, wi);
     } else {
-        if (o.KC <= 6 * MEGA_NW) mega_tiles<6, true>(p, sm, o, q.nloc, kc0, nc, rp, wi);
-        else if (o.KC <= 15 * MEGA_NW) mega_tiles<15, true>(p, sm, o, q.nloc, kc0, nc, rp, wi);
-        else mega_tiles<MEGA_MAXC, true>(p, sm, o, q.nloc, kc0, nc, rp, wi);
+        if (o.KC <= 6 * MEGA_NW) mega_tiles<6, true, false>(p, sm, o, q.nloc, kc0, nc, rp, wi);
+        else if (o.KC <= 15 * MEGA_NW) mega_tiles<15, true, false>(p, sm, o, q.nloc, kc0, nc, rp, wi);
+        else mega_tiles<MEGA_MAXC, true, false>(p, sm, o, q.nloc, kc0, nc, rp, wi);
     }
     wtrace(p, wi, 5);
     cons_sync();
