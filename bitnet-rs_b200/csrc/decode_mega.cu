@@ -308,8 +308,15 @@ __device__ __forceinline__ void mega_prologue(const MegaParams& p, const MegaSme
         float amax = 0.f;
 #pragma unroll 1
         if (pro == 2 && m == 0) {  // norm weights (L2-prefetched by the previous phase): in flight under the polls
-#pragma unroll 4
-            for (int c = 0; c < nc; ++c) stg[K + 32 * c] = __ldg(gamma + 32 * (kc0 + c) + lane);
+#pragma unroll 1
+            for (int c0 = 0; c0 < nc; c0 += 8) {  // eight loads in flight, then their stores: one L2 round per 8 chunks
+                float t[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) t[j] = c0 + j < nc ? __ldg(gamma + 32 * (kc0 + c0 + j) + lane) : 0.f;
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    if (c0 + j < nc) stg[K + 32 * (c0 + j)] = t[j];
+            }
         }
         const unsigned long long valid0 = (unsigned long long)ep_in << 32;  // what a slot beyond nc pretends to hold: (0.0f, ep_in)
 #pragma unroll 1
