@@ -80,7 +80,7 @@ __global__ void __launch_bounds__(H_THREADS, 1)
 gemm_f16_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_codes, const __grid_constant__ CUtensorMap tm_q,
                         const GemmF16Params p) {
     extern __shared__ unsigned char hsm_raw[];
-    unsigned char* base = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(hsm_raw) + 1023) & ~(uintptr_t)1023);
+    unsigned char* base = hsm_raw + ((1024u - (smem_u32(hsm_raw) & 1023u)) & 1023u);  // offset arithmetic keeps the shared address space (LDS / STS, not generic LD / ST)
     const uint32_t b_stage_bytes = (uint32_t)p.BN * 128u;
     unsigned char* b_base = base + (size_t)p.n_a * H_A_BYTES;
     unsigned char* pk_base = b_base + (size_t)p.n_b * b_stage_bytes;

@@ -116,7 +116,7 @@ gemm_small_kernel(const __grid_constant__ CUtensorMap tm_codes, const __grid_con
     extern __shared__ unsigned char smem_raw[];
     // 1024-byte alignment: the swizzle patterns are functions of the absolute shared address (same offset in every CTA
     // of a cluster, so the DSMEM addresses below still match)
-    unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // offset arithmetic keeps the shared address space (LDS / STS, not generic LD / ST)
     uint64_t* full = reinterpret_cast<uint64_t*>(smem);
     uint64_t* empty = full + SMALL_MAX_STAGES;
     int4* red = reinterpret_cast<int4*>(smem + p.red_off);
@@ -282,7 +282,7 @@ __global__ void __launch_bounds__(32 * SMALL_MAX_CONS)
 gemm_small_resident_kernel(const __grid_constant__ CUtensorMap tm_codes, const __grid_constant__ CUtensorMap tm_q,
                            const SmallParams p) {
     extern __shared__ unsigned char smem_raw[];
-    unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // offset arithmetic keeps the shared address space (LDS / STS, not generic LD / ST)
     uint64_t* full = reinterpret_cast<uint64_t*>(smem);
     uint64_t* empty = full + SMALL_MAX_STAGES;
     uint64_t* afull = empty + SMALL_MAX_STAGES;

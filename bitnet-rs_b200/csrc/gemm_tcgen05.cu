@@ -100,7 +100,7 @@ gemm_i8_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_codes, const __gri
                        const GemmParams p) {
     extern __shared__ unsigned char gsm_raw[];
     // 1024-byte alignment: the swizzle pattern is a function of the absolute shared address
-    unsigned char* base = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(gsm_raw) + 1023) & ~(uintptr_t)1023);
+    unsigned char* base = gsm_raw + ((1024u - (smem_u32(gsm_raw) & 1023u)) & 1023u);  // offset arithmetic keeps the shared address space (LDS / STS, not generic LD / ST)
     const uint32_t b_stage_bytes = (uint32_t)p.BN * 128u;
     unsigned char* b_base = base + (size_t)p.n_a * G_A_BYTES;
     unsigned char* pk_base = b_base + (size_t)p.n_b * b_stage_bytes;
