@@ -293,12 +293,13 @@ __global__ void __launch_bounds__(512) tp_rope_attn_gqa_kernel(float* __restrict
             qr[j] = a * c - bb * s;
             qr[j + PER / 2] = a * s + bb * c;
         }
-        if (sp == 0) {
-#pragma unroll
-            for (int j = 0; j < PER; ++j) q[lane + 32 * j] = qr[j];  // the contract says "RoPE on q in place"
-        }
     }
-    __syncthreads();
+    __syncthreads();  // every slice of every head has read its (unrotated) q row
+    if (sp == 0) {    // the contract says "RoPE on q in place": only now, or a slower slice would rotate the row twice
+        float* q = row + (size_t)head * D;
+#pragma unroll
+        for (int j = 0; j < PER; ++j) q[lane + 32 * j] = qr[j];
+    }
     const float scale = 1.0f / sqrtf((float)D);
     float m = -INFINITY, l = 0.f, acc[PER];
 #pragma unroll

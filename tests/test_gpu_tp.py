@@ -224,3 +224,31 @@ def test_fused_rope_attention_matches_the_two_kernel_form(ctx, b200, monkeypatch
     scale = ref.abs().max().item()
     assert (att_b - ref).abs().max().item() < 2e-5 * max(scale, 1.0)
     assert (att_a - ref).abs().max().item() < 2e-5 * max(scale, 1.0)
+
+
+# several position slices share one q row and slice 0 writes the rotated row back in place: a slice that read the row
+# after that write would rotate it twice. Many sequences, many repeats: the attention must come out the same every time.
+@pytest.mark.parametrize("NH,NKV,D,max_ctx,pos", [(4, 4, 128, 2048, 1500), (8, 2, 128, 1024, 700), (2, 1, 64, 6000, 37)])
+def test_fused_rope_attention_slices_read_q_before_it_is_rotated_in_place(ctx, b200, NH, NKV, D, max_ctx, pos):
+    B = 48
+    g = torch.Generator(device="cuda").manual_seed(NH + pos)
+    qkv0 = torch.randn(B, (NH + 2 * NKV) * D, device="cuda", generator=g)
+    kc = torch.randn(B, NKV, max_ctx, D, device="cuda", generator=g)
+    vc = torch.randn(B, NKV, max_ctx, D, device="cuda", generator=g)
+    ang = torch.rand(max_ctx, D // 2, device="cuda", generator=g) * 6.28
+    cos, sin = ang.cos().contiguous(), ang.sin().contiguous()
+    posd = torch.tensor(pos, dtype=torch.int32, device="cuda")
+    first = None
+    for rep in range(25):
+        qkv = qkv0.clone()
+        att = ctx.rope_attn_decode(qkv, cos, sin, kc, vc, posd, NH, NKV, D, max_ctx)   # the cache row at pos is rewritten alike
+        torch.cuda.synchronize()
+        if first is None:
+            first = att.clone()
+            R = NH // NKV
+            q = qkv[:, :NH * D].view(B, NKV, R, D)
+            sc = torch.einsum("bgrd,bgpd->bgrp", q.double(), kc[:, :, :pos + 1].double()) / (D ** 0.5)
+            ref = torch.einsum("bgrp,bgpd->bgrd", sc.softmax(-1), vc[:, :, :pos + 1].double()).reshape(B, NH * D).float()
+            assert (att - ref).abs().max().item() < 2e-5 * max(ref.abs().max().item(), 1.0)
+        else:
+            assert torch.equal(att, first), "repeat %d differs" % rep
